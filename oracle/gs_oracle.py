@@ -1,0 +1,253 @@
+"""numpy/ctypes front-end of the CPU oracle (oracle/gs_oracle.c).
+
+TEST INFRASTRUCTURE ONLY — *** parity unpinned *** (see the header of gs_oracle.c).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module; the product package (mvs_gaussian_splatting_b200) never does.
+
+The functions mirror the stages of the rasterizer the reference calls at
+/root/reference/gaussian_renderer/__init__.py:257-265:
+  preprocess -> bin (emit keys, stable sort, tile ranges) -> blend forward
+  blend backward -> preprocess backward
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_build", "libgs_oracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with its Makefile (gcc only; no reference sources involved)."""
+    if force or not os.path.exists(_LIB_PATH) or (
+        os.path.getmtime(_LIB_PATH) < os.path.getmtime(os.path.join(_HERE, "gs_oracle.c"))
+    ):
+        subprocess.run(["make", "-C", _HERE], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.orc_count_instances_f32.restype = ctypes.c_int64
+        _lib.orc_count_instances_f64.restype = ctypes.c_int64
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _c(a, dt):
+    return None if a is None else np.ascontiguousarray(a, dtype=dt)
+
+
+def _fn(name, dt):
+    return getattr(lib(), f"{name}_{'f64' if dt == np.float64 else 'f32'}")
+
+
+def _real(dt):
+    return ctypes.c_double if dt == np.float64 else ctypes.c_float
+
+
+def grid(W, H):
+    return (W + 15) // 16, (H + 15) // 16
+
+
+def _ranges(n, threads):
+    threads = max(1, min(threads, n))
+    step = (n + threads - 1) // threads
+    return [(b, min(n, b + step)) for b in range(0, n, step)]
+
+
+def preprocess(means3D, scales, rotations, opacities, shs, viewmatrix, projmatrix, campos, W, H,
+               tanfovx, tanfovy, sh_degree, scale_modifier=1.0, cov3D_precomp=None,
+               colors_precomp=None, dtype=np.float32, threads=1):
+    """K1. viewmatrix/projmatrix are the reference's *transposed* 4x4 tensors
+    (scene/cameras.py:54-56); flattened row-major they are the column-major arrays the
+    kernels index."""
+    dt = dtype
+    R = _real(dt)
+    means3D = _c(means3D, dt)
+    P = means3D.shape[0]
+    shs = _c(shs, dt)
+    M = 0 if shs is None else shs.shape[1]
+    scales, rotations = _c(scales, dt), _c(rotations, dt)
+    opacities = _c(opacities, dt).reshape(-1)
+    cov3D_precomp, colors_precomp = _c(cov3D_precomp, dt), _c(colors_precomp, dt)
+    view, proj = _c(viewmatrix, dt).reshape(16), _c(projmatrix, dt).reshape(16)
+    campos = _c(campos, dt).reshape(3)
+    out = dict(
+        radii=np.zeros(P, np.int32), means2D=np.zeros((P, 2), dt), depths=np.zeros(P, dt),
+        cov3D=np.zeros((P, 6), dt), rgb=np.zeros((P, 3), dt), conic_opacity=np.zeros((P, 4), dt),
+        tiles_touched=np.zeros(P, np.uint32), rects=np.zeros((P, 4), np.int32),
+        clamped=np.zeros((P, 3), np.uint8),
+    )
+    f = _fn("orc_preprocess", dt)
+
+    def run(rg):
+        f(P, int(sh_degree), M, _p(means3D), _p(scales), R(scale_modifier), _p(rotations),
+          _p(opacities), _p(shs), _p(cov3D_precomp), _p(colors_precomp), _p(view), _p(proj),
+          _p(campos), W, H, R(tanfovx), R(tanfovy), _p(out["radii"]), _p(out["means2D"]),
+          _p(out["depths"]), _p(out["cov3D"]), _p(out["rgb"]), _p(out["conic_opacity"]),
+          _p(out["tiles_touched"]), _p(out["rects"]), _p(out["clamped"]), rg[0], rg[1])
+
+    _run_ranges(run, _ranges(P, threads))
+    return out
+
+
+def _run_ranges(run, ranges):
+    if len(ranges) <= 1:
+        for rg in ranges:
+            run(rg)
+    else:
+        with ThreadPoolExecutor(len(ranges)) as ex:
+            list(ex.map(run, ranges))
+
+
+def mark_visible(means3D, viewmatrix, dtype=np.float32):
+    means3D = _c(means3D, dtype)
+    P = means3D.shape[0]
+    view = _c(viewmatrix, dtype).reshape(16)
+    present = np.zeros(P, np.uint8)
+    _fn("orc_mark_visible", dtype)(P, _p(means3D), _p(view), _p(present))
+    return present.astype(bool)
+
+
+def bin_instances(pre, W, H, dtype=np.float32):
+    """K2..K6: returns unsorted + sorted key/value lists and per-tile ranges."""
+    P = pre["radii"].shape[0]
+    gx, gy = grid(W, H)
+    R = int(_fn("orc_count_instances", dtype)(P, _p(pre["tiles_touched"])))
+    n = max(R, 1)
+    ku, vu = np.zeros(n, np.uint64), np.zeros(n, np.uint32)
+    ks, vs = np.zeros(n, np.uint64), np.zeros(n, np.uint32)
+    ranges = np.zeros((gx * gy, 2), np.uint32)
+    _fn("orc_bin", dtype)(P, _p(pre["radii"]), _p(pre["rects"]), _p(pre["depths"]), W, H,
+                          ctypes.c_int64(R), _p(ku), _p(vu), _p(ks), _p(vs), _p(ranges))
+    return dict(num_rendered=R, keys_unsorted=ku[:R], values_unsorted=vu[:R], keys=ks[:R],
+                point_list=vs[:R], ranges=ranges)
+
+
+def blend_forward(pre, binned, bg, W, H, dtype=np.float32, margin=1e-4, threads=1):
+    """K7."""
+    dt = dtype
+    gx, gy = grid(W, H)
+    out = np.zeros((3, H, W), dt)
+    final_T = np.zeros((H, W), dt)
+    n_contrib = np.zeros((H, W), np.uint32)
+    fragile = np.zeros((H, W), np.uint8)
+    bg = _c(bg, dt).reshape(3)
+    pl = np.ascontiguousarray(binned["point_list"]) if binned["num_rendered"] else np.zeros(1, np.uint32)
+    f = _fn("orc_blend_fwd", dt)
+
+    def run(rg):
+        f(W, H, _p(binned["ranges"]), _p(pl), _p(pre["means2D"]), _p(pre["rgb"]),
+          _p(pre["conic_opacity"]), _p(bg), _p(out), _p(final_T), _p(n_contrib), _p(fragile),
+          _real(dt)(margin), rg[0], rg[1])
+
+    _run_ranges(run, _ranges(gx * gy, threads * 8 if threads > 1 else 1))
+    return dict(color=out, final_T=final_T, n_contrib=n_contrib, fragile=fragile.astype(bool))
+
+
+def blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype=np.float32, threads=1):
+    """K8. Returns dL/dmean2D [P,2] (NDC-scaled), dL/dconic [P,3] (true partials of A,B,C),
+    dL/dopacity [P], dL/dcolor [P,3]."""
+    dt = dtype
+    P = pre["radii"].shape[0]
+    gx, gy = grid(W, H)
+    bg = _c(bg, dt).reshape(3)
+    dL_dpix = _c(dL_dpix, dt)
+    pl = np.ascontiguousarray(binned["point_list"]) if binned["num_rendered"] else np.zeros(1, np.uint32)
+    f = _fn("orc_blend_bwd", dt)
+    rgs = _ranges(gx * gy, threads)
+    bufs = []
+
+    def run(rg):
+        g = dict(dL_dmean2D=np.zeros((P, 2), dt), dL_dconic=np.zeros((P, 3), dt),
+                 dL_dopacity=np.zeros(P, dt), dL_dcolor=np.zeros((P, 3), dt))
+        f(W, H, _p(binned["ranges"]), _p(pl), _p(pre["means2D"]), _p(pre["rgb"]),
+          _p(pre["conic_opacity"]), _p(bg), _p(fwd["final_T"]), _p(fwd["n_contrib"]), _p(dL_dpix),
+          _p(g["dL_dmean2D"]), _p(g["dL_dconic"]), _p(g["dL_dopacity"]), _p(g["dL_dcolor"]),
+          rg[0], rg[1])
+        bufs.append(g)
+
+    _run_ranges(run, rgs)
+    acc = bufs[0]
+    for g in bufs[1:]:
+        for k in acc:
+            acc[k] += g[k]
+    return acc
+
+
+def preprocess_backward(means3D, scales, rotations, shs, viewmatrix, projmatrix, campos, W, H,
+                        tanfovx, tanfovy, sh_degree, pre, gblend, scale_modifier=1.0,
+                        cov3D_precomp=None, colors_precomp=None, dtype=np.float32, threads=1):
+    """K9 + K10. All outputs fully written (zeros for culled Gaussians)."""
+    dt = dtype
+    R = _real(dt)
+    means3D = _c(means3D, dt)
+    P = means3D.shape[0]
+    shs = _c(shs, dt)
+    M = 0 if shs is None else shs.shape[1]
+    scales, rotations = _c(scales, dt), _c(rotations, dt)
+    view, proj = _c(viewmatrix, dt).reshape(16), _c(projmatrix, dt).reshape(16)
+    campos = _c(campos, dt).reshape(3)
+    cov_in = pre["cov3D"] if cov3D_precomp is None else _c(cov3D_precomp, dt)
+    out = dict(dL_dmeans3D=np.zeros((P, 3), dt), dL_dcov3D=np.zeros((P, 6), dt),
+               dL_dsh=None if shs is None else np.zeros((P, M, 3), dt),
+               dL_dscales=None if scales is None else np.zeros((P, 3), dt),
+               dL_drots=None if rotations is None else np.zeros((P, 4), dt))
+    f = _fn("orc_preprocess_bwd", dt)
+
+    def run(rg):
+        f(P, int(sh_degree), M, _p(means3D), _p(pre["radii"]), _p(shs), _p(pre["clamped"]),
+          _p(scales), _p(rotations), R(scale_modifier), _p(cov_in),
+          int(cov3D_precomp is not None), int(colors_precomp is not None), _p(view), _p(proj),
+          _p(campos), W, H, R(tanfovx), R(tanfovy), _p(gblend["dL_dmean2D"]),
+          _p(gblend["dL_dconic"]), _p(gblend["dL_dcolor"]), _p(out["dL_dmeans3D"]),
+          _p(out["dL_dcov3D"]), _p(out["dL_dsh"]), _p(out["dL_dscales"]), _p(out["dL_drots"]),
+          rg[0], rg[1])
+
+    _run_ranges(run, _ranges(P, threads))
+    return out
+
+
+def rasterize(means3D, opacities, viewmatrix, projmatrix, campos, bg, W, H, tanfovx, tanfovy,
+              sh_degree=0, shs=None, colors_precomp=None, scales=None, rotations=None,
+              cov3D_precomp=None, scale_modifier=1.0, dL_dpix=None, dtype=np.float32,
+              margin=1e-4, threads=1):
+    """Whole path. With dL_dpix, also runs the reverse pass and returns the gradients the
+    reference's autograd function hands back (same order/meaning as SURVEY.md §8a a5)."""
+    pre = preprocess(means3D, scales, rotations, opacities, shs, viewmatrix, projmatrix, campos,
+                     W, H, tanfovx, tanfovy, sh_degree, scale_modifier, cov3D_precomp,
+                     colors_precomp, dtype, threads)
+    binned = bin_instances(pre, W, H, dtype)
+    fwd = blend_forward(pre, binned, bg, W, H, dtype, margin, threads)
+    res = dict(pre=pre, binned=binned, fwd=fwd, color=fwd["color"], radii=pre["radii"])
+    if dL_dpix is not None:
+        gb = blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype, threads)
+        gp = preprocess_backward(means3D, scales, rotations, shs, viewmatrix, projmatrix, campos,
+                                 W, H, tanfovx, tanfovy, sh_degree, pre, gb, scale_modifier,
+                                 cov3D_precomp, colors_precomp, dtype, threads)
+        P = pre["radii"].shape[0]
+        g2 = np.zeros((P, 3), dtype)
+        g2[:, :2] = gb["dL_dmean2D"]
+        res["grads"] = dict(
+            means3D=gp["dL_dmeans3D"], means2D=g2, shs=gp["dL_dsh"],
+            colors_precomp=gb["dL_dcolor"] if colors_precomp is not None else None,
+            opacities=gb["dL_dopacity"].reshape(P, 1), scales=gp["dL_dscales"],
+            rotations=gp["dL_drots"],
+            cov3D_precomp=gp["dL_dcov3D"] if cov3D_precomp is not None else None,
+        )
+        res["gblend"] = gb
+        res["gpre"] = gp
+    return res
