@@ -1,0 +1,151 @@
+/*
+ * gsrast_b200.h — C ABI of the B200-native differentiable Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for the ONE hot path of ChikaYan/mvs_gaussian_splatting:
+ * the rasterizer that /root/reference/gaussian_renderer/__init__.py:15 imports
+ * (`from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer`),
+ * constructs at :42-57 and calls at :257-265.  In the reference that module is a pybind11
+ * extension `_C` taking torch::Tensor (un-vendored submodule, .gitmodules:4-6); its three
+ * entry points `_C.rasterize_gaussians`, `_C.rasterize_gaussians_backward`, `_C.mark_visible`
+ * are what the functions below replace.  Plain `extern "C"`: raw DEVICE pointers, explicit
+ * sizes, an explicit cudaStream_t (passed as void*), an integer status return, no exceptions,
+ * no global state, no torch types.
+ *
+ * Ownership: the caller owns every byte.  The library never allocates or frees device memory;
+ * the three workspaces (geometry / binning / image — the reference's geomBuffer /
+ * binningBuffer / imgBuffer) are sized with gsr_workspace_bytes() and must stay alive, untouched,
+ * from a forward call until the matching backward call has been enqueued.
+ *
+ * Conventions (same as the reference call site):
+ *   means3D [P,3] f32 | shs [P,M,3] f32 (coefficient-major, RGB innermost) | colors_precomp [P,3]
+ *   opacities [P] f32 | scales [P,3] | rotations [P,4] (w,x,y,z; used as given) | cov3D_precomp [P,6]
+ *   viewmatrix / projmatrix: 16 f32, the reference's TRANSPOSED torch matrices read flat
+ *   (scene/cameras.py:54-56), i.e. column-major maths matrices | campos [3] | bg [3]
+ *   out_color [3,H,W] planar f32 | radii [P] i32 (0 = culled)
+ * Exactly one of (shs, colors_precomp) and one of ((scales,rotations), cov3D_precomp) is non-NULL.
+ * All pointers must be 16-byte aligned and dense.
+ */
+#ifndef GSRAST_B200_H_
+#define GSRAST_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_ABI_VERSION 1
+
+enum gsr_status {
+    GSR_OK = 0,
+    GSR_ERR_INVALID_ARGUMENT = 1, /* NULL / inconsistent pointers, negative sizes, bad degree */
+    GSR_ERR_CUDA = 2,             /* a CUDA runtime call or (debug mode) a kernel failed     */
+    GSR_ERR_WORKSPACE = 3,        /* workspace pointer NULL or misaligned                    */
+    GSR_ERR_UNSUPPORTED = 4       /* e.g. more than 2^16 tiles per axis, M > 16 coefficients */
+};
+
+/* Host-visible result block of a forward call.  `h_info` arguments point at PINNED host memory
+ * (or NULL); the library enqueues an async D2H copy of the device copy into it, so the values
+ * are valid once the stream has reached that point (no host sync inside the library). */
+typedef struct gsr_forward_info {
+    int32_t num_rendered;  /* R = sum(tiles_touched): tile instances the view needs            */
+    int32_t overflow;      /* 1 if R > instance_capacity: nothing was binned/blended; re-run
+                              gsr_forward_render with a larger binning workspace               */
+    int32_t num_visible;   /* Gaussians with radii > 0                                         */
+    int32_t reserved;
+} gsr_forward_info;
+
+/* Byte offsets of the arrays inside the three workspaces (for tests, debugging and tools; the
+ * layout is otherwise private).  Obtained from gsr_workspace_layout(). */
+typedef struct gsr_layout {
+    /* geometry workspace, per Gaussian */
+    size_t g_depths;        /* f32[P]   view-space z                                           */
+    size_t g_means2D;       /* f32[P,2] pixel centre                                           */
+    size_t g_conic_opacity; /* f32[P,4] conic A,B,C + opacity                                  */
+    size_t g_rgb;           /* f32[P,4] r,g,b + clamped bits (as u32 in .w, bit c = channel c) */
+    size_t g_tiles_touched; /* u32[P]                                                          */
+    size_t g_point_offsets; /* u32[P]   inclusive prefix sum of tiles_touched                  */
+    size_t g_info;          /* gsr_forward_info (device copy)                                  */
+    size_t g_grad_accum;    /* f32[P,12] backward blend accumulators                           */
+    size_t g_scan_tmp;      /* u32[...] scan block sums                                        */
+    size_t geom_bytes;
+    /* binning workspace, per tile instance (capacity entries each) */
+    size_t b_keys_unsorted; /* u64[C]  (tile << 32) | depth bits                               */
+    size_t b_vals_unsorted; /* u32[C]  Gaussian index                                          */
+    size_t b_keys;          /* u64[C]  sorted                                                  */
+    size_t b_point_list;    /* u32[C]  sorted                                                  */
+    size_t b_keys_alt;      /* u64[C]  radix-sort ping-pong buffer                             */
+    size_t b_vals_alt;      /* u32[C]                                                          */
+    size_t b_sort_tmp;      /* radix-sort histograms                                           */
+    size_t binning_bytes;
+    /* image workspace */
+    size_t i_ranges;        /* u32[tiles,2] [start,end) into point_list                        */
+    size_t i_final_T;       /* f32[H*W]                                                        */
+    size_t i_n_contrib;     /* u32[H*W] 1-based list position of the last blended entry        */
+    size_t image_bytes;
+} gsr_layout;
+
+int gsr_abi_version(void);
+
+/* Replaces: the exception text the reference's CHECK_CUDA macro raises. Never NULL. */
+const char* gsr_status_string(int status);
+/* cudaGetErrorString of the last CUDA error this THREAD saw inside the library ("" if none). */
+const char* gsr_last_cuda_error(void);
+
+/* Replaces: the three resize lambdas (`resizeFunctional`) the reference's glue hands to
+ * CudaRasterizer::Rasterizer::forward — here the caller sizes and owns the buffers up front. */
+int gsr_workspace_bytes(int P, int width, int height, int64_t instance_capacity,
+                        size_t* geom_bytes, size_t* binning_bytes, size_t* image_bytes);
+int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out);
+
+/* Forward, stage 1 (replaces the first half of `_C.rasterize_gaussians`: preprocess + prefix sum).
+ * Writes radii[P] and the geometry workspace; enqueues a copy of gsr_forward_info (num_rendered,
+ * num_visible) into h_info if non-NULL.  D = active SH degree 0..3, M = coefficients per channel
+ * in `shs` (>= (D+1)^2, <= 16). */
+int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D,
+                         const float* shs, const float* colors_precomp, const float* opacities,
+                         const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, const float* viewmatrix,
+                         const float* projmatrix, const float* campos, float tanfovx,
+                         float tanfovy, int prefiltered, int32_t* radii, void* geom_ws,
+                         gsr_forward_info* h_info, void* stream, int debug);
+
+/* Forward, stage 2 (replaces the second half: duplicateWithKeys, radix sort, identifyTileRanges,
+ * render).  Never syncs the host: R is read on the device; if R > instance_capacity the overflow
+ * flag is raised, nothing is binned (out_color then holds the background only), and the caller
+ * re-runs this stage with a larger binning workspace (the geometry workspace stays valid). */
+int gsr_forward_render(int P, int width, int height, const float* bg, const int32_t* radii,
+                       void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws,
+                       float* out_color, gsr_forward_info* h_info, void* stream, int debug);
+
+/* Backward (replaces `_C.rasterize_gaussians_backward`).  Needs the inputs and the three
+ * workspaces of the matching forward.  EVERY output array is fully written by the library
+ * (zeros where the reference would leave its zero-initialised tensors untouched); the caller
+ * passes uninitialised memory.  Outputs that do not apply may be NULL:
+ *   dL_dsh (colors_precomp path), dL_dscales/dL_drots (cov3D_precomp path).
+ * dL_dmeans2D is [P,3] (z = 0) in the reference's NDC-scaled convention
+ * (scene/gaussian_model.py:775-777 reads [:, :2]).  dL_dcolors [P,3], dL_dopacity [P],
+ * dL_dmeans3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3], dL_dscales [P,3], dL_drots [P,4]. */
+int gsr_backward(int P, int D, int M, int width, int height, const float* bg,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* scales, float scale_modifier, const float* rotations,
+                 const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                 const float* campos, float tanfovx, float tanfovy, const int32_t* radii,
+                 void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws,
+                 const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                 float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots, void* stream,
+                 int debug);
+
+/* Replaces `_C.mark_visible`: present[i] = 1 iff Gaussian i passes the near-plane test. */
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* Number of kernel launches the library has issued in this process (all threads); bench.py
+ * reports the difference across its timed region as `gpu_launches`. */
+int64_t gsr_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSRAST_B200_H_ */

@@ -1,0 +1,258 @@
+// gsr_api.cu — the C ABI declared in include/gsrast_b200.h: argument validation, workspace layout,
+// stage sequencing.  No device memory is allocated here and the host never waits on the device
+// (except in debug mode, where every launch is followed by a stream synchronise, as the
+// reference's `debug` flag does).
+#include <atomic>
+#include <cstring>
+
+#include "gsr_internal.cuh"
+
+namespace gsr {
+
+static std::atomic<int64_t> g_launches{0};
+static thread_local cudaError_t t_last_error = cudaSuccess;
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+int cuda_fail(cudaError_t e) {
+    t_last_error = e;
+    cudaGetLastError();  // clear the sticky-less error state
+    return GSR_ERR_CUDA;
+}
+
+void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
+    std::memset(L, 0, sizeof(*L));
+    const size_t p = (size_t)(P > 0 ? P : 1);
+    const size_t c = (size_t)(cap > 0 ? cap : 1);
+    const Grid g = make_grid(W, H);
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
+    L->g_depths = take(4 * p);
+    L->g_means2D = take(8 * p);
+    L->g_conic_opacity = take(16 * p);
+    L->g_rgb = take(16 * p);
+    L->g_tiles_touched = take(4 * p);
+    L->g_point_offsets = take(4 * p);
+    L->g_info = take(sizeof(gsr_forward_info));
+    L->g_grad_accum = take(48 * p);
+    L->g_scan_tmp = take(4 * scan_tmp_entries(p));
+    L->geom_bytes = o;
+    o = 0;
+    L->b_keys_unsorted = take(8 * c);
+    L->b_vals_unsorted = take(4 * c);
+    L->b_keys = take(8 * c);
+    L->b_point_list = take(4 * c);
+    L->b_keys_alt = take(8 * c);
+    L->b_vals_alt = take(4 * c);
+    L->b_sort_tmp = take(4 * sort_tmp_entries(c));
+    L->binning_bytes = o;
+    o = 0;
+    L->i_ranges = take(8 * (size_t)g.tiles);
+    L->i_final_T = take(4 * (size_t)W * H);
+    L->i_n_contrib = take(4 * (size_t)W * H);
+    L->image_bytes = o;
+}
+
+template <typename T>
+static T* at(void* ws, size_t off) { return reinterpret_cast<T*>(static_cast<char*>(ws) + off); }
+
+GeomView geom_view(void* ws, const gsr_layout& L) {
+    GeomView v;
+    v.depths = at<float>(ws, L.g_depths);
+    v.means2D = at<float2>(ws, L.g_means2D);
+    v.conic_opacity = at<float4>(ws, L.g_conic_opacity);
+    v.rgb = at<float4>(ws, L.g_rgb);
+    v.tiles_touched = at<uint32_t>(ws, L.g_tiles_touched);
+    v.point_offsets = at<uint32_t>(ws, L.g_point_offsets);
+    v.info = at<gsr_forward_info>(ws, L.g_info);
+    v.grad_accum = at<float>(ws, L.g_grad_accum);
+    v.scan_tmp = at<uint32_t>(ws, L.g_scan_tmp);
+    return v;
+}
+BinView bin_view(void* ws, const gsr_layout& L) {
+    BinView v;
+    v.keys_unsorted = at<uint64_t>(ws, L.b_keys_unsorted);
+    v.vals_unsorted = at<uint32_t>(ws, L.b_vals_unsorted);
+    v.keys = at<uint64_t>(ws, L.b_keys);
+    v.point_list = at<uint32_t>(ws, L.b_point_list);
+    v.keys_alt = at<uint64_t>(ws, L.b_keys_alt);
+    v.vals_alt = at<uint32_t>(ws, L.b_vals_alt);
+    v.sort_tmp = at<uint32_t>(ws, L.b_sort_tmp);
+    return v;
+}
+ImageView image_view(void* ws, const gsr_layout& L) {
+    ImageView v;
+    v.ranges = at<uint2>(ws, L.i_ranges);
+    v.final_T = at<float>(ws, L.i_final_T);
+    v.n_contrib = at<uint32_t>(ws, L.i_n_contrib);
+    return v;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int check_dims(int P, int W, int H, int64_t cap) {
+    if (P < 0 || W <= 0 || H <= 0 || cap < 0) return GSR_ERR_INVALID_ARGUMENT;
+    if (cap > 0xFFFFFFFFll) return GSR_ERR_UNSUPPORTED;
+    const Grid g = make_grid(W, H);
+    if ((int64_t)g.gx * g.gy > (1ll << 30)) return GSR_ERR_UNSUPPORTED;
+    return GSR_OK;
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+int gsr_abi_version(void) { return GSR_ABI_VERSION; }
+
+const char* gsr_status_string(int status) {
+    switch (status) {
+        case GSR_OK: return "ok";
+        case GSR_ERR_INVALID_ARGUMENT: return "invalid argument";
+        case GSR_ERR_CUDA: return "CUDA error";
+        case GSR_ERR_WORKSPACE: return "workspace pointer null or misaligned";
+        case GSR_ERR_UNSUPPORTED: return "unsupported size or configuration";
+        default: return "unknown status";
+    }
+}
+
+const char* gsr_last_cuda_error(void) {
+    return t_last_error == cudaSuccess ? "" : cudaGetErrorString(t_last_error);
+}
+
+int64_t gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out) {
+    if (!out) return GSR_ERR_INVALID_ARGUMENT;
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    compute_layout(P, width, height, instance_capacity, out);
+    return GSR_OK;
+}
+
+int gsr_workspace_bytes(int P, int width, int height, int64_t instance_capacity, size_t* geom_bytes,
+                        size_t* binning_bytes, size_t* image_bytes) {
+    gsr_layout L;
+    int st = gsr_workspace_layout(P, width, height, instance_capacity, &L);
+    if (st != GSR_OK) return st;
+    if (geom_bytes) *geom_bytes = L.geom_bytes;
+    if (binning_bytes) *binning_bytes = L.binning_bytes;
+    if (image_bytes) *image_bytes = L.image_bytes;
+    return GSR_OK;
+}
+
+int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D, const float* shs,
+                         const float* colors_precomp, const float* opacities, const float* scales,
+                         float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
+                         float tanfovy, int prefiltered, int32_t* radii, void* geom_ws, gsr_forward_info* h_info,
+                         void* stream, int debug) {
+    (void)prefiltered;  // accepted for API compatibility; the cull is always evaluated
+    int st = check_dims(P, width, height, 0);
+    if (st != GSR_OK) return st;
+    if (!geom_ws || !aligned16(geom_ws)) return GSR_ERR_WORKSPACE;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gsr_layout L;
+    compute_layout(P, width, height, 0, &L);
+    GeomView gv = geom_view(geom_ws, L);
+    GSR_CUDA(cudaMemsetAsync(gv.info, 0, sizeof(gsr_forward_info), s));
+    if (P > 0) {
+        if (!means3D || !opacities || !radii || !viewmatrix || !projmatrix || !campos) return GSR_ERR_INVALID_ARGUMENT;
+        if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+        const bool has_sr = scales != nullptr && rotations != nullptr;
+        if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+        if (!has_sr && (scales || rotations)) return GSR_ERR_INVALID_ARGUMENT;
+        if (shs) {
+            if (D < 0 || D > 3 || M < (D + 1) * (D + 1)) return GSR_ERR_INVALID_ARGUMENT;
+            if (M > 16) return GSR_ERR_UNSUPPORTED;
+        }
+        if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+            !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
+            return GSR_ERR_INVALID_ARGUMENT;
+        const Grid g = make_grid(width, height);
+        st = launch_preprocess(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
+                               rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii,
+                               gv, s, debug);
+        if (st != GSR_OK) return st;
+        st = launch_inclusive_scan(gv.tiles_touched, gv.point_offsets, (size_t)P, gv.scan_tmp, s, debug);
+        if (st != GSR_OK) return st;
+        GSR_CUDA(cudaMemcpyAsync(&gv.info->num_rendered, gv.point_offsets + (P - 1), sizeof(int32_t),
+                                 cudaMemcpyDeviceToDevice, s));
+    }
+    if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));
+    return GSR_OK;
+}
+
+int gsr_forward_render(int P, int width, int height, const float* bg, const int32_t* radii, void* geom_ws,
+                       void* binning_ws, int64_t instance_capacity, void* image_ws, float* out_color,
+                       gsr_forward_info* h_info, void* stream, int debug) {
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    if (!geom_ws || !image_ws || !aligned16(geom_ws) || !aligned16(image_ws)) return GSR_ERR_WORKSPACE;
+    if (instance_capacity > 0 && (!binning_ws || !aligned16(binning_ws))) return GSR_ERR_WORKSPACE;
+    if (!bg || !out_color || (P > 0 && !radii)) return GSR_ERR_INVALID_ARGUMENT;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gsr_layout L;
+    compute_layout(P, width, height, instance_capacity, &L);
+    GeomView gv = geom_view(geom_ws, L);
+    BinView bv = bin_view(binning_ws, L);
+    ImageView iv = image_view(image_ws, L);
+    const Grid g = make_grid(width, height);
+    if (P > 0) {
+        st = launch_binning(P, g, radii, gv, bv, instance_capacity, iv, s, debug);
+        if (st != GSR_OK) return st;
+    } else {
+        GSR_CUDA(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)g.tiles, s));
+    }
+    st = launch_blend_forward(g, bg, gv, bv, iv, out_color, s, debug);
+    if (st != GSR_OK) return st;
+    if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));
+    return GSR_OK;
+}
+
+int gsr_backward(int P, int D, int M, int width, int height, const float* bg, const float* means3D,
+                 const float* shs, const float* colors_precomp, const float* scales, float scale_modifier,
+                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                 const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int32_t* radii,
+                 void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws, const float* dL_dpix,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
+                 float* dL_dscales, float* dL_drots, void* stream, int debug) {
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    if (P == 0) return GSR_OK;
+    if (!geom_ws || !image_ws || !binning_ws || !aligned16(geom_ws) || !aligned16(image_ws) || !aligned16(binning_ws))
+        return GSR_ERR_WORKSPACE;
+    if (!bg || !means3D || !viewmatrix || !projmatrix || !campos || !radii || !dL_dpix || !dL_dmeans2D ||
+        !dL_dopacity || !dL_dmeans3D)
+        return GSR_ERR_INVALID_ARGUMENT;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
+    if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
+    if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gsr_layout L;
+    compute_layout(P, width, height, instance_capacity, &L);
+    GeomView gv = geom_view(geom_ws, L);
+    BinView bv = bin_view(binning_ws, L);
+    ImageView iv = image_view(image_ws, L);
+    const Grid g = make_grid(width, height);
+    st = launch_blend_backward(P, g, bg, gv, bv, iv, dL_dpix, s, debug);
+    if (st != GSR_OK) return st;
+    return launch_preprocess_backward(P, D, M, g, means3D, shs, colors_precomp != nullptr, scales, scale_modifier,
+                                      rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
+                                      radii, gv, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
+                                      dL_dsh, dL_dscales, dL_drots, s, debug);
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream) {
+    (void)projmatrix;  // the reference's test uses only the view-space depth
+    if (P < 0) return GSR_ERR_INVALID_ARGUMENT;
+    if (P == 0) return GSR_OK;
+    if (!means3D || !viewmatrix || !present) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_mark_visible(P, means3D, viewmatrix, present, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,164 @@
+// gsr_internal.cuh — shared declarations of the sm_100a rasterizer library (private).
+//
+// Numerics policy.  Everything that decides an INTEGER result (radii, tile rects, depth key bits,
+// cull decisions) is written with explicit round-to-nearest intrinsics (__fmul_rn / __fadd_rn /
+// __fmaf_rn / __fdiv_rn / __fsqrt_rn), which nvcc never contracts or reassociates, in exactly the
+// operation order oracle/gs_oracle.c documents.  The result is therefore independent of -fmad and
+// bit-identical to the oracle's -ffp-contract=off build.  Tolerance-level arithmetic (blending,
+// all gradients) is written naturally and left to the compiler.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gsrast_b200.h"
+
+namespace gsr {
+
+constexpr int kTile = 16;          // pixels per tile edge (16x16, as the reference bins)
+constexpr int kTilePixels = 256;
+constexpr float kNearPlane = 0.2f; // view-space z cull threshold
+
+// ---- launch accounting + error plumbing -------------------------------------------------
+void count_launch(int n = 1);
+int cuda_fail(cudaError_t e);  // records e for gsr_last_cuda_error(), returns GSR_ERR_CUDA
+
+#define GSR_CUDA(expr)                                    \
+    do {                                                  \
+        cudaError_t _e = (expr);                          \
+        if (_e != cudaSuccess) return ::gsr::cuda_fail(_e); \
+    } while (0)
+
+// After a launch: always catch launch-configuration errors; in debug mode also synchronise so a
+// faulting kernel is reported by the call that launched it (the reference's `debug` behaviour).
+#define GSR_AFTER_LAUNCH(stream, debug)                                  \
+    do {                                                                 \
+        ::gsr::count_launch();                                           \
+        cudaError_t _e = cudaGetLastError();                             \
+        if (_e == cudaSuccess && (debug)) _e = cudaStreamSynchronize(stream); \
+        if (_e != cudaSuccess) return ::gsr::cuda_fail(_e);              \
+    } while (0)
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Grid {
+    int W, H, gx, gy, tiles;
+};
+inline Grid make_grid(int W, int H) {
+    Grid g;
+    g.W = W; g.H = H;
+    g.gx = (W + kTile - 1) / kTile;
+    g.gy = (H + kTile - 1) / kTile;
+    g.tiles = g.gx * g.gy;
+    return g;
+}
+
+// Typed views of the three workspaces.
+struct GeomView {
+    float* depths;
+    float2* means2D;
+    float4* conic_opacity;
+    float4* rgb;  // .w carries the clamped bits
+    uint32_t* tiles_touched;
+    uint32_t* point_offsets;
+    gsr_forward_info* info;
+    float* grad_accum;  // [P,12]
+    uint32_t* scan_tmp;
+};
+struct BinView {
+    uint64_t* keys_unsorted;
+    uint32_t* vals_unsorted;
+    uint64_t* keys;
+    uint32_t* point_list;
+    uint64_t* keys_alt;   // radix-sort ping-pong partner of (keys, point_list)
+    uint32_t* vals_alt;
+    uint32_t* sort_tmp;
+};
+struct ImageView {
+    uint2* ranges;
+    float* final_T;
+    uint32_t* n_contrib;
+};
+void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L);
+GeomView geom_view(void* ws, const gsr_layout& L);
+BinView bin_view(void* ws, const gsr_layout& L);
+ImageView image_view(void* ws, const gsr_layout& L);
+
+// Number of u32 entries the generic scan needs as scratch for n elements.
+size_t scan_tmp_entries(size_t n);
+// Number of u32 entries the radix sort needs as scratch for `cap` elements.
+size_t sort_tmp_entries(size_t cap);
+
+// ---- stage launchers (each returns a gsr_status) ------------------------------------------
+int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                      const float* colors_precomp, const float* opacities, const float* scales,
+                      float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                      const float* view, const float* proj, const float* campos, float tanfovx,
+                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug);
+
+// Inclusive prefix sum of u32 (n elements); optionally stores the grand total to *total.
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp,
+                          cudaStream_t s, int debug);
+
+int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinView bv,
+                   int64_t cap, ImageView iv, cudaStream_t s, int debug);
+
+int launch_blend_forward(const Grid& g, const float* bg, GeomView gv, BinView bv, ImageView iv,
+                         float* out_color, cudaStream_t s, int debug);
+
+int launch_blend_backward(int P, const Grid& g, const float* bg, GeomView gv, BinView bv,
+                          ImageView iv, const float* dL_dpix, cudaStream_t s, int debug);
+
+int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* means3D,
+                               const float* shs, int colors_precomp, const float* scales,
+                               float scale_modifier, const float* rotations,
+                               const float* cov3D_precomp, const float* view, const float* proj,
+                               const float* campos, float tanfovx, float tanfovy,
+                               const int32_t* radii, GeomView gv, float* dL_dmeans2D,
+                               float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+                               float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots,
+                               cudaStream_t s, int debug);
+
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
+                        cudaStream_t s);
+
+// ---- device helpers shared by several translation units ------------------------------------
+#ifdef __CUDACC__
+
+// p0 + p1 + p2 with the oracle's contraction policy: fma(a2,b2, fma(a0,b0, rn(a1*b1))).
+__device__ __forceinline__ float dot3_rn(float a0, float b0, float a1, float b1, float a2, float b2) {
+    return __fmaf_rn(a2, b2, __fmaf_rn(a0, b0, __fmul_rn(a1, b1)));
+}
+__device__ __forceinline__ float dot2_rn(float a0, float b0, float a1, float b1) {
+    return __fmaf_rn(a0, b0, __fmul_rn(a1, b1));
+}
+// Column-major 4x4 (flat 16 floats) times point; row r = m[r], m[4+r], m[8+r], m[12+r].
+__device__ __forceinline__ float xform_row_rn(const float* m, int r, float x, float y, float z) {
+    return __fadd_rn(dot3_rn(m[r], x, m[4 + r], y, m[8 + r], z), m[12 + r]);
+}
+
+// Tile rectangle [min,max) of a splat, clamped to the grid (bit-exact with the oracle).
+__device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx, int gy,
+                                          int& x0, int& y0, int& x1, int& y1) {
+    const float rf = (float)radius;
+    x0 = min(gx, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(px, -rf), 16.0f))));
+    y0 = min(gy, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(py, -rf), 16.0f))));
+    x1 = min(gx, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(px, rf), 16.0f), -1.0f), 16.0f))));
+    y1 = min(gy, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(py, rf), 16.0f), -1.0f), 16.0f))));
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__device__ __forceinline__ unsigned lane_id() { return threadIdx.x & 31u; }
+
+#endif  // __CUDACC__
+
+}  // namespace gsr

@@ -1,0 +1,320 @@
+// gsr_preprocess.cu — forward per-Gaussian stage (the reference's `preprocessCUDA`, SURVEY §2.1 K1,
+// §8a rows a8-a12) and markVisible (K11), written for sm_100a.
+//
+// One thread per Gaussian, 128-thread CTAs.  HBM-bound: 44 B/Gaussian always + the active SH
+// prefix (up to 192 B) only for Gaussians that survive the cull.  means/scales are fetched as
+// coalesced float4 through shared memory; SH rows are fetched warp-cooperatively as float4 (lane j
+// of a warp fetches 16-byte piece j of the warp's surviving rows) into an odd-stride shared tile,
+// so every 32-byte sector requested from HBM is fully used and culled rows cost nothing.
+//
+// All arithmetic that decides radii / tile rects / depth bits follows oracle/gs_oracle.c
+// operation for operation with non-contractable _rn intrinsics (see gsr_internal.cuh).
+#include "gsr_internal.cuh"
+
+namespace gsr {
+
+namespace {
+
+constexpr int kPreThreads = 128;
+constexpr int kPreWarps = kPreThreads / 32;
+constexpr int kShStride = 49;  // 48 floats (16 coeffs x RGB) + 1 pad -> conflict-free column reads
+
+__constant__ float c_SH_C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                 -1.0925484305920792f, 0.5462742152960396f};
+__constant__ float c_SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f,  -0.4570457994644658f,
+                                 0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
+                                 -0.5900435899266435f};
+
+struct PreParams {
+    int P, D, M;
+    int W, H, gx, gy;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* opacities;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* view;
+    const float* proj;
+    const float* campos;
+    float tanfovx, tanfovy, focal_x, focal_y;
+    int32_t* radii;
+    GeomView gv;
+};
+
+// Stage a [n,3] f32 array slice for this CTA into shared memory with float4 loads.
+__device__ __forceinline__ void stage_xyz(const float* __restrict__ src, int P, int base, float* s) {
+    const int nfloat_total = 3 * P;
+    const int f0 = 3 * base;                                 // multiple of 384 floats -> 16B aligned
+    const int nfl = min(3 * kPreThreads, nfloat_total - f0); // floats this CTA needs
+    const int nvec = nfl >> 2;
+    const float4* src4 = reinterpret_cast<const float4*>(src + f0);
+    for (int j = threadIdx.x; j < nvec; j += kPreThreads) {
+        float4 v = __ldg(src4 + j);
+        s[4 * j + 0] = v.x; s[4 * j + 1] = v.y; s[4 * j + 2] = v.z; s[4 * j + 3] = v.w;
+    }
+    for (int j = 4 * nvec + threadIdx.x; j < nfl; j += kPreThreads) s[j] = __ldg(src + f0 + j);
+}
+
+// Sigma = R diag(s)^2 R^T (6 upper-tri floats), quaternion used as given.
+__device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float sz, float mod, float4 q,
+                                                     float* c6) {
+    const float s0 = __fmul_rn(mod, sx), s1 = __fmul_rn(mod, sy), s2 = __fmul_rn(mod, sz);
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    const float R00 = __fadd_rn(1.0f, -__fmul_rn(2.0f, dot2_rn(y, y, z, z)));
+    const float R01 = __fmul_rn(2.0f, __fmaf_rn(x, y, -__fmul_rn(r, z)));
+    const float R02 = __fmul_rn(2.0f, dot2_rn(x, z, r, y));
+    const float R10 = __fmul_rn(2.0f, dot2_rn(x, y, r, z));
+    const float R11 = __fadd_rn(1.0f, -__fmul_rn(2.0f, dot2_rn(x, x, z, z)));
+    const float R12 = __fmul_rn(2.0f, __fmaf_rn(y, z, -__fmul_rn(r, x)));
+    const float R20 = __fmul_rn(2.0f, __fmaf_rn(x, z, -__fmul_rn(r, y)));
+    const float R21 = __fmul_rn(2.0f, dot2_rn(y, z, r, x));
+    const float R22 = __fadd_rn(1.0f, -__fmul_rn(2.0f, dot2_rn(x, x, y, y)));
+    const float M00 = __fmul_rn(s0, R00), M01 = __fmul_rn(s0, R10), M02 = __fmul_rn(s0, R20);
+    const float M10 = __fmul_rn(s1, R01), M11 = __fmul_rn(s1, R11), M12 = __fmul_rn(s1, R21);
+    const float M20 = __fmul_rn(s2, R02), M21 = __fmul_rn(s2, R12), M22 = __fmul_rn(s2, R22);
+    c6[0] = dot3_rn(M00, M00, M10, M10, M20, M20);
+    c6[1] = dot3_rn(M00, M01, M10, M11, M20, M21);
+    c6[2] = dot3_rn(M00, M02, M10, M12, M20, M22);
+    c6[3] = dot3_rn(M01, M01, M11, M11, M21, M21);
+    c6[4] = dot3_rn(M01, M02, M11, M12, M21, M22);
+    c6[5] = dot3_rn(M02, M02, M12, M12, M22, M22);
+}
+
+// EWA projection of Sigma to the screen: (a,b,c) incl. the +0.3 dilation.  t = view-space mean.
+__device__ __forceinline__ void cov2d_project(float tx, float ty, float tz, float fx, float fy,
+                                              float tanx, float tany, const float* c6,
+                                              const float* __restrict__ v, float& a, float& b, float& c) {
+    const float limx = __fmul_rn(1.3f, tanx), limy = __fmul_rn(1.3f, tany);
+    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
+    tx = __fmul_rn(fminf(limx, fmaxf(-limx, txtz)), tz);
+    ty = __fmul_rn(fminf(limy, fmaxf(-limy, tytz)), tz);
+    const float j00 = __fdiv_rn(fx, tz);
+    const float j11 = __fdiv_rn(fy, tz);
+    const float tz2 = __fmul_rn(tz, tz);
+    const float j02 = __fdiv_rn(-__fmul_rn(fx, tx), tz2);
+    const float j12 = __fdiv_rn(-__fmul_rn(fy, ty), tz2);
+    float M0[3], M1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        M0[k] = __fmaf_rn(v[4 * k + 2], j02, __fmul_rn(v[4 * k + 0], j00));
+        M1[k] = __fmaf_rn(v[4 * k + 2], j12, __fmul_rn(v[4 * k + 1], j11));
+    }
+    const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+    float A0[3], A1[3];
+#pragma unroll
+    for (int cc = 0; cc < 3; ++cc) {
+        A0[cc] = dot3_rn(M0[0], S[0][cc], M0[1], S[1][cc], M0[2], S[2][cc]);
+        A1[cc] = dot3_rn(M1[0], S[0][cc], M1[1], S[1][cc], M1[2], S[2][cc]);
+    }
+    a = __fadd_rn(dot3_rn(A0[0], M0[0], A0[1], M0[1], A0[2], M0[2]), 0.3f);
+    b = dot3_rn(A1[0], M0[0], A1[1], M0[1], A1[2], M0[2]);
+    c = __fadd_rn(dot3_rn(A1[0], M1[0], A1[1], M1[1], A1[2], M1[2]), 0.3f);
+}
+
+// Degree 0..3 real SH -> RGB (+0.5, clamp >= 0, clamped bits).  sh = this Gaussian's row in the
+// shared tile: sh[3*k + c].  Same evaluation order as the oracle's sh_to_rgb.
+__device__ __forceinline__ void sh_to_rgb(int deg, float dx, float dy, float dz, const float* sh,
+                                          float* rgb, uint32_t& clamped) {
+    const float len = __fsqrt_rn(dot3_rn(dx, dx, dy, dy, dz, dz));
+    const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+    const float SH_C0 = 0.28209479177387814f, SH_C1 = 0.4886025119029199f;
+    clamped = 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#define SH(k) sh[3 * (k) + c]
+        float res = __fmul_rn(SH_C0, SH(0));
+        if (deg > 0) {
+            res = __fmaf_rn(-__fmul_rn(SH_C1, y), SH(1), res);
+            res = __fmaf_rn(__fmul_rn(SH_C1, z), SH(2), res);
+            res = __fmaf_rn(-__fmul_rn(SH_C1, x), SH(3), res);
+            if (deg > 1) {
+                const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+                const float xy = __fmul_rn(x, y), yz = __fmul_rn(y, z), xz = __fmul_rn(x, z);
+                res = __fmaf_rn(__fmul_rn(c_SH_C2[0], xy), SH(4), res);
+                res = __fmaf_rn(__fmul_rn(c_SH_C2[1], yz), SH(5), res);
+                res = __fmaf_rn(__fmul_rn(c_SH_C2[2], __fadd_rn(__fmaf_rn(2.0f, zz, -xx), -yy)), SH(6), res);
+                res = __fmaf_rn(__fmul_rn(c_SH_C2[3], xz), SH(7), res);
+                res = __fmaf_rn(__fmul_rn(c_SH_C2[4], __fadd_rn(xx, -yy)), SH(8), res);
+                if (deg > 2) {
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[0], y), __fmaf_rn(3.0f, xx, -yy)), SH(9), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[1], xy), z), SH(10), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[2], y), __fadd_rn(__fmaf_rn(4.0f, zz, -xx), -yy)), SH(11), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[3], z),
+                                              __fmaf_rn(-3.0f, yy, __fmaf_rn(2.0f, zz, -__fmul_rn(3.0f, xx)))),
+                                    SH(12), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[4], x), __fadd_rn(__fmaf_rn(4.0f, zz, -xx), -yy)), SH(13), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[5], z), __fadd_rn(xx, -yy)), SH(14), res);
+                    res = __fmaf_rn(__fmul_rn(__fmul_rn(c_SH_C3[6], x), __fmaf_rn(-3.0f, yy, xx)), SH(15), res);
+                }
+            }
+        }
+#undef SH
+        res = __fadd_rn(res, 0.5f);
+        if (res < 0.0f) clamped |= (1u << c);
+        rgb[c] = fmaxf(res, 0.0f);
+    }
+}
+
+__global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams p) {
+    __shared__ float s_mean[3 * kPreThreads];
+    __shared__ float s_scale[3 * kPreThreads];
+    __shared__ float s_sh[kPreWarps][32 * kShStride];
+    __shared__ float s_cam[35];  // view[16] proj[16] campos[3]
+
+    const int base = blockIdx.x * kPreThreads;
+    const int idx = base + threadIdx.x;
+    const unsigned lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(p.view + threadIdx.x);
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(p.proj + threadIdx.x - 16);
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(p.campos + threadIdx.x - 32);
+    stage_xyz(p.means3D, p.P, base, s_mean);
+    if (p.scales) stage_xyz(p.scales, p.P, base, s_scale);
+    __syncthreads();
+    const float* view = s_cam;
+    const float* proj = s_cam + 16;
+
+    bool alive = idx < p.P;
+    float mx = 0, my = 0, mz = 0, depth = 0, px = 0, py = 0, ca = 0, cb = 0, cc = 0, det_inv = 0;
+    int rad = 0, x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+
+    if (alive) {
+        mx = s_mean[3 * threadIdx.x]; my = s_mean[3 * threadIdx.x + 1]; mz = s_mean[3 * threadIdx.x + 2];
+        const float tx = xform_row_rn(view, 0, mx, my, mz);
+        const float ty = xform_row_rn(view, 1, mx, my, mz);
+        depth = xform_row_rn(view, 2, mx, my, mz);
+        alive = depth > kNearPlane;  // near-plane cull only; NaN fails too
+        if (alive) {
+            const float hx = xform_row_rn(proj, 0, mx, my, mz);
+            const float hy = xform_row_rn(proj, 1, mx, my, mz);
+            const float hw = xform_row_rn(proj, 3, mx, my, mz);
+            const float pw = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
+            const float ndcx = __fmul_rn(hx, pw), ndcy = __fmul_rn(hy, pw);
+            float c6[6];
+            if (p.cov3D_precomp) {
+                const float2* cp = reinterpret_cast<const float2*>(p.cov3D_precomp) + 3 * (size_t)idx;
+                float2 u0 = __ldg(cp), u1 = __ldg(cp + 1), u2 = __ldg(cp + 2);
+                c6[0] = u0.x; c6[1] = u0.y; c6[2] = u1.x; c6[3] = u1.y; c6[4] = u2.x; c6[5] = u2.y;
+            } else {
+                const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                cov3d_from_scale_rot(s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1],
+                                     s_scale[3 * threadIdx.x + 2], p.scale_modifier, q, c6);
+            }
+            cov2d_project(tx, ty, depth, p.focal_x, p.focal_y, p.tanfovx, p.tanfovy, c6, view, ca, cb, cc);
+            const float det = __fmaf_rn(ca, cc, -__fmul_rn(cb, cb));
+            alive = det != 0.0f;
+            if (alive) {
+                det_inv = __fdiv_rn(1.0f, det);
+                const float mid = __fmul_rn(0.5f, __fadd_rn(ca, cc));
+                const float sq = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+                const float lam1 = __fadd_rn(mid, sq), lam2 = __fadd_rn(mid, -sq);
+                rad = __float2int_rz(ceilf(__fmul_rn(3.0f, __fsqrt_rn(fmaxf(lam1, lam2)))));
+                px = __fmul_rn(__fmaf_rn(__fadd_rn(ndcx, 1.0f), (float)p.W, -1.0f), 0.5f);
+                py = __fmul_rn(__fmaf_rn(__fadd_rn(ndcy, 1.0f), (float)p.H, -1.0f), 0.5f);
+                tile_rect(px, py, rad, p.gx, p.gy, x0, y0, x1, y1);
+                alive = (x1 - x0) * (y1 - y0) != 0;
+            }
+        }
+    }
+
+    // ---- colour: SH rows of surviving Gaussians, fetched warp-cooperatively ----
+    const unsigned vis = __ballot_sync(0xffffffffu, alive);
+    float rgb[3] = {0.f, 0.f, 0.f};
+    uint32_t clamped = 0;
+    if (p.colors_precomp) {
+        if (alive) {
+            rgb[0] = __ldg(p.colors_precomp + 3 * (size_t)idx);
+            rgb[1] = __ldg(p.colors_precomp + 3 * (size_t)idx + 1);
+            rgb[2] = __ldg(p.colors_precomp + 3 * (size_t)idx + 2);
+        }
+    } else if (vis) {
+        float* tile = s_sh[warp];
+        const int row = 3 * p.M;                      // floats per Gaussian in global memory
+        const int need = 3 * (p.D + 1) * (p.D + 1);   // floats of the active degree
+        const int warp_base = base + warp * 32;
+        const int nvis = __popc(vis);
+        if ((row & 3) == 0) {
+            const int vpr = (need + 3) >> 2;  // float4 pieces per row (row start is 16B aligned)
+            const int total = nvis * vpr;
+            for (int j = lane; j < total; j += 32) {
+                const int v = j / vpr, part = j - v * vpr;
+                const int src_lane = __fns(vis, 0, v + 1);
+                const float4 val = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_base + src_lane) * row) + part);
+                float* d = tile + src_lane * kShStride + 4 * part;
+                d[0] = val.x; d[1] = val.y; d[2] = val.z; d[3] = val.w;
+            }
+        } else {
+            const int total = nvis * need;
+            for (int j = lane; j < total; j += 32) {
+                const int v = j / need, part = j - v * need;
+                const int src_lane = __fns(vis, 0, v + 1);
+                tile[src_lane * kShStride + part] = __ldg(p.shs + (size_t)(warp_base + src_lane) * row + part);
+            }
+        }
+        __syncwarp();
+        if (alive) {
+            sh_to_rgb(p.D, __fadd_rn(mx, -view[32]), __fadd_rn(my, -view[33]), __fadd_rn(mz, -view[34]),
+                      tile + lane * kShStride, rgb, clamped);
+        }
+    }
+
+    if (idx < p.P) {
+        p.radii[idx] = alive ? rad : 0;
+        p.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
+        if (alive) {
+            p.gv.depths[idx] = depth;
+            p.gv.means2D[idx] = make_float2(px, py);
+            p.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
+                                                  __fmul_rn(ca, det_inv), __ldg(p.opacities + idx));
+            p.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
+        }
+    }
+    if (lane == 0 && vis) atomicAdd(&p.gv.info->num_visible, __popc(vis));
+}
+
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
+                                    const float* __restrict__ view, uint8_t* __restrict__ present) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float x = __ldg(means3D + 3 * (size_t)idx), y = __ldg(means3D + 3 * (size_t)idx + 1),
+                z = __ldg(means3D + 3 * (size_t)idx + 2);
+    float m[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m[k] = __ldg(view + k);
+    present[idx] = xform_row_rn(m, 2, x, y, z) > kNearPlane ? 1 : 0;
+}
+
+}  // namespace
+
+int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                      const float* colors_precomp, const float* opacities, const float* scales,
+                      float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                      const float* view, const float* proj, const float* campos, float tanfovx,
+                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug) {
+    PreParams p;
+    p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H; p.gx = g.gx; p.gy = g.gy;
+    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.opacities = opacities;
+    p.scales = scales; p.scale_modifier = scale_modifier; p.rotations = rotations;
+    p.cov3D_precomp = cov3D_precomp; p.view = view; p.proj = proj; p.campos = campos;
+    p.tanfovx = tanfovx; p.tanfovy = tanfovy;
+    p.focal_x = (float)g.W / (2.0f * tanfovx);
+    p.focal_y = (float)g.H / (2.0f * tanfovy);
+    p.radii = radii; p.gv = gv;
+    const int blocks = (P + kPreThreads - 1) / kPreThreads;
+    preprocess_kernel<<<blocks, kPreThreads, 0, s>>>(p);
+    GSR_AFTER_LAUNCH(s, debug);
+    return GSR_OK;
+}
+
+int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
+                        cudaStream_t s) {
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+    GSR_AFTER_LAUNCH(s, 0);
+    return GSR_OK;
+}
+
+}  // namespace gsr
