@@ -37,6 +37,12 @@ extern "C" {
 
 #define GSR_ABI_VERSION 1
 
+#if defined(__GNUC__)
+#define GSR_API __attribute__((visibility("default")))
+#else
+#define GSR_API
+#endif
+
 enum gsr_status {
     GSR_OK = 0,
     GSR_ERR_INVALID_ARGUMENT = 1, /* NULL / inconsistent pointers, negative sizes, bad degree */
@@ -86,24 +92,24 @@ typedef struct gsr_layout {
     size_t image_bytes;
 } gsr_layout;
 
-int gsr_abi_version(void);
+GSR_API int gsr_abi_version(void);
 
 /* Replaces: the exception text the reference's CHECK_CUDA macro raises. Never NULL. */
-const char* gsr_status_string(int status);
+GSR_API const char* gsr_status_string(int status);
 /* cudaGetErrorString of the last CUDA error this THREAD saw inside the library ("" if none). */
-const char* gsr_last_cuda_error(void);
+GSR_API const char* gsr_last_cuda_error(void);
 
 /* Replaces: the three resize lambdas (`resizeFunctional`) the reference's glue hands to
  * CudaRasterizer::Rasterizer::forward — here the caller sizes and owns the buffers up front. */
-int gsr_workspace_bytes(int P, int width, int height, int64_t instance_capacity,
+GSR_API int gsr_workspace_bytes(int P, int width, int height, int64_t instance_capacity,
                         size_t* geom_bytes, size_t* binning_bytes, size_t* image_bytes);
-int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out);
+GSR_API int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out);
 
 /* Forward, stage 1 (replaces the first half of `_C.rasterize_gaussians`: preprocess + prefix sum).
  * Writes radii[P] and the geometry workspace; enqueues a copy of gsr_forward_info (num_rendered,
  * num_visible) into h_info if non-NULL.  D = active SH degree 0..3, M = coefficients per channel
  * in `shs` (>= (D+1)^2, <= 16). */
-int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D,
+GSR_API int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D,
                          const float* shs, const float* colors_precomp, const float* opacities,
                          const float* scales, float scale_modifier, const float* rotations,
                          const float* cov3D_precomp, const float* viewmatrix,
@@ -115,7 +121,7 @@ int gsr_forward_geometry(int P, int D, int M, int width, int height, const float
  * render).  Never syncs the host: R is read on the device; if R > instance_capacity the overflow
  * flag is raised, nothing is binned (out_color then holds the background only), and the caller
  * re-runs this stage with a larger binning workspace (the geometry workspace stays valid). */
-int gsr_forward_render(int P, int width, int height, const float* bg, const int32_t* radii,
+GSR_API int gsr_forward_render(int P, int width, int height, const float* bg, const int32_t* radii,
                        void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws,
                        float* out_color, gsr_forward_info* h_info, void* stream, int debug);
 
@@ -127,7 +133,7 @@ int gsr_forward_render(int P, int width, int height, const float* bg, const int3
  * dL_dmeans2D is [P,3] (z = 0) in the reference's NDC-scaled convention
  * (scene/gaussian_model.py:775-777 reads [:, :2]).  dL_dcolors [P,3], dL_dopacity [P],
  * dL_dmeans3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3], dL_dscales [P,3], dL_drots [P,4]. */
-int gsr_backward(int P, int D, int M, int width, int height, const float* bg,
+GSR_API int gsr_backward(int P, int D, int M, int width, int height, const float* bg,
                  const float* means3D, const float* shs, const float* colors_precomp,
                  const float* scales, float scale_modifier, const float* rotations,
                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
@@ -138,12 +144,12 @@ int gsr_backward(int P, int D, int M, int width, int height, const float* bg,
                  int debug);
 
 /* Replaces `_C.mark_visible`: present[i] = 1 iff Gaussian i passes the near-plane test. */
-int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
 
 /* Number of kernel launches the library has issued in this process (all threads); bench.py
  * reports the difference across its timed region as `gpu_launches`. */
-int64_t gsr_launch_count(void);
+GSR_API int64_t gsr_launch_count(void);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,152 @@
+"""ctypes binding of libgsrast_b200.so — the C ABI declared in include/gsrast_b200.h.
+
+This is the only place the package touches native code.  There is NO fallback: if the shared
+library is missing or does not export the ABI this module raises, and every op built on it
+fails loudly (north_star: "no CPU fallback").  The library replaces the pybind11 module `_C`
+of the reference's rasterizer dependency (imported at
+/root/reference/gaussian_renderer/__init__.py:15).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libgsrast_b200.so")
+CSRC_DIR = os.path.join(_HERE, "csrc")
+ABI_VERSION = 1
+
+GSR_OK = 0
+GSR_ERR_INVALID_ARGUMENT = 1
+GSR_ERR_CUDA = 2
+GSR_ERR_WORKSPACE = 3
+GSR_ERR_UNSUPPORTED = 4
+
+# Every symbol include/gsrast_b200.h declares (tests check the .so exports all of them).
+EXPORTS = (
+    "gsr_abi_version", "gsr_status_string", "gsr_last_cuda_error", "gsr_workspace_bytes",
+    "gsr_workspace_layout", "gsr_forward_geometry", "gsr_forward_render", "gsr_backward",
+    "gsr_mark_visible", "gsr_launch_count",
+)
+
+
+class ForwardInfo(ctypes.Structure):
+    _fields_ = [("num_rendered", ctypes.c_int32), ("overflow", ctypes.c_int32),
+                ("num_visible", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+class Layout(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_size_t) for n in (
+        "g_depths", "g_means2D", "g_conic_opacity", "g_rgb", "g_tiles_touched", "g_point_offsets",
+        "g_info", "g_grad_accum", "g_scan_tmp", "geom_bytes",
+        "b_keys_unsorted", "b_vals_unsorted", "b_keys", "b_point_list", "b_keys_alt", "b_vals_alt",
+        "b_sort_tmp", "binning_bytes",
+        "i_ranges", "i_final_T", "i_n_contrib", "image_bytes")]
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+class GsrError(RuntimeError):
+    def __init__(self, status: int, where: str):
+        L = lib()
+        msg = L.gsr_status_string(status).decode()
+        cuda = L.gsr_last_cuda_error().decode()
+        super().__init__(f"{where}: {msg}" + (f" ({cuda})" if status == GSR_ERR_CUDA and cuda else ""))
+        self.status = status
+
+
+def build(verbose: bool = False, extra_nvflags: str = "") -> str:
+    """Compile the CUDA sources for sm_100a with the in-tree Makefile (nvcc cross-compiles
+    without a GPU).  Output stays in-tree so it travels to the GPU box."""
+    cmd = ["make", "-C", CSRC_DIR, "-j", str(os.cpu_count() or 4)]
+    if extra_nvflags:
+        cmd.append(f"EXTRA_NVFLAGS={extra_nvflags}")
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout)
+    if r.returncode != 0:
+        raise NativeLibraryError("building libgsrast_b200.so failed:\n" + r.stdout[-4000:])
+    return LIB_PATH
+
+
+_lib = None
+_lock = threading.Lock()
+_vp, _i, _f, _i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_int64
+
+
+def lib() -> ctypes.CDLL:
+    """Load (once) and type the shared library.  Raises NativeLibraryError if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise NativeLibraryError(
+                f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "or `make -C mvs_gaussian_splatting_b200/csrc`. There is no CPU or PyTorch fallback.")
+        L = ctypes.CDLL(LIB_PATH)
+        for name in EXPORTS:
+            if not hasattr(L, name):
+                raise NativeLibraryError(f"{LIB_PATH} does not export {name}")
+        L.gsr_abi_version.restype = _i
+        if L.gsr_abi_version() != ABI_VERSION:
+            raise NativeLibraryError(f"ABI version mismatch: library {L.gsr_abi_version()}, binding {ABI_VERSION}")
+        L.gsr_status_string.restype = ctypes.c_char_p
+        L.gsr_status_string.argtypes = [_i]
+        L.gsr_last_cuda_error.restype = ctypes.c_char_p
+        L.gsr_launch_count.restype = _i64
+        L.gsr_workspace_bytes.argtypes = [_i, _i, _i, _i64] + [ctypes.POINTER(ctypes.c_size_t)] * 3
+        L.gsr_workspace_layout.argtypes = [_i, _i, _i, _i64, ctypes.POINTER(Layout)]
+        L.gsr_forward_geometry.argtypes = [
+            _i, _i, _i, _i, _i,          # P D M W H
+            _vp, _vp, _vp, _vp,          # means3D shs colors_precomp opacities
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _vp, _vp, _vp, _f, _f,       # view proj campos tanfovx tanfovy
+            _i, _vp, _vp, _vp, _vp, _i]  # prefiltered radii geom_ws h_info stream debug
+        L.gsr_forward_render.argtypes = [
+            _i, _i, _i, _vp, _vp,        # P W H bg radii
+            _vp, _vp, _i64, _vp,         # geom_ws binning_ws capacity image_ws
+            _vp, _vp, _vp, _i]           # out_color h_info stream debug
+        L.gsr_backward.argtypes = [
+            _i, _i, _i, _i, _i, _vp,     # P D M W H bg
+            _vp, _vp, _vp,               # means3D shs colors_precomp
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _vp, _vp, _vp, _f, _f, _vp,  # view proj campos tanfovx tanfovy radii
+            _vp, _vp, _i64, _vp,         # geom_ws binning_ws capacity image_ws
+            _vp,                         # dL_dpix
+            _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{means2D,colors,opacity,means3D,cov3D,sh,scales,rots}
+            _vp, _i]                     # stream debug
+        L.gsr_mark_visible.argtypes = [_i, _vp, _vp, _vp, _vp, _vp]
+        for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",
+                     "gsr_forward_render", "gsr_backward", "gsr_mark_visible"):
+            getattr(L, name).restype = _i
+        _lib = L
+    return _lib
+
+
+def check(status: int, where: str) -> None:
+    if status != GSR_OK:
+        raise GsrError(status, where)
+
+
+def workspace_bytes(P: int, W: int, H: int, capacity: int):
+    g, b, i = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+    check(lib().gsr_workspace_bytes(P, W, H, capacity, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i)),
+          "gsr_workspace_bytes")
+    return g.value, b.value, i.value
+
+
+def workspace_layout(P: int, W: int, H: int, capacity: int) -> Layout:
+    out = Layout()
+    check(lib().gsr_workspace_layout(P, W, H, capacity, ctypes.byref(out)), "gsr_workspace_layout")
+    return out
+
+
+def launch_count() -> int:
+    return int(lib().gsr_launch_count())
