@@ -1,0 +1,126 @@
+"""Generates the golden fixtures in this directory by IMPORTING the reference's own Python code
+from /root/reference (run in the build container only; the GPU box has no /root/reference, so the
+.npz outputs are committed next to this script).
+
+What the reference tree holds for the rasterizer path is the Python restatement of two preprocess
+sub-steps plus the camera conventions:
+  utils/sh_utils.py:57-112            eval_sh            -> sh_eval.npz
+  gaussian_renderer/__init__.py:80-84 direction / +0.5 / clamp recipe around it
+  utils/general_utils.py:64-110       build_rotation, build_scaling_rotation, strip_symmetric
+  scene/gaussian_model.py:28-32       Sigma = L L^T                      -> cov3d.npz
+  utils/graphics_utils.py:38-71       getWorld2View2, getProjectionMatrix
+  scene/cameras.py:54-57              transposes, full_proj, camera_center -> cameras.npz
+Those helpers hard-code device="cuda"; torch.zeros is patched to ignore the device so they run on
+the CPU unmodified.
+
+    python tests/golden/make_golden.py
+"""
+import math
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = "/root/reference"
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REF)
+
+_zeros = torch.zeros
+
+
+def _cpu_zeros(*a, **k):
+    k.pop("device", None)
+    return _zeros(*a, **k)
+
+
+torch.zeros = _cpu_zeros
+from utils.sh_utils import eval_sh  # noqa: E402
+from utils.general_utils import build_rotation, build_scaling_rotation, strip_symmetric  # noqa: E402
+from utils.graphics_utils import getWorld2View2, getProjectionMatrix  # noqa: E402
+
+
+def sh_fixture():
+    rng = np.random.Generator(np.random.PCG64(11))
+    P = 512
+    xyz = rng.normal(0, 3, (P, 3))
+    campos = np.array([0.3, -0.2, 0.1])
+    shs = rng.normal(0, 0.6, (P, 16, 3))  # [P, coeff, rgb] as the rasterizer receives it
+    out = {"xyz": xyz, "campos": campos, "shs": shs}
+    for dt, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+        feats = torch.from_numpy(shs).to(dt)
+        x = torch.from_numpy(xyz).to(dt)
+        c = torch.from_numpy(campos).to(dt)
+        for deg in range(4):
+            # gaussian_renderer/__init__.py:80-84
+            shs_view = feats.transpose(1, 2).view(-1, 3, 16)
+            dir_pp = x - c.repeat(feats.shape[0], 1)
+            dir_pp_normalized = dir_pp / dir_pp.norm(dim=1, keepdim=True)
+            sh2rgb = eval_sh(deg, shs_view, dir_pp_normalized)
+            out[f"colors_deg{deg}_{tag}"] = torch.clamp_min(sh2rgb + 0.5, 0.0).numpy()
+            out[f"raw_deg{deg}_{tag}"] = (sh2rgb + 0.5).numpy()
+    np.savez_compressed(os.path.join(HERE, "sh_eval.npz"), **out)
+
+
+def cov_fixture():
+    rng = np.random.Generator(np.random.PCG64(12))
+    P = 512
+    scales = np.exp(rng.normal(-2, 1, (P, 3)))
+    q = rng.normal(0, 1, (P, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)  # the rasterizer uses q as given; the helper normalises
+    out = {"scales": scales, "rotations": q}
+    for mod in (1.0, 0.37):
+        for dt, tag in ((torch.float64, "f64"), (torch.float32, "f32")):
+            s = torch.from_numpy(scales).to(dt)
+            r = torch.from_numpy(q).to(dt)
+            if dt == torch.float32:
+                L = build_scaling_rotation(mod * s, r)           # the helper as shipped (float32 buffers)
+            else:
+                # the helper allocates float32 buffers; for a float64 truth run its rotation formula
+                # with the allocation patched to float64 and compose L = R diag(s) as it does
+                torch.zeros = lambda *a, **k: _cpu_zeros(*a, **{**k, "dtype": torch.float64})
+                Rm = build_rotation(r)
+                torch.zeros = _cpu_zeros
+                L = Rm @ torch.diag_embed(mod * s)
+            cov = L @ L.transpose(1, 2)
+            if dt == torch.float32:
+                sym = strip_symmetric(cov)
+            else:
+                sym = torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], 1)
+            out[f"cov6_mod{mod}_{tag}"] = sym.numpy()
+    np.savez_compressed(os.path.join(HERE, "cov3d.npz"), **out)
+
+
+def camera_fixture():
+    rng = np.random.Generator(np.random.PCG64(13))
+    out = {}
+    n = 6
+    out["n"] = np.array(n)
+    for i in range(n):
+        A = rng.normal(size=(3, 3))
+        Q, _ = np.linalg.qr(A)
+        if np.linalg.det(Q) < 0:
+            Q[:, 0] = -Q[:, 0]
+        if i == 0:
+            Q = np.eye(3)
+        T = rng.normal(0, 2, 3) if i else np.zeros(3)
+        fovx = math.radians(40 + 10 * i)
+        W, H = [(1920, 1080), (800, 800), (100, 70), (3840, 2160), (1008, 756), (640, 360)][i]
+        fovy = 2 * math.atan(H / (2 * (W / (2 * math.tan(fovx / 2)))))
+        # scene/cameras.py:54-57 on the CPU
+        wvt = torch.tensor(getWorld2View2(Q, T, np.array([0.0, 0.0, 0.0]), 1.0)).transpose(0, 1)
+        proj = getProjectionMatrix(znear=0.01, zfar=100.0, fovX=fovx, fovY=fovy).transpose(0, 1)
+        full = (wvt.unsqueeze(0).bmm(proj.unsqueeze(0))).squeeze(0)
+        center = wvt.inverse()[3, :3]
+        out[f"R{i}"], out[f"T{i}"] = Q, T
+        out[f"fovx{i}"], out[f"fovy{i}"], out[f"WH{i}"] = np.array(fovx), np.array(fovy), np.array([W, H])
+        out[f"view{i}"], out[f"proj{i}"] = wvt.contiguous().numpy(), proj.contiguous().numpy()
+        out[f"full{i}"], out[f"center{i}"] = full.contiguous().numpy(), center.numpy()
+    np.savez_compressed(os.path.join(HERE, "cameras.npz"), **out)
+
+
+if __name__ == "__main__":
+    sh_fixture()
+    cov_fixture()
+    camera_fixture()
+    print("wrote", [f for f in os.listdir(HERE) if f.endswith(".npz")])
