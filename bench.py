@@ -1,0 +1,486 @@
+"""bench.py — fwd+bwd of the differentiable Gaussian-splatting rasterizer on B200.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
+    python bench.py --impl reference --steps K --warmup W    # the CPU arm (oracle port, host cores)
+
+Workload (BASELINE.json configs[2], the one the metric is quoted on): 3 M synthetic Gaussians,
+SH degree 3, 1920x1080, one view per step per GPU, forward + backward with a fixed seeded
+dL/dpixel.  A "step" is one fwd+bwd of one view on every rank; with N > 1 each rank renders its
+own camera of the batch (weak scaling, one camera subset per GPU) and the 59-float-per-Gaussian
+parameter gradients are summed with ONE NCCL all-reduce inside the timed region.
+Prints ONE JSON line on rank 0 (contract: see DESIGN.md "Measurement").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from mvs_gaussian_splatting_b200 import synthetic as S  # noqa: E402  (numpy only)
+
+METRIC = "rasterizer_fwd_bwd_views_per_s"
+UNIT = "views/s"
+
+# Algorithmic cost model (DESIGN.md "Kernels and rooflines").
+FLOP_PER_EVAL = 18.0       # quadratic form, exp, opacity mul, min, compares, 1-alpha, T*
+FLOP_PER_BLEND_FWD = 8.0   # weight + 3 fma
+FLOP_PER_BLEND_BWD = 73.0  # reference backward per contributing pair (counted in DESIGN.md)
+FP32_LANES_PER_SM = 128
+N_SM = 148
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--points", type=int, default=3_000_000)
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--sh-degree", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=200.0,
+                    help="--impl reference: wall-clock budget the K+W CPU steps are sized for")
+    return ap.parse_args()
+
+
+def bench_camera(k: int, W: int, H: int) -> S.Camera:
+    """Camera k of the batch: k = 0 is the front camera the scene was generated for; the others sit
+    on a 0.5-unit ring around it and look at the scene centre (similar work per rank)."""
+    if k == 0:
+        return S.front_camera(W, H)
+    a = 2 * math.pi * (k - 1) / 7.0
+    R, t = S.look_at([0.5 * math.cos(a), 0.5 * math.sin(a), 0.0], [0.0, 0.0, 10.5])
+    return S.make_camera(R, t, math.radians(60.0), W, H)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=float(d["hbm_gbs"]), sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)), source="measured")
+    return dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+
+
+# ------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; same fields as the profiling recipe's nvidia-smi line)
+# ------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    def __init__(self, index: int, period_s: float = 0.05):
+        super().__init__(daemon=True)
+        self.index, self.period, self.samples, self.reasons = index, period_s, [], set()
+        self.stop_flag = threading.Event()
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                 "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                 "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self.stop_flag.wait(self.period)
+
+    def result(self):
+        self.stop_flag.set()
+        if self.nv is None or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (oracle/gs_oracle.c) on the host cores.  The reference's own CPU/CUDA
+# implementation of this path is an un-vendored submodule, so kind = "port".
+# ------------------------------------------------------------------------------------------
+def host_threads() -> int:
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+class CpuArm:
+    """fwd+bwd of one view with the oracle; the two blend stages may run on a strided subset of the
+    tile rows (bounded sample), the per-Gaussian and binning stages always run in full."""
+
+    def __init__(self, g, cam, D, dL, threads):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import gs_oracle as O
+        O.build()
+        self.O, self.g, self.cam, self.D, self.dL, self.threads = O, g, cam, D, dL, threads
+        self.gx, self.gy = O.grid(cam.width, cam.height)
+
+    def rows(self, stride):
+        return [(r * self.gx, (r + 1) * self.gx) for r in range(0, self.gy, stride)]
+
+    def step(self, stride=1):
+        O, g, cam, th = self.O, self.g, self.cam, self.threads
+        W, H = cam.width, cam.height
+        common = (cam.world_view_transform, cam.full_proj_transform, cam.camera_center, W, H, cam.tanfovx,
+                  cam.tanfovy, self.D)
+        bg = np.zeros(3, np.float32)
+        t0 = time.perf_counter()
+        pre = O.preprocess(g["means3D"], g["scales"], g["rotations"], g["opacities"], g["shs"], *common, threads=th)
+        binned = O.bin_instances(pre, W, H)
+        t1 = time.perf_counter()
+        tr = None if stride == 1 else self.rows(stride)
+        fwd = O.blend_forward(pre, binned, bg, W, H, threads=th, tile_ranges=tr)
+        gb = O.blend_backward(pre, binned, fwd, bg, self.dL, W, H, threads=th, tile_ranges=tr)
+        t2 = time.perf_counter()
+        O.preprocess_backward(g["means3D"], g["scales"], g["rotations"], g["shs"], *common, pre, gb, threads=th)
+        t3 = time.perf_counter()
+        frac = 1.0 if stride == 1 else len(tr) / self.gy
+        t_full = (t1 - t0) + (t3 - t2) + (t2 - t1) / frac
+        return dict(t_view_s=t_full, t_wall_s=t3 - t0, rows_frac=frac, t_fixed_s=(t1 - t0) + (t3 - t2),
+                    t_blend_s=t2 - t1)
+
+    def describe(self, stride):
+        if stride == 1:
+            return "full view: all Gaussians, all tiles"
+        return (f"all Gaussians through preprocess/binning/preprocess-backward; blend fwd+bwd on every "
+                f"{stride}th tile row ({len(self.rows(stride))}/{self.gy} rows), blend time scaled by rows")
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # under torchrun only rank 0 runs the CPU arm
+    W, H, P, D = args.width, args.height, args.points, args.sh_degree
+    cam = bench_camera(0, W, H)
+    g = S.make_gaussians(P, cam, seed=0)
+    dL = np.random.Generator(np.random.PCG64(1234)).normal(size=(3, H, W)).astype(np.float32)
+    th = host_threads()
+    arm = CpuArm(g, cam, D, dL, th)
+    # size the per-step sample: one full calibration step (untimed), then pick the row stride
+    cal = arm.step(1)
+    n = args.steps + args.warmup
+    per_step = max(args.cpu_budget_s - cal["t_wall_s"], 1.0) / max(n, 1)
+    stride = 1
+    while stride < arm.gy and arm_estimate(cal, stride, arm.gy) > per_step:
+        stride += 1
+    for _ in range(args.warmup):
+        arm.step(stride)
+    ts = [arm.step(stride)["t_view_s"] for _ in range(args.steps)]
+    t = float(np.mean(ts)) if ts else cal["t_view_s"]
+    value = 1.0 / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, 1 view", "arm": "CPU oracle port, host cores"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": th, "kind": "port", "sample": arm.describe(stride)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def arm_estimate(cal, stride, gy):
+    """Predicted wall seconds of one sampled step from the full calibration step."""
+    rows = len(range(0, gy, stride))
+    return cal["t_fixed_s"] + cal["t_blend_s"] * rows / gy
+
+
+# ------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------
+def stage_rooflines(stage_ms, counts, peaks, clocks):
+    """Per-stage algorithmic cost / measured time against the roofline that bounds the stage.
+    Bytes and FLOPs per unit are the figures of SURVEY 8(d), restated in DESIGN.md."""
+    P, Pv, R, tiles = counts["P"], counts["P_visible"], counts["R"], counts["tiles"]
+    E, C, En = counts["pairs_evaluated"], counts["pairs_blended"], counts["sum_n_contrib"]
+    keybits = 32 + max(1, math.ceil(math.log2(max(tiles, 2))))
+    hbm = {
+        "preprocess": 52.0 * P + 259.0 * Pv,
+        "scan": 8.0 * P,
+        "emit_keys": 12.0 * R + 24.0 * Pv,
+        "radix_sort": (24.0 * math.ceil(keybits / 8) + 8.0) * R,
+        "tile_ranges": 8.0 * R + 8.0 * tiles,
+        "preprocess_backward": 303.0 * Pv + 240.0 * P,
+    }
+    flops = {
+        "blend_forward": FLOP_PER_EVAL * E + FLOP_PER_BLEND_FWD * C,
+        "blend_backward": FLOP_PER_EVAL * En + FLOP_PER_BLEND_BWD * C,
+    }
+    fp32_peak = N_SM * FP32_LANES_PER_SM * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s, FMA = 2
+    out = {}
+    for name, ms in stage_ms.items():
+        if ms <= 0:
+            continue
+        if name in hbm:
+            a = hbm[name] / (ms * 1e-3) / 1e9
+            out[name] = {"bound": "hbm", "achieved": a, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "frac": a / peaks["hbm_gbs"], "traffic": None, "ms": ms,
+                         "algorithmic_bytes": hbm[name], "peak_source": peaks["source"]}
+        elif name in flops:
+            a = flops[name] / (ms * 1e-3) / 1e12
+            out[name] = {"bound": "fp32_simt_issue", "achieved": a, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": a / fp32_peak, "traffic": None, "ms": ms, "algorithmic_flops": flops[name],
+                         "peak_source": "nominal 148 SM x 128 lanes x 2 x clocks.max.sm (no tensor-core work on "
+                                        "this path; MEASURED_PEAKS.json has no FP32 SIMT figure)"}
+    return out
+
+
+def load_traffic():
+    """dram bytes per launch from the committed ncu --set full capture, if one is recorded."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
+
+
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from mvs_gaussian_splatting_b200 import (GaussianRasterizationSettings, GaussianRasterizer, GradientArena,
+                                             _native, blend_pair_counts, last_forward_stats, rasterize_backward,
+                                             rasterize_forward)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the rasterizer has no CPU path; use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    _native.lib()  # fail loudly when libgsrast_b200.so is missing
+
+    W, H, P, D = args.width, args.height, args.points, args.sh_degree
+    M = 16
+    g = S.make_gaussians(P, bench_camera(0, W, H), sh_coeffs=M, seed=0)   # same scene on every rank
+    cam = bench_camera(rank, W, H)                                        # this rank's camera of the batch
+    host = {k: torch.from_numpy(v).pin_memory() for k, v in g.items()}
+    t = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+    kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], D)
+    cam_host = torch.from_numpy(np.concatenate([kw["viewmatrix"].ravel(), kw["projmatrix"].ravel(),
+                                                kw["campos"].ravel(), kw["bg"].ravel()]).astype(np.float32)).pin_memory()
+
+    def settings_from(block):
+        k2 = dict(kw)
+        k2.update(viewmatrix=block[0:16].view(4, 4), projmatrix=block[16:32].view(4, 4), campos=block[32:35],
+                  bg=block[35:38])
+        return GaussianRasterizationSettings(**k2)
+
+    rs = settings_from(cam_host.to(dev))
+    rng = np.random.Generator(np.random.PCG64(1234))
+    dL_np = rng.normal(size=(3, H, W)).astype(np.float32)
+    dL = torch.from_numpy(dL_np).to(dev)
+    arena = GradientArena(P, M, dev)
+
+    def step():
+        color, radii, ctx, inp = rasterize_forward(t["means3D"], t["shs"], None, t["opacities"], t["scales"],
+                                                   t["rotations"], None, rs)
+        rasterize_backward(ctx, inp, rs, dL, arena=arena)
+        if world > 1:
+            dist.all_reduce(arena.flat)
+        return ctx
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        ctx = step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    _native.stage_timing_enable(True)
+    _native.stage_timing_read()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = _native.launch_count()
+    e0.record()
+    for _ in range(args.steps):
+        ctx = step()
+    e1.record()
+    barrier()
+    launches = _native.launch_count() - n0
+    ms_total = e0.elapsed_time(e1)
+    _native.stage_timing_enable(False)
+    stages = _native.stage_timing_read()
+    clocks = sampler.result()
+    if world > 1:
+        tt = torch.tensor([ms_total], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = world * 1e3 / ms_step
+
+    # ---- counts for the algorithmic cost model (outside the timed region) ----
+    st = last_forward_stats(dev)
+    ev, bl = blend_pair_counts(ctx)
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    counts = dict(P=P, P_visible=st["num_visible"], R=st["num_rendered"], tiles=gx * gy, pairs_evaluated=ev,
+                  pairs_blended=bl, sum_n_contrib=int(ctx.array("n_contrib").long().sum().item()))
+    stage_ms = {k: v[0] / max(v[1], 1) for k, v in stages.items() if v[1]}
+    peaks = load_peaks()
+    roofs = stage_rooflines(stage_ms, counts, peaks, clocks)
+    traffic = load_traffic()
+    for k, r in roofs.items():
+        r["traffic"] = traffic.get(k)
+    dominant = max(stage_ms, key=stage_ms.get)
+
+    # ---- e2e: the public autograd API with host-side per-step inputs ----
+    e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer)
+    e2e_hp = run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward,
+                                 arena) if world == 1 else None
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, 1 view per GPU per step"
+                               + (", + NCCL all-reduce of 59 f32/Gaussian gradients" if world > 1 else ""),
+                   "baseline_config": "BASELINE.json configs[2]", "l2": "inputs (708 MB) larger than L2, no flush",
+                   "parallelism": f"views x{world}", "counts": counts},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofs.get(dominant),
+        "dominant_stage": dominant,
+        "stages": roofs,
+        "stage_ms_sum": sum(stage_ms.values()),
+        "e2e": e2e,
+    }
+    if e2e_hp is not None:
+        line["e2e_host_params"] = e2e_hp
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_baseline(g, cam, D, dL_np, budget_s=30.0):
+    th = host_threads()
+    arm = CpuArm(g, cam, D, dL_np, th)
+    cal = arm.step(1)                      # warm-up + calibration (untimed)
+    stride = 1
+    while stride < arm.gy and 2 * arm_estimate(cal, stride, arm.gy) > budget_s:
+        stride += 1
+    ts = [arm.step(stride)["t_view_s"] for _ in range(2)]
+    t = float(np.mean(ts))
+    return {"value": 1.0 / t, "unit": UNIT, "cores": th, "kind": "port", "sample": arm.describe(stride),
+            "ms_per_view": 1e3 * t}
+
+
+def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer):
+    """The call a user of the reference makes (gaussian_renderer/__init__.py:257-265 + train.py:95-113):
+    per step the camera block and the ground-truth image come from PINNED HOST memory, the image is
+    rendered through GaussianRasterizer (autograd), an L1 loss is formed, backward() runs, and the
+    loss is read back to the host.  The Gaussian parameters are model state and stay in HBM, as in
+    the reference's training loop."""
+    H, W = args.height, args.width
+    gt_host = torch.from_numpy((0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)).pin_memory()
+    params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+
+    def step():
+        block = cam_host.to(dev, non_blocking=True)
+        gt = gt_host.to(dev, non_blocking=True)
+        rs = settings_from(block)
+        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                              opacities=params["opacities"], scales=params["scales"],
+                                              rotations=params["rotations"])
+        loss = (color - gt).abs().mean()
+        loss.backward()
+        if world > 1:
+            for p in params.values():
+                dist.all_reduce(p.grad)
+        val = loss.item()                                   # D2H read of the step's result
+        for p in params.values():
+            p.grad = None                                   # train.py:142 zero_grad(set_to_none=True)
+        return val
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    n = max(5, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([dt], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+    return {"value": world * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
+            "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4,
+            "api": "GaussianRasterizer(settings)(...) + L1 loss + backward(), camera + ground-truth image from "
+                   "pinned host memory, loss read back; Gaussian parameters resident in HBM (model state)"}
+
+
+def run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward, arena):
+    """Cold variant: EVERY input of the C-ABI call starts in pinned host memory (all 236 B/Gaussian)
+    and every gradient is copied back to pinned host memory, each step.  PCIe-bound by construction;
+    reported so the reader can see what the boundary costs when nothing is resident."""
+    grad_host = torch.empty(arena.flat.numel(), dtype=torch.float32).pin_memory()
+
+    def step():
+        d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        color, radii, ctx, inp = rasterize_forward(d["means3D"], d["shs"], None, d["opacities"], d["scales"],
+                                                   d["rotations"], None, rs)
+        rasterize_backward(ctx, inp, rs, dL, arena=arena)
+        grad_host.copy_(arena.flat, non_blocking=True)
+        torch.cuda.synchronize()
+
+    step()
+    n = 5
+    t0 = time.perf_counter()
+    for _ in range(n):
+        step()
+    dt = time.perf_counter() - t0
+    h2d = sum(v.numel() * 4 for v in host.values())
+    return {"value": n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(grad_host.numel() * 4)}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -151,6 +151,25 @@ GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatri
  * reports the difference across its timed region as `gpu_launches`. */
 GSR_API int64_t gsr_launch_count(void);
 
+/* Instrumented re-run of the blend forward over the workspaces of a finished forward call (no
+ * reference equivalent; SURVEY 8d "debug counters in a separate instrumented build, not the timed
+ * one").  Writes two u64 to DEVICE memory: d_counters[0] = (pixel, splat) pairs the reference
+ * algorithm evaluates (each pixel walks its tile list until it saturates), d_counters[1] = pairs
+ * that are blended.  bench.py derives the blend kernels' algorithmic FLOPs from them. */
+GSR_API int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
+                                  int64_t instance_capacity, void* image_ws, uint64_t* d_counters,
+                                  void* stream);
+
+/* Optional per-stage device timing for benchmarks (no reference equivalent; the reference's only
+ * timer is the CUDA-event pair at train.py:47-48,70,109).  While enabled, the launches of each
+ * stage are bracketed by a CUDA event pair ON THE CALLER'S STREAM; gsr_stage_timing_read waits for
+ * the recorded events, returns per-stage summed milliseconds and bracket counts since the last
+ * read (arrays of at least gsr_stage_count() entries) and recycles the events.  Process-wide. */
+GSR_API int gsr_stage_count(void);
+GSR_API const char* gsr_stage_name(int stage);
+GSR_API int gsr_stage_timing_enable(int enable);
+GSR_API int gsr_stage_timing_read(double* ms_sum, int64_t* calls, int n);
+
 #ifdef __cplusplus
 }
 #endif

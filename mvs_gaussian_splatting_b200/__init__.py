@@ -7,12 +7,13 @@ Drop-in for the one hot path of ChikaYan/mvs_gaussian_splatting: the rasterizer 
 """
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians,
                          rasterize_forward, rasterize_backward, mark_visible, RasterContext,
-                         set_capacity_hint, last_forward_stats)
+                         set_capacity_hint, last_forward_stats, GradientArena, blend_pair_counts)
 from . import _native
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
            "rasterize_forward", "rasterize_backward", "mark_visible", "RasterContext",
-           "set_capacity_hint", "last_forward_stats", "build_native"]
+           "set_capacity_hint", "last_forward_stats", "GradientArena", "blend_pair_counts",
+           "build_native"]
 
 
 def build_native(verbose: bool = False) -> str:

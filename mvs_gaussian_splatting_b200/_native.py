@@ -28,7 +28,8 @@ GSR_ERR_UNSUPPORTED = 4
 EXPORTS = (
     "gsr_abi_version", "gsr_status_string", "gsr_last_cuda_error", "gsr_workspace_bytes",
     "gsr_workspace_layout", "gsr_forward_geometry", "gsr_forward_render", "gsr_backward",
-    "gsr_mark_visible", "gsr_launch_count",
+    "gsr_mark_visible", "gsr_launch_count", "gsr_stage_count", "gsr_stage_name",
+    "gsr_stage_timing_enable", "gsr_stage_timing_read", "gsr_blend_pair_counts",
 )
 
 
@@ -123,6 +124,15 @@ def lib() -> ctypes.CDLL:
             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{means2D,colors,opacity,means3D,cov3D,sh,scales,rots}
             _vp, _i]                     # stream debug
         L.gsr_mark_visible.argtypes = [_i, _vp, _vp, _vp, _vp, _vp]
+        L.gsr_blend_pair_counts.argtypes = [_i, _i, _i, _vp, _vp, _i64, _vp, _vp, _vp]
+        L.gsr_blend_pair_counts.restype = _i
+        L.gsr_stage_count.restype = _i
+        L.gsr_stage_name.restype = ctypes.c_char_p
+        L.gsr_stage_name.argtypes = [_i]
+        L.gsr_stage_timing_enable.argtypes = [_i]
+        L.gsr_stage_timing_enable.restype = _i
+        L.gsr_stage_timing_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(_i64), _i]
+        L.gsr_stage_timing_read.restype = _i
         for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",
                      "gsr_forward_render", "gsr_backward", "gsr_mark_visible"):
             getattr(L, name).restype = _i
@@ -150,3 +160,17 @@ def workspace_layout(P: int, W: int, H: int, capacity: int) -> Layout:
 
 def launch_count() -> int:
     return int(lib().gsr_launch_count())
+
+
+def stage_timing_enable(on: bool) -> None:
+    check(lib().gsr_stage_timing_enable(1 if on else 0), "gsr_stage_timing_enable")
+
+
+def stage_timing_read() -> dict:
+    """{stage name: (summed ms, number of brackets)} since the last read; waits for the events."""
+    L = lib()
+    n = L.gsr_stage_count()
+    ms = (ctypes.c_double * n)()
+    calls = (_i64 * n)()
+    check(L.gsr_stage_timing_read(ms, calls, n), "gsr_stage_timing_read")
+    return {L.gsr_stage_name(i).decode(): (float(ms[i]), int(calls[i])) for i in range(n)}

@@ -4,6 +4,8 @@
 // reference's `debug` flag does).
 #include <atomic>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "gsr_internal.cuh"
 
@@ -17,6 +19,36 @@ int cuda_fail(cudaError_t e) {
     t_last_error = e;
     cudaGetLastError();  // clear the sticky-less error state
     return GSR_ERR_CUDA;
+}
+
+// ---- per-stage timing: event pairs appended while enabled, summed by gsr_stage_timing_read ----
+static std::atomic<bool> g_timing{false};
+static std::mutex g_timing_mu;
+struct StageMark { int stage; cudaEvent_t ev[2]; };
+static std::vector<StageMark> g_marks;       // in use since the last read
+static std::vector<cudaEvent_t> g_event_pool; // recycled events
+
+bool stage_timing_on() { return g_timing.load(std::memory_order_relaxed); }
+
+void stage_mark(int stage, cudaStream_t s, bool begin) {
+    std::lock_guard<std::mutex> lock(g_timing_mu);
+    auto get_event = []() {
+        cudaEvent_t e = nullptr;
+        if (!g_event_pool.empty()) { e = g_event_pool.back(); g_event_pool.pop_back(); }
+        else cudaEventCreate(&e);
+        return e;
+    };
+    if (begin) {
+        StageMark m;
+        m.stage = stage;
+        m.ev[0] = get_event();
+        m.ev[1] = get_event();
+        cudaEventRecord(m.ev[0], s);
+        g_marks.push_back(m);
+    } else {
+        for (size_t i = g_marks.size(); i-- > 0;)
+            if (g_marks[i].stage == stage) { cudaEventRecord(g_marks[i].ev[1], s); break; }
+    }
 }
 
 void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
@@ -121,6 +153,37 @@ const char* gsr_last_cuda_error(void) {
 }
 
 int64_t gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int gsr_stage_count(void) { return kStageCount; }
+
+const char* gsr_stage_name(int stage) {
+    static const char* names[kStageCount] = {"preprocess", "scan", "emit_keys", "radix_sort", "tile_ranges",
+                                             "blend_forward", "blend_backward", "preprocess_backward"};
+    return (stage >= 0 && stage < kStageCount) ? names[stage] : "";
+}
+
+int gsr_stage_timing_enable(int enable) {
+    g_timing.store(enable != 0, std::memory_order_relaxed);
+    return GSR_OK;
+}
+
+int gsr_stage_timing_read(double* ms_sum, int64_t* calls, int n) {
+    if (!ms_sum || !calls || n < kStageCount) return GSR_ERR_INVALID_ARGUMENT;
+    std::lock_guard<std::mutex> lock(g_timing_mu);
+    for (int i = 0; i < n; ++i) { ms_sum[i] = 0.0; calls[i] = 0; }
+    int st = GSR_OK;
+    for (const StageMark& m : g_marks) {
+        float ms = 0.f;
+        cudaError_t e = cudaEventSynchronize(m.ev[1]);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, m.ev[0], m.ev[1]);
+        if (e == cudaSuccess) { ms_sum[m.stage] += ms; calls[m.stage] += 1; }
+        else st = cuda_fail(e);
+        g_event_pool.push_back(m.ev[0]);
+        g_event_pool.push_back(m.ev[1]);
+    }
+    g_marks.clear();
+    return st;
+}
 
 int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out) {
     if (!out) return GSR_ERR_INVALID_ARGUMENT;
@@ -244,6 +307,18 @@ int gsr_backward(int P, int D, int M, int width, int height, const float* bg, co
                                       rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
                                       radii, gv, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
                                       dL_dsh, dL_dscales, dL_drots, s, debug);
+}
+
+int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
+                           int64_t instance_capacity, void* image_ws, uint64_t* d_counters, void* stream) {
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    if (!geom_ws || !image_ws || !binning_ws || !d_counters) return GSR_ERR_WORKSPACE;
+    gsr_layout L;
+    compute_layout(P, width, height, instance_capacity, &L);
+    return launch_blend_pair_counts(make_grid(width, height), geom_view(geom_ws, L), bin_view(binning_ws, L),
+                                    image_view(image_ws, L), reinterpret_cast<unsigned long long*>(d_counters),
+                                    static_cast<cudaStream_t>(stream));
 }
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -374,6 +374,7 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
     p.dL_dmeans2D = dL_dmeans2D; p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity;
     p.dL_dmeans3D = dL_dmeans3D; p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscales = dL_dscales;
     p.dL_drots = dL_drots;
+    StageScope scope(kStagePreprocessBwd, s);
     preprocess_backward_kernel<<<(P + kBwdThreads - 1) / kBwdThreads, kBwdThreads, 0, s>>>(p);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;

@@ -332,6 +332,7 @@ size_t sort_tmp_entries(size_t cap) {
 
 int launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp, cudaStream_t s,
                           int debug) {
+    StageScope scope(kStageScan, s);
     return scan_u32(in, out, n, tmp, false, s, debug);
 }
 
@@ -344,9 +345,12 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
     GSR_CUDA(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)g.tiles, s));
     if (cap == 0) return GSR_OK;
 
+    {
+    StageScope scope(kStageEmitKeys, s);
     emit_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, g.gx, g.gy, radii, gv.means2D, gv.depths,
                                                      gv.point_offsets, cap, bv.keys_unsorted, bv.vals_unsorted);
     GSR_AFTER_LAUNCH(s, debug);
+    }
 
     int passes, bits;
     sort_plan(32 + higher_msb((uint32_t)g.tiles), passes, bits);
@@ -368,6 +372,8 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
     const uint32_t* vin = bv.vals_unsorted;
     uint64_t* kout = bv.keys;
     uint32_t* vout = bv.point_list;
+    {
+    StageScope scope(kStageSort, s);
     for (int pass = 0; pass < passes; ++pass) {
         const int shift = pass * bits;
         sort_hist_kernel<<<nblk, kSortThreads, hist_smem, s>>>(kin, r_ptr, cap, shift, bits, table, nblk);
@@ -383,6 +389,8 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
         kout = to_alt ? bv.keys_alt : bv.keys;
         vout = to_alt ? bv.vals_alt : bv.point_list;
     }
+    }
+    StageScope scope(kStageTileRanges, s);
     tile_ranges_kernel<<<(cap + 255) / 256, 256, 0, s>>>(bv.keys, r_ptr, cap, iv.ranges);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;

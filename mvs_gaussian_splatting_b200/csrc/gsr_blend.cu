@@ -100,11 +100,14 @@ __device__ __forceinline__ int compact_slot(bool keep, int* s_wcount, int& total
 }
 
 // ------------------------------------ forward ----------------------------------------------
+// kCount = true is the INSTRUMENTED variant (gsr_blend_pair_counts): same decisions, no image
+// outputs, counts the (pixel, splat) pairs the reference algorithm evaluates and blends.
+template <bool kCount>
 __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
     int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, float* __restrict__ out_color, float* __restrict__ final_T,
-    uint32_t* __restrict__ n_contrib) {
+    uint32_t* __restrict__ n_contrib, unsigned long long* __restrict__ counters) {
     __shared__ float4 s_g[kBlendThreads];    // x, y, a2, b2
     __shared__ float2 s_c[kBlendThreads];    // c2, opacity
     __shared__ float4 s_col[kBlendThreads];  // r, g, b, list position (1-based, int bits)
@@ -118,6 +121,7 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
     uint32_t last = 0;
     bool done = !c.inside;
+    uint32_t n_blended = 0, stop_pos = 0;  // kCount only
 
     for (int base = 0; base < n; base += kBlendThreads) {
         if (__syncthreads_count(done) == kBlendThreads) break;
@@ -153,8 +157,10 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
             const float test_T = T * (1.0f - alpha);
             if (test_T < kTmin) {
                 done = true;
+                if (kCount) stop_pos = (uint32_t)__float_as_int(s_col[j].w);
                 continue;
             }
+            if (kCount) ++n_blended;
             const float4 col = s_col[j];
             const float wgt = alpha * T;
             C0 = fmaf(col.x, wgt, C0);
@@ -165,6 +171,21 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
         }
     }
 
+    if (kCount) {
+        // the reference walks its tile list until the pixel is done: stop position, else all n
+        unsigned long long ev = c.inside ? (stop_pos ? stop_pos : (uint32_t)n) : 0u;
+        unsigned long long bl = n_blended;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            ev += __shfl_xor_sync(0xffffffffu, ev, d);
+            bl += __shfl_xor_sync(0xffffffffu, bl, d);
+        }
+        if (lane_id() == 0) {
+            atomicAdd(counters, ev);
+            atomicAdd(counters + 1, bl);
+        }
+        return;
+    }
     if (c.inside) {
         const size_t pix = (size_t)c.py * W + c.px;
         const size_t plane = (size_t)W * H;
@@ -354,15 +375,27 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
 
 int launch_blend_forward(const Grid& g, const float* bg, GeomView gv, BinView bv, ImageView iv,
                          float* out_color, cudaStream_t s, int debug) {
-    blend_forward_kernel<<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
-                                                           gv.conic_opacity, gv.rgb, bg, out_color, iv.final_T,
-                                                           iv.n_contrib);
+    StageScope scope(kStageBlendFwd, s);
+    blend_forward_kernel<false><<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list,
+                                                                  gv.means2D, gv.conic_opacity, gv.rgb, bg, out_color,
+                                                                  iv.final_T, iv.n_contrib, nullptr);
     GSR_AFTER_LAUNCH(s, debug);
+    return GSR_OK;
+}
+
+int launch_blend_pair_counts(const Grid& g, GeomView gv, BinView bv, ImageView iv, unsigned long long* counters,
+                             cudaStream_t s) {
+    GSR_CUDA(cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned long long), s));
+    blend_forward_kernel<true><<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list,
+                                                                 gv.means2D, gv.conic_opacity, gv.rgb, nullptr, nullptr,
+                                                                 nullptr, nullptr, counters);
+    GSR_AFTER_LAUNCH(s, 0);
     return GSR_OK;
 }
 
 int launch_blend_backward(int P, const Grid& g, const float* bg, GeomView gv, BinView bv, ImageView iv,
                           const float* dL_dpix, cudaStream_t s, int debug) {
+    StageScope scope(kStageBlendBwd, s);
     GSR_CUDA(cudaMemsetAsync(gv.grad_accum, 0, sizeof(float) * 12 * (size_t)P, s));
     blend_backward_kernel<<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
                                                             gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,

@@ -38,6 +38,22 @@ int cuda_fail(cudaError_t e);  // records e for gsr_last_cuda_error(), returns G
         if (_e != cudaSuccess) return ::gsr::cuda_fail(_e);              \
     } while (0)
 
+// ---- optional per-stage device timing (gsr_stage_timing_*; off by default) -----------------
+enum Stage {
+    kStagePreprocess = 0, kStageScan, kStageEmitKeys, kStageSort, kStageTileRanges, kStageBlendFwd,
+    kStageBlendBwd, kStagePreprocessBwd, kStageCount
+};
+bool stage_timing_on();
+void stage_mark(int stage, cudaStream_t s, bool begin);
+// RAII: brackets the launches of one stage with a CUDA event pair on `s` when timing is enabled.
+struct StageScope {
+    int stage; cudaStream_t s; bool on;
+    StageScope(int stage_, cudaStream_t s_) : stage(stage_), s(s_), on(stage_timing_on()) {
+        if (on) stage_mark(stage, s, true);
+    }
+    ~StageScope() { if (on) stage_mark(stage, s, false); }
+};
+
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct Grid {
@@ -104,6 +120,11 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
 
 int launch_blend_forward(const Grid& g, const float* bg, GeomView gv, BinView bv, ImageView iv,
                          float* out_color, cudaStream_t s, int debug);
+
+// Instrumented forward (no outputs): counters[0] = pairs the reference algorithm evaluates,
+// counters[1] = pairs it blends.  Tools / benchmarks only.
+int launch_blend_pair_counts(const Grid& g, GeomView gv, BinView bv, ImageView iv,
+                             unsigned long long* counters, cudaStream_t s);
 
 int launch_blend_backward(int P, const Grid& g, const float* bg, GeomView gv, BinView bv,
                           ImageView iv, const float* dL_dpix, cudaStream_t s, int debug);

@@ -305,6 +305,7 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
     p.focal_y = (float)g.H / (2.0f * tanfovy);
     p.radii = radii; p.gv = gv;
     const int blocks = (P + kPreThreads - 1) / kPreThreads;
+    StageScope scope(kStagePreprocess, s);
     preprocess_kernel<<<blocks, kPreThreads, 0, s>>>(p);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;

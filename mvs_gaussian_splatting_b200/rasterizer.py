@@ -23,7 +23,7 @@ from . import _native
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
            "RasterContext", "rasterize_forward", "rasterize_backward", "mark_visible",
-           "set_capacity_hint", "last_forward_stats"]
+           "set_capacity_hint", "last_forward_stats", "GradientArena", "blend_pair_counts"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -230,11 +230,32 @@ def rasterize_forward(means3D, shs, colors_precomp, opacities, scales, rotations
     return color, radii, ctx, ctx_inputs
 
 
+class GradientArena:
+    """One flat float32 buffer holding the parameter gradients of a view back to back
+    (means3D [P,3] | shs [P,M,3] | opacities [P,1] | scales [P,3] | rotations [P,4], each segment
+    16-byte aligned), so that the multi-GPU step sums them with ONE all-reduce and no packing copy:
+    the backward kernel writes straight into the segments.  59 floats per Gaussian at M = 16
+    (the six Adam groups of scene/gaussian_model.py:245-252)."""
+
+    def __init__(self, P: int, M: int, device):
+        sizes = dict(means3D=3 * P, shs=3 * M * P, opacities=P, scales=3 * P, rotations=4 * P)
+        off, self.offsets = 0, {}
+        for k, n in sizes.items():
+            self.offsets[k] = (off, n)
+            off += (n + 3) // 4 * 4
+        self.flat = torch.zeros(off, dtype=torch.float32, device=device)
+        self.P, self.M = P, M
+        v = lambda k, *shape: self.flat[self.offsets[k][0]:self.offsets[k][0] + self.offsets[k][1]].view(*shape)
+        self.means3D, self.shs = v("means3D", P, 3), v("shs", P, M, 3)
+        self.opacities, self.scales, self.rotations = v("opacities", P, 1), v("scales", P, 3), v("rotations", P, 4)
+
+
 def rasterize_backward(ctx: RasterContext, ctx_inputs, raster_settings: GaussianRasterizationSettings,
-                       grad_out_color: torch.Tensor):
+                       grad_out_color: torch.Tensor, arena: Optional[GradientArena] = None):
     """Backward through the C ABI.  Returns the 8 gradients in the reference's order
     (means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3D_precomp);
-    entries for inputs that were not given are None."""
+    entries for inputs that were not given are None.  With `arena`, the parameter gradients are
+    written into its segments (overwritten, not accumulated)."""
     rs = raster_settings
     means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, view, proj, campos, bg = ctx_inputs
     device = means3D.device
@@ -244,12 +265,16 @@ def rasterize_backward(ctx: RasterContext, ctx_inputs, raster_settings: Gaussian
     if g is None or tuple(g.shape) != (3, ctx.H, ctx.W):
         raise RuntimeError("grad_out_color must be [3,H,W]")
     e = lambda *s: torch.empty(s, dtype=torch.float32, device=device)
-    d_means2D, d_opacity, d_means3D = e(P, 3), e(P, 1), e(P, 3)
+    if arena is not None and (arena.P != P or arena.M != M or shs is None or scales is None):
+        raise RuntimeError("gradient arena does not match this call (P, M, SH + scale/rotation inputs)")
+    d_means2D = e(P, 3)
+    d_opacity = arena.opacities if arena else e(P, 1)
+    d_means3D = arena.means3D if arena else e(P, 3)
     d_colors = e(P, 3) if colors_precomp is not None else None
     d_cov3D = e(P, 6) if cov3D_precomp is not None else None
-    d_sh = e(P, M, 3) if shs is not None else None
-    d_scales = e(P, 3) if scales is not None else None
-    d_rots = e(P, 4) if rotations is not None else None
+    d_sh = (arena.shs if arena else e(P, M, 3)) if shs is not None else None
+    d_scales = (arena.scales if arena else e(P, 3)) if scales is not None else None
+    d_rots = (arena.rotations if arena else e(P, 4)) if rotations is not None else None
     with torch.cuda.device(device):
         stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
         _native.check(L.gsr_backward(
@@ -260,6 +285,20 @@ def rasterize_backward(ctx: RasterContext, ctx_inputs, raster_settings: Gaussian
             _ptr(d_means2D), _ptr(d_colors), _ptr(d_opacity), _ptr(d_means3D), _ptr(d_cov3D), _ptr(d_sh),
             _ptr(d_scales), _ptr(d_rots), stream, 1 if rs.debug else 0), "gsr_backward")
     return d_means3D, d_means2D, d_sh, d_colors, d_opacity, d_scales, d_rots, d_cov3D
+
+
+def blend_pair_counts(ctx: RasterContext):
+    """(evaluated, blended) (pixel, splat) pair counts of the reference algorithm for a finished
+    forward (instrumented kernel; benchmarks only).  Synchronises."""
+    device = ctx.geom_ws.device
+    out = torch.zeros(2, dtype=torch.int64, device=device)
+    with torch.cuda.device(device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        _native.check(_native.lib().gsr_blend_pair_counts(
+            ctx.P, ctx.W, ctx.H, _ptr(ctx.geom_ws), _ptr(ctx.binning_ws), ctx.capacity, _ptr(ctx.image_ws),
+            _ptr(out), stream), "gsr_blend_pair_counts")
+    ev, bl = out.cpu().tolist()
+    return int(ev), int(bl)
 
 
 def mark_visible(positions: torch.Tensor, raster_settings: GaussianRasterizationSettings) -> torch.Tensor:

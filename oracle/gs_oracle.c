@@ -231,6 +231,19 @@ static void tile_rect(real px, real py, int radius, int gx, int gy, int* r4) {
     r4[3] = imin(gy, imax(0, f2i((((py + rf) + K(16.0)) - K(1.0)) / K(16.0))));
 }
 
+/* Direct entry points for the two sub-steps the reference restates in its own Python
+ * (tests/golden/sh_eval.npz, cov3d.npz pin them). */
+void FN(orc_sh_eval)(int P, int D, int M, const real* pos, const real* campos, const real* shs,
+                     real* rgb, uint8_t* clamped) {
+    for (int i = 0; i < P; ++i)
+        sh_to_rgb(D, pos + 3 * (size_t)i, campos, shs + 3 * (size_t)M * i, rgb + 3 * (size_t)i,
+                  clamped + 3 * (size_t)i);
+}
+void FN(orc_cov3d)(int P, const real* scales, real mod, const real* rots, real* cov6) {
+    for (int i = 0; i < P; ++i)
+        cov3d_from_scale_rot(scales + 3 * (size_t)i, mod, rots + 4 * (size_t)i, cov6 + 6 * (size_t)i);
+}
+
 /* ---- K1: preprocess forward ---------------------------------------------------------- */
 /* One Gaussian at a time: near-plane cull (view z <= 0.2), cov3D, EWA cov2D, conic, radius,
  * pixel centre, tile rect, SH colour.  Outputs for culled Gaussians are zero. */

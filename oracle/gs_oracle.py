@@ -63,6 +63,8 @@ def grid(W, H):
 
 
 def _ranges(n, threads):
+    if n <= 0:
+        return []
     threads = max(1, min(threads, n))
     step = (n + threads - 1) // threads
     return [(b, min(n, b + step)) for b in range(0, n, step)]
@@ -104,6 +106,24 @@ def preprocess(means3D, scales, rotations, opacities, shs, viewmatrix, projmatri
     return out
 
 
+def sh_eval(xyz, campos, shs, sh_degree, dtype=np.float32):
+    """SH colour of each point seen from campos: (rgb [P,3] after +0.5 and clamp, clamped [P,3])."""
+    xyz, shs, campos = _c(xyz, dtype), _c(shs, dtype), _c(campos, dtype).reshape(3)
+    P, M = xyz.shape[0], shs.shape[1]
+    rgb, clamped = np.zeros((P, 3), dtype), np.zeros((P, 3), np.uint8)
+    _fn("orc_sh_eval", dtype)(P, int(sh_degree), M, _p(xyz), _p(campos), _p(shs), _p(rgb), _p(clamped))
+    return rgb, clamped.astype(bool)
+
+
+def cov3d(scales, rotations, scale_modifier=1.0, dtype=np.float32):
+    """6-float upper-triangular 3D covariance from scale and (un-normalised) quaternion."""
+    scales, rotations = _c(scales, dtype), _c(rotations, dtype)
+    P = scales.shape[0]
+    out = np.zeros((P, 6), dtype)
+    _fn("orc_cov3d", dtype)(P, _p(scales), _real(dtype)(scale_modifier), _p(rotations), _p(out))
+    return out
+
+
 def _run_ranges(run, ranges):
     if len(ranges) <= 1:
         for rg in ranges:
@@ -137,8 +157,9 @@ def bin_instances(pre, W, H, dtype=np.float32):
                 point_list=vs[:R], ranges=ranges)
 
 
-def blend_forward(pre, binned, bg, W, H, dtype=np.float32, margin=1e-4, threads=1):
-    """K7."""
+def blend_forward(pre, binned, bg, W, H, dtype=np.float32, margin=1e-4, threads=1, tile_ranges=None):
+    """K7.  tile_ranges: optional list of [t0,t1) tile-index ranges to process instead of all tiles
+    (bench.py's bounded CPU sample); other pixels stay zero."""
     dt = dtype
     gx, gy = grid(W, H)
     out = np.zeros((3, H, W), dt)
@@ -154,12 +175,16 @@ def blend_forward(pre, binned, bg, W, H, dtype=np.float32, margin=1e-4, threads=
           _p(pre["conic_opacity"]), _p(bg), _p(out), _p(final_T), _p(n_contrib), _p(fragile),
           _real(dt)(margin), rg[0], rg[1])
 
-    _run_ranges(run, _ranges(gx * gy, threads * 8 if threads > 1 else 1))
+    if tile_ranges is None:
+        _run_ranges(run, _ranges(gx * gy, threads * 8 if threads > 1 else 1))
+    else:
+        with ThreadPoolExecutor(max(1, threads)) as ex:
+            list(ex.map(run, tile_ranges))
     return dict(color=out, final_T=final_T, n_contrib=n_contrib, fragile=fragile.astype(bool))
 
 
-def blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype=np.float32, threads=1):
-    """K8. Returns dL/dmean2D [P,2] (NDC-scaled), dL/dconic [P,3] (true partials of A,B,C),
+def blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype=np.float32, threads=1, tile_ranges=None):
+    """K8 (tile_ranges as in blend_forward). Returns dL/dmean2D [P,2] (NDC-scaled), dL/dconic [P,3] (true partials of A,B,C),
     dL/dopacity [P], dL/dcolor [P,3]."""
     dt = dtype
     P = pre["radii"].shape[0]
@@ -168,19 +193,24 @@ def blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype=np.float32, thread
     dL_dpix = _c(dL_dpix, dt)
     pl = np.ascontiguousarray(binned["point_list"]) if binned["num_rendered"] else np.zeros(1, np.uint32)
     f = _fn("orc_blend_bwd", dt)
-    rgs = _ranges(gx * gy, threads)
+    if tile_ranges is None:
+        tile_ranges = _ranges(gx * gy, threads * 8 if threads > 1 else 1)
+    # one accumulator per thread, ranges dealt round-robin (balances dense and sparse image regions)
+    nt = max(1, min(threads, len(tile_ranges)))
+    groups = [list(tile_ranges[i::nt]) for i in range(nt)]
     bufs = []
 
-    def run(rg):
+    def run(group):
         g = dict(dL_dmean2D=np.zeros((P, 2), dt), dL_dconic=np.zeros((P, 3), dt),
                  dL_dopacity=np.zeros(P, dt), dL_dcolor=np.zeros((P, 3), dt))
-        f(W, H, _p(binned["ranges"]), _p(pl), _p(pre["means2D"]), _p(pre["rgb"]),
-          _p(pre["conic_opacity"]), _p(bg), _p(fwd["final_T"]), _p(fwd["n_contrib"]), _p(dL_dpix),
-          _p(g["dL_dmean2D"]), _p(g["dL_dconic"]), _p(g["dL_dopacity"]), _p(g["dL_dcolor"]),
-          rg[0], rg[1])
+        for rg in group:
+            f(W, H, _p(binned["ranges"]), _p(pl), _p(pre["means2D"]), _p(pre["rgb"]),
+              _p(pre["conic_opacity"]), _p(bg), _p(fwd["final_T"]), _p(fwd["n_contrib"]), _p(dL_dpix),
+              _p(g["dL_dmean2D"]), _p(g["dL_dconic"]), _p(g["dL_dopacity"]), _p(g["dL_dcolor"]),
+              rg[0], rg[1])
         bufs.append(g)
 
-    _run_ranges(run, rgs)
+    _run_ranges(run, groups)
     acc = bufs[0]
     for g in bufs[1:]:
         for k in acc:
