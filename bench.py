@@ -77,7 +77,7 @@ def load_peaks():
 # clocks during the timed region (NVML; same fields as the profiling recipe's nvidia-smi line)
 # ------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    def __init__(self, index: int, period_s: float = 0.05):
+    def __init__(self, index: int, period_s: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.period, self.samples, self.reasons = index, period_s, [], set()
         self.stop_flag = threading.Event()
