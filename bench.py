@@ -343,10 +343,11 @@ def run_b200_arm(args):
 
     # ---- counts for the algorithmic cost model (outside the timed region) ----
     st = last_forward_stats(dev)
-    ev, bl = blend_pair_counts(ctx)
+    ev, bl, ev_ours, warp_iters = blend_pair_counts(ctx)
     gx, gy = (W + 15) // 16, (H + 15) // 16
     counts = dict(P=P, P_visible=st["num_visible"], R=st["num_rendered"], tiles=gx * gy, pairs_evaluated=ev,
-                  pairs_blended=bl, sum_n_contrib=int(ctx.array("n_contrib").long().sum().item()))
+                  pairs_blended=bl, pairs_evaluated_after_culling=ev_ours, warp_splat_iterations=warp_iters,
+                  sum_n_contrib=int(ctx.array("n_contrib").long().sum().item()))
     stage_ms = {k: v[0] / max(v[1], 1) for k, v in stages.items() if v[1]}
     peaks = load_peaks()
     roofs = stage_rooflines(stage_ms, counts, peaks, clocks)

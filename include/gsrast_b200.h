@@ -153,9 +153,11 @@ GSR_API int64_t gsr_launch_count(void);
 
 /* Instrumented re-run of the blend forward over the workspaces of a finished forward call (no
  * reference equivalent; SURVEY 8d "debug counters in a separate instrumented build, not the timed
- * one").  Writes two u64 to DEVICE memory: d_counters[0] = (pixel, splat) pairs the reference
+ * one").  Writes FOUR u64 to DEVICE memory: d_counters[0] = (pixel, splat) pairs the reference
  * algorithm evaluates (each pixel walks its tile list until it saturates), d_counters[1] = pairs
- * that are blended.  bench.py derives the blend kernels' algorithmic FLOPs from them. */
+ * that are blended, d_counters[2] = pairs THIS library's kernel evaluates after its two culling
+ * levels, d_counters[3] = (warp, splat) loop iterations it issues.  bench.py derives the blend
+ * kernels' algorithmic FLOPs from [0] and [1]. */
 GSR_API int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
                                   int64_t instance_capacity, void* image_ws, uint64_t* d_counters,
                                   void* stream);

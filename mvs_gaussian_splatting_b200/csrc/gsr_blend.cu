@@ -5,20 +5,23 @@
 // lanes of a warp are spatially compact.  Splats are staged through shared memory in batches of
 // 256 list entries.  B200-first differences from the reference algorithm, none of which changes
 // a result:
-//   * staging applies a CONSERVATIVE exact-ellipse-vs-tile test (minimum of the conic's quadratic
-//     form over the tile rectangle against ln(255*opacity)) and compacts the batch in order with a
-//     ballot, so entries that cannot reach alpha >= 1/255 anywhere in the tile are never evaluated
-//     per pixel.  Such entries are `continue`d by every pixel in the reference, so dropping them
-//     is exact; the original list position travels with each entry so n_contrib keeps its meaning.
-//   * the conic is pre-scaled by -log2(e)/2 at staging, so the per-pair exponent is 5 FP32 ops and
+//   * two-level exact culling.  Staging applies a CONSERVATIVE ellipse-vs-rectangle test (maximum of
+//     the conic's exponent over the rectangle against -log2(255*opacity)) for the TILE and compacts
+//     the batch in order with a ballot; then every WARP tests the compacted entries, 32 at a time
+//     (one per lane), against its own 8x4 pixel block and walks only the set bits of the ballot.
+//     Entries that cannot reach alpha >= 1/255 anywhere in the block are `continue`d by every one of
+//     its pixels in the reference, so dropping them is exact; the original list position travels
+//     with each entry so n_contrib keeps its meaning.  Small splats touch 1-3 of the 8 blocks of a
+//     tile, so most (warp, splat) iterations of the reference never issue.
+//   * the conic is pre-scaled by -log2(e)/2 at staging, so the per-pair exponent is 7 FP32 ops and
 //     one MUFU.EX2 (ex2.approx), not an expf() call.
-//   * a warp leaves the inner loop as soon as all 32 of its pixels are saturated (vote), the CTA
-//     leaves the batch loop when all 256 are.
+//   * a warp leaves the loop as soon as all 32 of its pixels are saturated (vote), the CTA leaves
+//     the batch loop when all 256 are.
 //   * backward: per-pair gradients are reduced across the warp with a 12-shuffle transposing
-//     butterfly (9 sums land in 9 different lanes), per-warp partials are combined through shared
-//     memory WITHOUT shared float atomics (those are CAS loops on sm_100), and each (tile, splat)
-//     issues three 128-bit vector reductions (REDG.E.ADD.F32x4) to L2 — versus 9 scalar global
-//     atomics per contributing (pixel, splat) pair in the reference.
+//     butterfly (9 sums land in 9 different lanes), parked in a per-warp shared buffer, and flushed
+//     once per 32 staged entries as 128-bit vector reductions (RED.E.ADD.F32x4) to L2: three per
+//     (8x4 block, splat) — versus 9 scalar global atomics per contributing (pixel, splat) pair in
+//     the reference.  No CTA-wide barrier inside the walk.
 #include "gsr_internal.cuh"
 
 namespace gsr {
@@ -31,39 +34,42 @@ constexpr float kTmin = 0.0001f;
 constexpr int kBlendThreads = 256;
 constexpr int kBlendWarps = 8;
 
-// Can the splat reach alpha >= 1/255 at some pixel centre of [rx0,rx1]x[ry0,ry1]?  Conservative:
-// false only when certainly not.  q(d) = (A dx^2 + C dy^2)/2 + B dx dy is convex; when the centre
-// is outside the rectangle its minimum over the rectangle lies on an edge facing the centre.
-__device__ __forceinline__ bool splat_may_touch(float x, float y, float A, float B, float C, float op,
-                                                float rx0, float ry0, float rx1, float ry1) {
-    const float o255 = op * 255.0f;
-    if (o255 < 1.0f) return false;  // alpha <= opacity < 1/255 everywhere
-    const bool in_x = (x >= rx0) && (x <= rx1), in_y = (y >= ry0) && (y <= ry1);
+struct Rect { float x0, y0, x1, y1; };
+
+// Can the splat reach alpha >= 1/255 at some pixel centre of the rectangle?  Conservative: false
+// only when certainly not.  Works on the pre-scaled conic: e(d) = a2 dx^2 + b2 dx dy + c2 dy^2 is
+// the base-2 exponent (concave, <= 0), alpha = op * 2^e, so the question is whether max e over the
+// rectangle reaches -tau2 with tau2 = log2(255 * op).  When the centre is outside the rectangle the
+// maximum lies on an edge facing the centre.
+__device__ __forceinline__ bool splat_may_reach(float x, float y, float a2, float b2, float c2, float tau2,
+                                                const Rect& r) {
+    const bool in_x = (x >= r.x0) && (x <= r.x1), in_y = (y >= r.y0) && (y <= r.y1);
     if (in_x && in_y) return true;
-    if (!(A > 0.0f) || !(C > 0.0f)) return true;  // not a proper conic: leave it to the pixels
-    const float tau = __logf(o255);
-    const float dxe = fminf(fmaxf(x, rx0), rx1) - x, dye = fminf(fmaxf(y, ry0), ry1) - y;
-    float qmin = 3.0e38f;
+    if (!(a2 < 0.0f) || !(c2 < 0.0f)) return true;  // not a proper conic: leave it to the pixels
+    const float dxe = fminf(fmaxf(x, r.x0), r.x1) - x, dye = fminf(fmaxf(y, r.y0), r.y1) - y;
+    float emax = -3.0e38f;
     if (!in_x) {
-        const float py = fminf(fmaxf(y - __fdividef(B * dxe, C), ry0), ry1);
+        const float py = fminf(fmaxf(y - __fdividef(0.5f * b2 * dxe, c2), r.y0), r.y1);
         const float dy = py - y;
-        qmin = 0.5f * (A * dxe * dxe + C * dy * dy) + B * dxe * dy;
+        emax = a2 * dxe * dxe + c2 * dy * dy + b2 * dxe * dy;
     }
     if (!in_y) {
-        const float px = fminf(fmaxf(x - __fdividef(B * dye, A), rx0), rx1);
+        const float px = fminf(fmaxf(x - __fdividef(0.5f * b2 * dye, a2), r.x0), r.x1);
         const float dx = px - x;
-        qmin = fminf(qmin, 0.5f * (A * dx * dx + C * dye * dye) + B * dx * dye);
+        emax = fmaxf(emax, a2 * dx * dx + c2 * dye * dye + b2 * dx * dye);
     }
-    const float dxm = fmaxf(fabsf(rx0 - x), fabsf(rx1 - x)), dym = fmaxf(fabsf(ry0 - y), fabsf(ry1 - y));
-    const float smax = 0.5f * (A * dxm * dxm + C * dym * dym) + fabsf(B) * dxm * dym;
-    return !(qmin > tau + 0.02f + 3.0e-6f * smax);  // NaN -> keep
+    const float dxm = fmaxf(fabsf(r.x0 - x), fabsf(r.x1 - x)), dym = fmaxf(fabsf(r.y0 - y), fabsf(r.y1 - y));
+    const float smax = fabsf(b2) * dxm * dym - a2 * dxm * dxm - c2 * dym * dym;
+    return !(emax < -(tau2 + 0.03f + 3.0e-6f * smax));  // NaN -> keep
 }
 
 struct TileCtx {
     int tile, tx, ty;
     int px, py;  // this thread's pixel
     bool inside;
-    float rx0, ry0, rx1, ry1;
+    Rect tile_rect;  // pixel centres of the tile, clipped to the image
+    Rect warp_rect;  // pixel centres of this warp's 8x4 block, clipped to the image
+    bool warp_inside;  // the block has at least one pixel inside the image
 };
 
 __device__ __forceinline__ TileCtx tile_ctx(int gx, int W, int H) {
@@ -72,13 +78,19 @@ __device__ __forceinline__ TileCtx tile_ctx(int gx, int W, int H) {
     c.ty = c.tile / gx;
     c.tx = c.tile - c.ty * gx;
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    c.px = c.tx * kTile + (w & 1) * 8 + (l & 7);
-    c.py = c.ty * kTile + (w >> 1) * 4 + (l >> 3);
+    const int bx = c.tx * kTile + (w & 1) * 8, by = c.ty * kTile + (w >> 1) * 4;
+    c.px = bx + (l & 7);
+    c.py = by + (l >> 3);
     c.inside = c.px < W && c.py < H;
-    c.rx0 = (float)(c.tx * kTile);
-    c.ry0 = (float)(c.ty * kTile);
-    c.rx1 = (float)min(c.tx * kTile + kTile - 1, W - 1);
-    c.ry1 = (float)min(c.ty * kTile + kTile - 1, H - 1);
+    c.tile_rect.x0 = (float)(c.tx * kTile);
+    c.tile_rect.y0 = (float)(c.ty * kTile);
+    c.tile_rect.x1 = (float)min(c.tx * kTile + kTile - 1, W - 1);
+    c.tile_rect.y1 = (float)min(c.ty * kTile + kTile - 1, H - 1);
+    c.warp_inside = bx < W && by < H;
+    c.warp_rect.x0 = (float)bx;
+    c.warp_rect.y0 = (float)by;
+    c.warp_rect.x1 = (float)min(bx + 7, W - 1);
+    c.warp_rect.y1 = (float)min(by + 3, H - 1);
     return c;
 }
 
@@ -99,29 +111,43 @@ __device__ __forceinline__ int compact_slot(bool keep, int* s_wcount, int& total
     return off + __popc(bal & ((1u << lane_id()) - 1u));
 }
 
+// Tile-level staging test of one list entry; on keep, returns the pre-scaled conic and tau2.
+__device__ __forceinline__ bool stage_test(float2 m, float4 co, const Rect& tile_rect, float& a2, float& b2,
+                                           float& c2, float& tau2) {
+    const float o255 = co.w * 255.0f;
+    a2 = -0.5f * kLog2e * co.x;
+    b2 = -kLog2e * co.y;
+    c2 = -0.5f * kLog2e * co.z;
+    tau2 = __log2f(o255);
+    if (o255 < 1.0f) return false;  // alpha <= opacity < 1/255 everywhere
+    return splat_may_reach(m.x, m.y, a2, b2, c2, tau2, tile_rect);
+}
+
 // ------------------------------------ forward ----------------------------------------------
 // kCount = true is the INSTRUMENTED variant (gsr_blend_pair_counts): same decisions, no image
-// outputs, counts the (pixel, splat) pairs the reference algorithm evaluates and blends.
+// outputs, counts the (pixel, splat) pairs the reference algorithm evaluates and blends, plus the
+// pairs this kernel actually evaluates after both culling levels.
 template <bool kCount>
 __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
     int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, float* __restrict__ out_color, float* __restrict__ final_T,
     uint32_t* __restrict__ n_contrib, unsigned long long* __restrict__ counters) {
-    __shared__ float4 s_g[kBlendThreads];    // x, y, a2, b2
-    __shared__ float2 s_c[kBlendThreads];    // c2, opacity
-    __shared__ float4 s_col[kBlendThreads];  // r, g, b, list position (1-based, int bits)
+    __shared__ float4 s_a[kBlendThreads];    // x, y, a2, b2
+    __shared__ float4 s_b[kBlendThreads];    // c2, opacity, tau2, list position (1-based, int bits)
+    __shared__ float4 s_col[kBlendThreads];  // r, g, b, -
     __shared__ int s_wcount[kBlendWarps];
 
     const TileCtx c = tile_ctx(gx, W, H);
     const uint2 range = ranges[c.tile];
     const int n = (int)(range.y - range.x);
     const float fx = (float)c.px, fy = (float)c.py;
+    const unsigned lane = lane_id();
 
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
     uint32_t last = 0;
     bool done = !c.inside;
-    uint32_t n_blended = 0, stop_pos = 0;  // kCount only
+    uint32_t n_blended = 0, stop_pos = 0, n_eval = 0, n_iter = 0;  // kCount only
 
     for (int base = 0; base < n; base += kBlendThreads) {
         if (__syncthreads_count(done) == kBlendThreads) break;
@@ -129,60 +155,77 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
         bool keep = false;
         uint32_t gid = 0;
         float2 m = make_float2(0.f, 0.f);
-        float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+        float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
         if (p < n) {
             gid = __ldg(point_list + range.x + p);
             m = __ldg(means2D + gid);
-            co = __ldg(conic_opacity + gid);
-            keep = splat_may_touch(m.x, m.y, co.x, co.y, co.z, co.w, c.rx0, c.ry0, c.rx1, c.ry1);
+            const float4 co = __ldg(conic_opacity + gid);
+            op = co.w;
+            keep = stage_test(m, co, c.tile_rect, a2, b2, c2, tau2);
         }
         int total;
         const int slot = compact_slot(keep, s_wcount, total);
         if (keep) {
             const float4 col = __ldg(rgb + gid);
-            s_g[slot] = make_float4(m.x, m.y, -0.5f * kLog2e * co.x, -kLog2e * co.y);
-            s_c[slot] = make_float2(-0.5f * kLog2e * co.z, co.w);
-            s_col[slot] = make_float4(col.x, col.y, col.z, __int_as_float(p + 1));
+            s_a[slot] = make_float4(m.x, m.y, a2, b2);
+            s_b[slot] = make_float4(c2, op, tau2, __int_as_float(p + 1));
+            s_col[slot] = col;
         }
         __syncthreads();
 
-        for (int j = 0; j < total; ++j) {
+        for (int cb = 0; cb < total; cb += 32) {
             if (__all_sync(0xffffffffu, done)) break;
-            const float4 g = s_g[j];
-            const float2 cc = s_c[j];
-            const float dx = g.x - fx, dy = g.y - fy;
-            const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
-            const float alpha = fminf(0.99f, cc.y * ex2_approx(pw));
-            if (done || pw > 0.0f || alpha < kAlphaMin) continue;
-            const float test_T = T * (1.0f - alpha);
-            if (test_T < kTmin) {
-                done = true;
-                if (kCount) stop_pos = (uint32_t)__float_as_int(s_col[j].w);
-                continue;
+            const int jt = cb + (int)lane;
+            bool hit = false;
+            if (jt < total) {
+                const float4 ta = s_a[jt];
+                const float4 tb = s_b[jt];
+                hit = splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
             }
-            if (kCount) ++n_blended;
-            const float4 col = s_col[j];
-            const float wgt = alpha * T;
-            C0 = fmaf(col.x, wgt, C0);
-            C1 = fmaf(col.y, wgt, C1);
-            C2 = fmaf(col.z, wgt, C2);
-            T = test_T;
-            last = (uint32_t)__float_as_int(col.w);
+            unsigned mask = __ballot_sync(0xffffffffu, hit);
+            while (mask) {
+                const int j = cb + __ffs(mask) - 1;
+                mask &= mask - 1;
+                const float4 g = s_a[j];
+                const float4 cc = s_b[j];
+                const float dx = g.x - fx, dy = g.y - fy;
+                const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
+                const float alpha = fminf(0.99f, cc.y * ex2_approx(pw));
+                if (kCount) { if (!done) ++n_eval; ++n_iter; }
+                if (done || pw > 0.0f || alpha < kAlphaMin) continue;
+                const float test_T = T * (1.0f - alpha);
+                if (test_T < kTmin) {
+                    done = true;
+                    if (kCount) stop_pos = (uint32_t)__float_as_int(cc.w);
+                    continue;
+                }
+                if (kCount) ++n_blended;
+                const float4 col = s_col[j];
+                const float wgt = alpha * T;
+                C0 = fmaf(col.x, wgt, C0);
+                C1 = fmaf(col.y, wgt, C1);
+                C2 = fmaf(col.z, wgt, C2);
+                T = test_T;
+                last = (uint32_t)__float_as_int(cc.w);
+            }
         }
     }
 
     if (kCount) {
         // the reference walks its tile list until the pixel is done: stop position, else all n
         unsigned long long ev = c.inside ? (stop_pos ? stop_pos : (uint32_t)n) : 0u;
-        unsigned long long bl = n_blended;
+        unsigned long long bl = n_blended, ne = n_eval;
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) {
             ev += __shfl_xor_sync(0xffffffffu, ev, d);
             bl += __shfl_xor_sync(0xffffffffu, bl, d);
+            ne += __shfl_xor_sync(0xffffffffu, ne, d);
         }
-        if (lane_id() == 0) {
+        if (lane == 0) {
             atomicAdd(counters, ev);
             atomicAdd(counters + 1, bl);
+            atomicAdd(counters + 2, ne);
+            atomicAdd(counters + 3, (unsigned long long)n_iter);  // (warp, splat) iterations issued
         }
         return;
     }
@@ -244,17 +287,16 @@ __device__ __forceinline__ float warp_reduce9(const float* v, unsigned lane) {
     return r;
 }
 
-constexpr int kSub = 32;  // splats per flush group
-
 __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
     int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, float* __restrict__ grad_accum) {
-    __shared__ float4 s_g[kBlendThreads];    // x, y, a2, b2
-    __shared__ float4 s_c[kBlendThreads];    // c2, opacity, list position (1-based), gaussian id
-    __shared__ float4 s_col[kBlendThreads];  // r, g, b, -
-    __shared__ __align__(16) float s_part[kBlendWarps][kSub][12];
+    __shared__ float4 s_a[kBlendThreads];    // x, y, a2, b2
+    __shared__ float4 s_b[kBlendThreads];    // c2, opacity, tau2, list position (1-based, int bits)
+    __shared__ float4 s_col[kBlendThreads];  // r, g, b, gaussian id (uint bits)
+    __shared__ __align__(16) float s_part[kBlendWarps][32][12];  // per-warp parked sums of one 32-entry chunk
+    __shared__ uint32_t s_gid[kBlendWarps][32];
     __shared__ int s_wcount[kBlendWarps];
     __shared__ uint32_t s_wmax[kBlendWarps];
 
@@ -278,7 +320,7 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
     }
     const float bgdot = __ldg(bg) * g0 + __ldg(bg + 1) * g1 + __ldg(bg + 2) * g2;
 
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);  // nothing behind this matters to the warp
     if (lane == 0) s_wmax[warp] = wmax;
     __syncthreads();
     uint32_t m = 0;
@@ -294,39 +336,52 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
         bool keep = false;
         uint32_t gid = 0;
         float2 mm = make_float2(0.f, 0.f);
-        float4 co = make_float4(0.f, 0.f, 0.f, 0.f);
+        float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
         if (p >= 0) {
             gid = __ldg(point_list + range.x + p);
             mm = __ldg(means2D + gid);
-            co = __ldg(conic_opacity + gid);
-            keep = splat_may_touch(mm.x, mm.y, co.x, co.y, co.z, co.w, c.rx0, c.ry0, c.rx1, c.ry1);
+            const float4 co = __ldg(conic_opacity + gid);
+            op = co.w;
+            keep = stage_test(mm, co, c.tile_rect, a2, b2, c2, tau2);
         }
         int total;
         const int slot = compact_slot(keep, s_wcount, total);
         if (keep) {
             const float4 col = __ldg(rgb + gid);
-            s_g[slot] = make_float4(mm.x, mm.y, -0.5f * kLog2e * co.x, -kLog2e * co.y);
-            s_c[slot] = make_float4(-0.5f * kLog2e * co.z, co.w, __int_as_float(p + 1), __uint_as_float(gid));
-            s_col[slot] = col;
+            s_a[slot] = make_float4(mm.x, mm.y, a2, b2);
+            s_b[slot] = make_float4(c2, op, tau2, __int_as_float(p + 1));
+            s_col[slot] = make_float4(col.x, col.y, col.z, __uint_as_float(gid));
         }
         __syncthreads();
+        if (wmax == 0) continue;  // warp-uniform: block outside the image or nothing blended
 
-        for (int sb = 0; sb < total; sb += kSub) {
-            const int nsub = min(kSub, total - sb);
-            for (int jj = 0; jj < nsub; ++jj) {
-                const int j = sb + jj;
-                const float4 g = s_g[j];
-                const float4 cc = s_c[j];
+        for (int cb = 0; cb < total; cb += 32) {
+            const int jt = cb + (int)lane;
+            bool hit = false;
+            if (jt < total) {
+                const float4 ta = s_a[jt];
+                const float4 tb = s_b[jt];
+                hit = ((uint32_t)__float_as_int(tb.w) <= wmax) &&
+                      splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
+            }
+            unsigned mask = __ballot_sync(0xffffffffu, hit);
+            int nh = 0;  // parked entries of this chunk (warp-uniform)
+            while (mask) {
+                const int j = cb + __ffs(mask) - 1;
+                mask &= mask - 1;
+                const float4 g = s_a[j];
+                const float4 cc = s_b[j];
                 const float dx = g.x - fx, dy = g.y - fy;
                 const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
                 const float G = ex2_approx(pw);
                 const float alpha = fminf(0.99f, cc.y * G);
-                const bool ok = ((uint32_t)__float_as_int(cc.z) <= last) && !(pw > 0.0f) && !(alpha < kAlphaMin);
+                const bool ok = ((uint32_t)__float_as_int(cc.w) <= last) && !(pw > 0.0f) && !(alpha < kAlphaMin);
+                if (!__any_sync(0xffffffffu, ok)) continue;
+                const float4 col = s_col[j];
                 float v[9];
 #pragma unroll
                 for (int k = 0; k < 9; ++k) v[k] = 0.0f;
                 if (ok) {
-                    const float4 col = s_col[j];
                     const float ra = rcp_approx(1.0f - alpha);
                     T *= ra;
                     const float wgt = alpha * T;
@@ -344,29 +399,20 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
                     v[5] = G * dL_dalpha;
                     v[6] = wgt * g0; v[7] = wgt * g1; v[8] = wgt * g2;
                 }
-                if (__any_sync(0xffffffffu, ok)) {
-                    const float r = warp_reduce9(v, lane);
-                    if (my_slot >= 0) s_part[warp][jj][my_slot] = r;
-                } else if (lane < 12) {
-                    s_part[warp][jj][lane] = 0.0f;
-                }
+                const float r = warp_reduce9(v, lane);
+                if (my_slot >= 0) s_part[warp][nh][my_slot] = r;
+                if (lane == 0) s_gid[warp][nh] = __float_as_uint(col.w);
+                ++nh;
             }
-            __syncthreads();
-            // flush: one thread per (splat, float4 quad)
-            if ((int)threadIdx.x < nsub * 3) {
-                const int jj = threadIdx.x / 3, quad = threadIdx.x - jj * 3;
-                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int w = 0; w < kBlendWarps; ++w) {
-                    const float4 pv = *reinterpret_cast<const float4*>(&s_part[w][jj][quad * 4]);
-                    acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
-                }
-                if (acc.x != 0.f || acc.y != 0.f || acc.z != 0.f || acc.w != 0.f) {
-                    const uint32_t gid2 = __float_as_uint(s_c[sb + jj].w);
-                    atomicAdd(reinterpret_cast<float4*>(grad_accum + (size_t)gid2 * 12 + quad * 4), acc);
-                }
+            __syncwarp();
+            // flush: one lane per (parked entry, float4 quad)
+            for (int t = (int)lane; t < nh * 3; t += 32) {
+                const int e = t / 3, quad = t - e * 3;
+                const float4 acc = *reinterpret_cast<const float4*>(&s_part[warp][e][quad * 4]);
+                if (acc.x != 0.f || acc.y != 0.f || acc.z != 0.f || acc.w != 0.f)
+                    atomicAdd(reinterpret_cast<float4*>(grad_accum + (size_t)s_gid[warp][e] * 12 + quad * 4), acc);
             }
-            __syncthreads();
+            __syncwarp();
         }
     }
 }
@@ -385,7 +431,7 @@ int launch_blend_forward(const Grid& g, const float* bg, GeomView gv, BinView bv
 
 int launch_blend_pair_counts(const Grid& g, GeomView gv, BinView bv, ImageView iv, unsigned long long* counters,
                              cudaStream_t s) {
-    GSR_CUDA(cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned long long), s));
+    GSR_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), s));
     blend_forward_kernel<true><<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list,
                                                                  gv.means2D, gv.conic_opacity, gv.rgb, nullptr, nullptr,
                                                                  nullptr, nullptr, counters);

@@ -289,16 +289,16 @@ def rasterize_backward(ctx: RasterContext, ctx_inputs, raster_settings: Gaussian
 
 def blend_pair_counts(ctx: RasterContext):
     """(evaluated, blended) (pixel, splat) pair counts of the reference algorithm for a finished
-    forward (instrumented kernel; benchmarks only).  Synchronises."""
+    forward, then the pairs this library evaluates after culling and its (warp, splat) iterations
+    (instrumented kernel; benchmarks only).  Synchronises."""
     device = ctx.geom_ws.device
-    out = torch.zeros(2, dtype=torch.int64, device=device)
+    out = torch.zeros(4, dtype=torch.int64, device=device)
     with torch.cuda.device(device):
         stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
         _native.check(_native.lib().gsr_blend_pair_counts(
             ctx.P, ctx.W, ctx.H, _ptr(ctx.geom_ws), _ptr(ctx.binning_ws), ctx.capacity, _ptr(ctx.image_ws),
             _ptr(out), stream), "gsr_blend_pair_counts")
-    ev, bl = out.cpu().tolist()
-    return int(ev), int(bl)
+    return tuple(int(v) for v in out.cpu().tolist())
 
 
 def mark_visible(positions: torch.Tensor, raster_settings: GaussianRasterizationSettings) -> torch.Tensor:
