@@ -222,9 +222,11 @@ def stage_rooflines(stage_ms, counts, peaks, clocks):
     keybits = 32 + max(1, math.ceil(math.log2(max(tiles, 2))))
     hbm = {
         "preprocess": 52.0 * P + 259.0 * Pv,
-        "scan": 8.0 * P,
+        "depth_sort": 68.0 * P,          # one histogram read + 4 passes x (8 B read + 8 B write)
+        "scan": 12.0 * P,                # order + gathered tiles_touched read, offsets written
         "emit_keys": 12.0 * R + 24.0 * Pv,
-        "radix_sort": (24.0 * math.ceil(keybits / 8) + 8.0) * R,
+        # tile-bit sort only (the depth order comes from depth_sort): histogram read + passes x (12 r + 12 w)
+        "radix_sort": (8.0 + 24.0 * math.ceil((keybits - 32) / 8)) * R,
         "tile_ranges": 8.0 * R + 8.0 * tiles,
         "preprocess_backward": 303.0 * Pv + 240.0 * P,
     }

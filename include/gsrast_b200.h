@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 1
+#define GSR_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define GSR_API __attribute__((visibility("default")))
@@ -66,24 +66,28 @@ typedef struct gsr_forward_info {
  * layout is otherwise private).  Obtained from gsr_workspace_layout(). */
 typedef struct gsr_layout {
     /* geometry workspace, per Gaussian */
-    size_t g_depths;        /* f32[P]   view-space z                                           */
+    size_t g_depths;        /* f32[P]   view-space z; culled Gaussians hold the bits 0xFFFFFFFF  */
     size_t g_means2D;       /* f32[P,2] pixel centre                                           */
     size_t g_conic_opacity; /* f32[P,4] conic A,B,C + opacity                                  */
     size_t g_rgb;           /* f32[P,4] r,g,b + clamped bits (as u32 in .w, bit c = channel c) */
     size_t g_tiles_touched; /* u32[P]                                                          */
-    size_t g_point_offsets; /* u32[P]   inclusive prefix sum of tiles_touched                  */
+    size_t g_point_offsets; /* u32[P]   inclusive prefix sum of tiles_touched in DEPTH order     */
     size_t g_info;          /* gsr_forward_info (device copy)                                  */
     size_t g_grad_accum;    /* f32[P,12] backward blend accumulators                           */
-    size_t g_scan_tmp;      /* u32[...] scan block sums                                        */
+    size_t g_order_keys;    /* u32[P]   depth bits ascending (stable), culled (0xFFFFFFFF) last  */
+    size_t g_order;         /* u32[P]   Gaussian index of depth-order slot k                     */
+    size_t g_order_keys_alt;/* u32[P]   sort ping-pong                                           */
+    size_t g_order_alt;     /* u32[P]                                                            */
+    size_t g_sort_ctl;      /* u32[...] histograms, tickets, look-back status                    */
     size_t geom_bytes;
     /* binning workspace, per tile instance (capacity entries each) */
-    size_t b_keys_unsorted; /* u64[C]  (tile << 32) | depth bits                               */
+    size_t b_keys_unsorted; /* u64[C]  (tile << 32) | depth bits, emitted in DEPTH order         */
     size_t b_vals_unsorted; /* u32[C]  Gaussian index                                          */
     size_t b_keys;          /* u64[C]  sorted                                                  */
     size_t b_point_list;    /* u32[C]  sorted                                                  */
     size_t b_keys_alt;      /* u64[C]  radix-sort ping-pong buffer                             */
     size_t b_vals_alt;      /* u32[C]                                                          */
-    size_t b_sort_tmp;      /* radix-sort histograms                                           */
+    size_t b_sort_ctl;      /* u32[...] histograms, tickets, look-back status                    */
     size_t binning_bytes;
     /* image workspace */
     size_t i_ranges;        /* u32[tiles,2] [start,end) into point_list                        */

@@ -16,7 +16,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -41,9 +41,10 @@ class ForwardInfo(ctypes.Structure):
 class Layout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_size_t) for n in (
         "g_depths", "g_means2D", "g_conic_opacity", "g_rgb", "g_tiles_touched", "g_point_offsets",
-        "g_info", "g_grad_accum", "g_scan_tmp", "geom_bytes",
+        "g_info", "g_grad_accum", "g_order_keys", "g_order", "g_order_keys_alt", "g_order_alt", "g_sort_ctl",
+        "geom_bytes",
         "b_keys_unsorted", "b_vals_unsorted", "b_keys", "b_point_list", "b_keys_alt", "b_vals_alt",
-        "b_sort_tmp", "binning_bytes",
+        "b_sort_ctl", "binning_bytes",
         "i_ranges", "i_final_T", "i_n_contrib", "image_bytes")]
 
 

@@ -66,7 +66,11 @@ void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
     L->g_point_offsets = take(4 * p);
     L->g_info = take(sizeof(gsr_forward_info));
     L->g_grad_accum = take(48 * p);
-    L->g_scan_tmp = take(4 * scan_tmp_entries(p));
+    L->g_order_keys = take(4 * p);
+    L->g_order = take(4 * p);
+    L->g_order_keys_alt = take(4 * p);
+    L->g_order_alt = take(4 * p);
+    L->g_sort_ctl = take(4 * depth_sort_ctl_entries(p));
     L->geom_bytes = o;
     o = 0;
     L->b_keys_unsorted = take(8 * c);
@@ -75,7 +79,7 @@ void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
     L->b_point_list = take(4 * c);
     L->b_keys_alt = take(8 * c);
     L->b_vals_alt = take(4 * c);
-    L->b_sort_tmp = take(4 * sort_tmp_entries(c));
+    L->b_sort_ctl = take(4 * tile_sort_ctl_entries(c));
     L->binning_bytes = o;
     o = 0;
     L->i_ranges = take(8 * (size_t)g.tiles);
@@ -97,7 +101,11 @@ GeomView geom_view(void* ws, const gsr_layout& L) {
     v.point_offsets = at<uint32_t>(ws, L.g_point_offsets);
     v.info = at<gsr_forward_info>(ws, L.g_info);
     v.grad_accum = at<float>(ws, L.g_grad_accum);
-    v.scan_tmp = at<uint32_t>(ws, L.g_scan_tmp);
+    v.order_keys = at<uint32_t>(ws, L.g_order_keys);
+    v.order = at<uint32_t>(ws, L.g_order);
+    v.order_keys_alt = at<uint32_t>(ws, L.g_order_keys_alt);
+    v.order_alt = at<uint32_t>(ws, L.g_order_alt);
+    v.sort_ctl = at<uint32_t>(ws, L.g_sort_ctl);
     return v;
 }
 BinView bin_view(void* ws, const gsr_layout& L) {
@@ -108,7 +116,7 @@ BinView bin_view(void* ws, const gsr_layout& L) {
     v.point_list = at<uint32_t>(ws, L.b_point_list);
     v.keys_alt = at<uint64_t>(ws, L.b_keys_alt);
     v.vals_alt = at<uint32_t>(ws, L.b_vals_alt);
-    v.sort_tmp = at<uint32_t>(ws, L.b_sort_tmp);
+    v.sort_ctl = at<uint32_t>(ws, L.b_sort_ctl);
     return v;
 }
 ImageView image_view(void* ws, const gsr_layout& L) {
@@ -123,7 +131,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 static int check_dims(int P, int W, int H, int64_t cap) {
     if (P < 0 || W <= 0 || H <= 0 || cap < 0) return GSR_ERR_INVALID_ARGUMENT;
-    if (cap > 0xFFFFFFFFll) return GSR_ERR_UNSUPPORTED;
+    if (cap >= (1ll << 30) || P >= (1 << 30)) return GSR_ERR_UNSUPPORTED;  // 30-bit look-back counts
     const Grid g = make_grid(W, H);
     if ((int64_t)g.gx * g.gy > (1ll << 30)) return GSR_ERR_UNSUPPORTED;
     return GSR_OK;
@@ -157,7 +165,7 @@ int64_t gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxe
 int gsr_stage_count(void) { return kStageCount; }
 
 const char* gsr_stage_name(int stage) {
-    static const char* names[kStageCount] = {"preprocess", "scan", "emit_keys", "radix_sort", "tile_ranges",
+    static const char* names[kStageCount] = {"preprocess", "depth_sort", "scan", "emit_keys", "radix_sort", "tile_ranges",
                                              "blend_forward", "blend_backward", "preprocess_backward"};
     return (stage >= 0 && stage < kStageCount) ? names[stage] : "";
 }
@@ -237,10 +245,8 @@ int gsr_forward_geometry(int P, int D, int M, int width, int height, const float
                                rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii,
                                gv, s, debug);
         if (st != GSR_OK) return st;
-        st = launch_inclusive_scan(gv.tiles_touched, gv.point_offsets, (size_t)P, gv.scan_tmp, s, debug);
+        st = launch_depth_order(P, gv, s, debug);
         if (st != GSR_OK) return st;
-        GSR_CUDA(cudaMemcpyAsync(&gv.info->num_rendered, gv.point_offsets + (P - 1), sizeof(int32_t),
-                                 cudaMemcpyDeviceToDevice, s));
     }
     if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));
     return GSR_OK;

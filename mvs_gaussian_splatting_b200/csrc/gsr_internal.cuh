@@ -40,7 +40,7 @@ int cuda_fail(cudaError_t e);  // records e for gsr_last_cuda_error(), returns G
 
 // ---- optional per-stage device timing (gsr_stage_timing_*; off by default) -----------------
 enum Stage {
-    kStagePreprocess = 0, kStageScan, kStageEmitKeys, kStageSort, kStageTileRanges, kStageBlendFwd,
+    kStagePreprocess = 0, kStageDepthSort, kStageScan, kStageEmitKeys, kStageSort, kStageTileRanges, kStageBlendFwd,
     kStageBlendBwd, kStagePreprocessBwd, kStageCount
 };
 bool stage_timing_on();
@@ -75,10 +75,14 @@ struct GeomView {
     float4* conic_opacity;
     float4* rgb;  // .w carries the clamped bits
     uint32_t* tiles_touched;
-    uint32_t* point_offsets;
+    uint32_t* point_offsets;   // inclusive prefix of tiles_touched in DEPTH order (slot k of `order`)
     gsr_forward_info* info;
     float* grad_accum;  // [P,12]
-    uint32_t* scan_tmp;
+    uint32_t* order_keys;      // [P] depth bits, ascending; culled Gaussians (0xFFFFFFFF) last
+    uint32_t* order;           // [P] Gaussian index of slot k
+    uint32_t* order_keys_alt;  // ping-pong partners of the per-Gaussian sort
+    uint32_t* order_alt;
+    uint32_t* sort_ctl;        // histograms, tickets, look-back status words
 };
 struct BinView {
     uint64_t* keys_unsorted;
@@ -87,7 +91,7 @@ struct BinView {
     uint32_t* point_list;
     uint64_t* keys_alt;   // radix-sort ping-pong partner of (keys, point_list)
     uint32_t* vals_alt;
-    uint32_t* sort_tmp;
+    uint32_t* sort_ctl;   // histograms, tickets, look-back status words
 };
 struct ImageView {
     uint2* ranges;
@@ -99,10 +103,10 @@ GeomView geom_view(void* ws, const gsr_layout& L);
 BinView bin_view(void* ws, const gsr_layout& L);
 ImageView image_view(void* ws, const gsr_layout& L);
 
-// Number of u32 entries the generic scan needs as scratch for n elements.
-size_t scan_tmp_entries(size_t n);
-// Number of u32 entries the radix sort needs as scratch for `cap` elements.
-size_t sort_tmp_entries(size_t cap);
+// u32 entries of the control regions of the per-Gaussian depth sort (+ prefix sum) and of the
+// per-instance tile sort.
+size_t depth_sort_ctl_entries(size_t P);
+size_t tile_sort_ctl_entries(size_t cap);
 
 // ---- stage launchers (each returns a gsr_status) ------------------------------------------
 int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
@@ -111,9 +115,9 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
                       const float* view, const float* proj, const float* campos, float tanfovx,
                       float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug);
 
-// Inclusive prefix sum of u32 (n elements); optionally stores the grand total to *total.
-int launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp,
-                          cudaStream_t s, int debug);
+// Depth-order sort of the P (depth bits, index) pairs + prefix sum of tiles_touched in that order;
+// writes info->num_rendered on the device.
+int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug);
 
 int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinView bv,
                    int64_t cap, ImageView iv, cudaStream_t s, int debug);

@@ -265,8 +265,9 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
     if (idx < p.P) {
         p.radii[idx] = alive ? rad : 0;
         p.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
+        // the depth array doubles as the key of the per-Gaussian depth sort: culled rows sink to the end
+        p.gv.depths[idx] = alive ? depth : __uint_as_float(0xFFFFFFFFu);
         if (alive) {
-            p.gv.depths[idx] = depth;
             p.gv.means2D[idx] = make_float2(px, py);
             p.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
                                                   __fmul_rn(ca, det_inv), __ldg(p.opacities + idx));

@@ -119,6 +119,8 @@ class RasterContext:
             "tiles_touched": (self.geom_ws, L.g_tiles_touched, torch.int32, (P,)),
             "point_offsets": (self.geom_ws, L.g_point_offsets, torch.int32, (P,)),
             "grad_accum": (self.geom_ws, L.g_grad_accum, torch.float32, (P, 12)),
+            "order_keys": (self.geom_ws, L.g_order_keys, torch.int32, (P,)),
+            "order": (self.geom_ws, L.g_order, torch.int32, (P,)),
             "keys_unsorted": (self.binning_ws, L.b_keys_unsorted, torch.int64, (C,)),
             "values_unsorted": (self.binning_ws, L.b_vals_unsorted, torch.int32, (C,)),
             "keys": (self.binning_ws, L.b_keys, torch.int64, (C,)),

@@ -81,3 +81,16 @@ def grad_report(a, b64, o32, rel=REL_TOL):
     ok = (rep["rel_l1"] <= rel and rep["frac"] <= 2 * rep["frac_fp32_oracle"] + 1e-3
           and rep["worst"] <= 5 * rep["worst_fp32_oracle"] + rel)
     return ok, rep
+
+
+def depth_order_emission(pre, binned):
+    """The oracle's unsorted (key, value) lists re-ordered block-wise into the emission order the
+    CUDA path documents: Gaussians by (depth bits, index), each Gaussian's tiles row-major."""
+    tt = pre["tiles_touched"].astype(np.int64)
+    ends = np.cumsum(tt)
+    starts = ends - tt
+    vis = pre["radii"] > 0
+    ids = np.flatnonzero(vis)
+    ids = ids[np.argsort(pre["depths"].view(np.uint32)[vis], kind="stable")]
+    idx = np.concatenate([np.arange(starts[i], ends[i]) for i in ids]) if len(ids) else np.zeros(0, np.int64)
+    return binned["keys_unsorted"][idx], binned["values_unsorted"][idx]

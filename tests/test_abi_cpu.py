@@ -40,7 +40,7 @@ def test_status_strings(native):
         assert L.gsr_status_string(code)
     assert L.gsr_last_cuda_error() == b""
     names = [L.gsr_stage_name(i).decode() for i in range(L.gsr_stage_count())]
-    assert names == ["preprocess", "scan", "emit_keys", "radix_sort", "tile_ranges", "blend_forward",
+    assert names == ["preprocess", "depth_sort", "scan", "emit_keys", "radix_sort", "tile_ranges", "blend_forward",
                      "blend_backward", "preprocess_backward"]
 
 
@@ -56,7 +56,7 @@ def test_workspace_sizes_and_layout(native):
     tiles = 50 * 50
     assert i >= 8 * tiles + 8 * W * H
     offs = [L.g_depths, L.g_means2D, L.g_conic_opacity, L.g_rgb, L.g_tiles_touched, L.g_point_offsets, L.g_info,
-            L.g_grad_accum, L.g_scan_tmp]
+            L.g_grad_accum, L.g_order_keys, L.g_order, L.g_order_keys_alt, L.g_order_alt, L.g_sort_ctl]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs)
     # the geometry and image layouts do not depend on the instance capacity
     L0 = native.workspace_layout(P, W, H, 0)

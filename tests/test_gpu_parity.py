@@ -69,8 +69,17 @@ def test_forward_bit_exact_lists_and_image(cuda, oracle, P, W, H, D, M, seed):
     R = binned["num_rendered"]
     assert ctx.num_rendered == R
     if R:
-        np.testing.assert_array_equal(ctx.array("keys_unsorted").cpu().numpy().view(np.uint64)[:R], binned["keys_unsorted"])
-        np.testing.assert_array_equal(ctx.array("values_unsorted").cpu().numpy().view(np.uint32)[:R], binned["values_unsorted"])
+        # the library emits instances in (depth bits, index) order of their Gaussians — a permutation
+        # of the reference's Gaussian-order emission made of the same per-Gaussian blocks
+        want_k, want_v = Hh.depth_order_emission(pre, binned)
+        np.testing.assert_array_equal(ctx.array("keys_unsorted").cpu().numpy().view(np.uint64)[:R], want_k)
+        np.testing.assert_array_equal(ctx.array("values_unsorted").cpu().numpy().view(np.uint32)[:R], want_v)
+        order = ctx.array("order").cpu().numpy().view(np.uint32)
+        nvis = int(vis.sum())
+        dbits = pre["depths"].view(np.uint32)
+        want_order = np.flatnonzero(vis)[np.argsort(dbits[vis], kind="stable")]
+        np.testing.assert_array_equal(order[:nvis], want_order)
+        np.testing.assert_array_equal(np.sort(order[nvis:]), np.flatnonzero(~vis))
         np.testing.assert_array_equal(ctx.array("keys").cpu().numpy().view(np.uint64)[:R], binned["keys"])
         np.testing.assert_array_equal(ctx.array("point_list").cpu().numpy().view(np.uint32)[:R], binned["point_list"])
     np.testing.assert_array_equal(ctx.array("ranges").cpu().numpy().view(np.uint32), binned["ranges"])
