@@ -12,7 +12,7 @@
 //   4. stable radix sort of the R instances on the TILE bits only (2 passes for <= 65536 tiles).
 // Every radix pass is ONE kernel: chunk histograms are chained with decoupled look-back (ticketed
 // chunks, 2 flag bits + 30 count bits per (chunk, digit) status word), keys are ranked per warp with
-// match.any, reordered through shared memory and written as coalesced per-digit runs.  Digit
+// one ballot per digit bit, reordered through shared memory and written as coalesced per-digit runs.  Digit
 // histograms of all passes of a sort come from one read of the keys.
 //
 // Everything is integer work bound by HBM / L2.  The instance count R lives on the DEVICE
@@ -74,8 +74,9 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp
 }
 
 // Effective instance count on the device: R if it fits the capacity, else 0 (overflow).
+// (R was written by an earlier kernel of the stream, so the read-only path is safe.)
 __device__ __forceinline__ uint32_t effective_n(const uint32_t* __restrict__ r_ptr, uint32_t cap) {
-    const uint32_t r = ld_relaxed(r_ptr);
+    const uint32_t r = __ldg(r_ptr);
     return r <= cap ? r : 0u;
 }
 
@@ -175,8 +176,8 @@ constexpr int kMaxPasses = 4;
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kValMask = (1u << 30) - 1u;
 
 // Digit histograms of ALL passes of one sort from a single read of the keys: hist[pass][digit].
-// Warp-aggregated (match.any) shared atomics, so constant digits (culled keys, high depth bytes)
-// do not serialise.
+// Shared atomics, with a vote so that warps whose digit is constant (culled keys, high depth bytes)
+// issue one add instead of 32 serialised ones.
 template <typename K>
 __global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ keys, const uint32_t* __restrict__ n_ptr,
                                                           uint32_t n_host, uint32_t cap, int shift0, int bits,
@@ -187,16 +188,21 @@ __global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ 
     const uint32_t n = n_ptr ? effective_n(n_ptr, cap) : n_host;
     const uint32_t mask = (1u << bits) - 1u;
     const unsigned lane = lane_id();
-    // whole warps iterate together (match.any needs converged lanes): round n up to a warp multiple
+    // whole warps iterate together (the uniformity vote needs converged lanes): round n up to a warp multiple
     const size_t stride = (size_t)gridDim.x * kBlk;
     const size_t n_up = ((size_t)n + 31) & ~(size_t)31;
     for (size_t i = (size_t)blockIdx.x * kBlk + threadIdx.x; i < n_up; i += stride) {
         const bool valid = i < n;
         const K key = valid ? keys[i] : (K)0;
+        const bool full = __all_sync(0xffffffffu, valid);
         for (int p = 0; p < npass; ++p) {
-            const uint32_t d = valid ? ((uint32_t)(key >> (shift0 + p * bits)) & mask) : 0xffffffffu;
-            const unsigned peers = __match_any_sync(0xffffffffu, d);
-            if (valid && (peers & ((1u << lane) - 1u)) == 0) atomicAdd(&s_h[p][d], (uint32_t)__popc(peers));
+            const uint32_t d = (uint32_t)(key >> (shift0 + p * bits)) & mask;
+            const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
+            if (full && __all_sync(0xffffffffu, d == d0)) {  // constant digit (culled keys, high depth bytes)
+                if (lane == 0) atomicAdd(&s_h[p][d0], 32u);
+            } else if (valid) {
+                atomicAdd(&s_h[p][d], 1u);
+            }
         }
     }
     __syncthreads();
@@ -211,7 +217,7 @@ __global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ 
 // One pass.  kIdentityVal: the payload of item i is i itself (first pass of the depth sort), so no
 // payload array is read.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.
 template <typename K, bool kIdentityVal>
-__global__ void __launch_bounds__(kBlk) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+__global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                           K* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                           const uint32_t* __restrict__ n_ptr, uint32_t n_host, uint32_t cap,
                                                           int shift, int bits, const uint32_t* __restrict__ hist,
@@ -243,28 +249,34 @@ __global__ void __launch_bounds__(kBlk) radix_pass_kernel(const K* __restrict__ 
     const size_t wbase = start + (size_t)warp * kSortWarpSpan;
 
     K key[kSortItems];
-    uint32_t val[kSortItems];
     uint32_t rank[kSortItems];
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         const size_t i = wbase + (size_t)k * 32 + lane;
         key[k] = i < n ? keys_in[i] : (K)0;
-        if (kIdentityVal) val[k] = (uint32_t)i;
-        else val[k] = i < n ? vals_in[i] : 0u;
     }
+    // Rank inside the warp: lanes holding the same digit are found with one ballot per digit bit
+    // (pipelined votes; MATCH.ANY costs ~150 cycles a piece on sm_100), the lowest such lane bumps the
+    // warp's private counter with one shared atomic and broadcasts the old value.
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         const size_t i = wbase + (size_t)k * 32 + lane;
         const bool valid = i < n;
-        const uint32_t d = valid ? ((uint32_t)(key[k] >> shift) & mask) : 0xffffffffu;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t r = __popc(peers & lt);
+        const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
+        unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int bit = 0; bit < 8; ++bit) {
+            if (bit < bits) {
+                const bool one = (d >> bit) & 1u;
+                const unsigned bal = __ballot_sync(0xffffffffu, one);
+                peers &= one ? bal : ~bal;
+            }
+        }
+        const int leader = __ffs(peers) - 1;
         uint32_t prior = 0;
-        if (valid) prior = my[d];
-        __syncwarp();
-        if (valid && r == 0) my[d] = prior + __popc(peers);
-        __syncwarp();
-        rank[k] = prior + r;
+        if (valid && (int)lane == leader) prior = atomicAdd(&my[d], (uint32_t)__popc(peers));
+        prior = __shfl_sync(0xffffffffu, prior, leader < 0 ? 0 : leader);
+        rank[k] = prior + __popc(peers & lt);
     }
     __syncthreads();
 
@@ -277,27 +289,41 @@ __global__ void __launch_bounds__(kBlk) radix_pass_kernel(const K* __restrict__ 
             s_cnt[w * bins + threadIdx.x] = h;
             h += c;
         }
-        uint32_t* st = status + (size_t)b * bins + threadIdx.x;
-        if (b != 0) st_relaxed(st, kFlagAgg | h);
+        if (b != 0) st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagAgg | h);
     }
     uint32_t total;
     const uint32_t binstart = block_excl_scan(h, s_warp, total);  // position of digit d in the sorted chunk
     const uint32_t gh = ((int)threadIdx.x < bins) ? __ldg(hist + threadIdx.x) : 0u;
     const uint32_t gstart = block_excl_scan(gh, s_warp, total);   // global start of digit d
     if ((int)threadIdx.x < bins) {
+        // decoupled look-back, kWin predecessors per round trip
+        constexpr int kWin = 8;
         uint32_t excl = 0;
-        uint32_t* st = status + (size_t)b * bins + threadIdx.x;
-        if (b != 0) {
-            const uint32_t* prev = st - bins;
-            while (true) {
-                uint32_t s;
-                do { s = ld_relaxed(prev); } while ((s >> 30) == 0);
-                excl += s & kValMask;
-                if ((s >> 30) == 2) break;
-                prev -= bins;
+        int prev = (int)b - 1;
+        bool done = (b == 0);
+        const uint32_t* col = status + threadIdx.x;
+        while (!done) {
+            uint32_t sw[kWin];
+#pragma unroll
+            for (int j = 0; j < kWin; ++j) {
+                const int idx = prev - j;
+                sw[j] = idx >= 0 ? ld_relaxed(col + (size_t)idx * bins) : kFlagIncl;
+            }
+            bool halt = false;
+#pragma unroll
+            for (int j = 0; j < kWin; ++j) {
+                const uint32_t f = sw[j] >> 30;
+                if (!halt && !done) {
+                    if (f == 0) halt = true;  // not published yet: retry from here
+                    else {
+                        excl += sw[j] & kValMask;
+                        --prev;
+                        if (f == 2) done = true;
+                    }
+                }
             }
         }
-        st_relaxed(st, kFlagIncl | (excl + h));
+        st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagIncl | (excl + h));
         s_binstart[threadIdx.x] = binstart;
         s_gbase[threadIdx.x] = gstart + excl - binstart;
     }
@@ -311,7 +337,7 @@ __global__ void __launch_bounds__(kBlk) radix_pass_kernel(const K* __restrict__ 
             const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
             const uint32_t pos = s_binstart[d] + my[d] + rank[k];
             s_keys[pos] = key[k];
-            s_vals[pos] = val[k];
+            s_vals[pos] = kIdentityVal ? (uint32_t)i : __ldg(vals_in + i);
         }
     }
     __syncthreads();
@@ -390,22 +416,32 @@ __global__ void __launch_bounds__(256) emit_keys_kernel(int P, int gx, int gy, c
 }
 
 // =========================== tile ranges ==================================================
+// Two sorted keys per thread (one 16-byte load); the predecessor of the pair comes from the
+// neighbouring lane, lane 0 fetches it.
 __global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __restrict__ keys,
                                                           const uint32_t* __restrict__ r_ptr, uint32_t cap,
                                                           uint2* __restrict__ ranges) {
     const uint32_t n = effective_n(r_ptr, cap);
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t t = (uint32_t)(keys[i] >> 32);
-    if (i == 0) ranges[t].x = 0;
-    else {
-        const uint32_t tp = (uint32_t)(keys[i - 1] >> 32);
-        if (tp != t) {
-            ranges[tp].y = i;
-            ranges[t].x = i;
-        }
+    const uint32_t i = 2u * (blockIdx.x * blockDim.x + threadIdx.x);
+    uint32_t t0 = 0xffffffffu, t1 = 0xffffffffu;
+    if (i + 1 < n) {
+        const ulonglong2 kk = *reinterpret_cast<const ulonglong2*>(keys + i);
+        t0 = (uint32_t)(kk.x >> 32);
+        t1 = (uint32_t)(kk.y >> 32);
+    } else if (i < n) {
+        t0 = (uint32_t)(keys[i] >> 32);
     }
-    if (i == n - 1) ranges[t].y = n;
+    uint32_t tp = __shfl_up_sync(0xffffffffu, t1, 1);
+    if (lane_id() == 0 && i > 0 && i < n) tp = (uint32_t)(keys[i - 1] >> 32);
+    if (i < n) {
+        if (i == 0) ranges[t0].x = 0;
+        else if (tp != t0) { ranges[tp].y = i; ranges[t0].x = i; }
+        if (i == n - 1) ranges[t0].y = n;
+    }
+    if (i + 1 < n) {
+        if (t0 != t1) { ranges[t0].y = i + 1; ranges[t1].x = i + 1; }
+        if (i + 1 == n - 1) ranges[t1].y = n;
+    }
 }
 
 int higher_msb(uint32_t n) {  // number of bits needed to represent values < n (at least 1)
@@ -538,7 +574,7 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
         }
     }
     StageScope scope(kStageTileRanges, s);
-    tile_ranges_kernel<<<(cap + 255) / 256, 256, 0, s>>>(bv.keys, r_ptr, cap, iv.ranges);
+    tile_ranges_kernel<<<(cap + 511) / 512, 256, 0, s>>>(bv.keys, r_ptr, cap, iv.ranges);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;
 }
