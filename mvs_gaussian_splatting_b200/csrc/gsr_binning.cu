@@ -216,12 +216,13 @@ __global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ 
 
 // One pass.  kIdentityVal: the payload of item i is i itself (first pass of the depth sort), so no
 // payload array is read.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.
-template <typename K, bool kIdentityVal>
+template <typename K, bool kIdentityVal, int kBits>
 __global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                           K* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                           const uint32_t* __restrict__ n_ptr, uint32_t n_host, uint32_t cap,
-                                                          int shift, int bits, const uint32_t* __restrict__ hist,
+                                                          int shift, const uint32_t* __restrict__ hist,
                                                           uint32_t* status, uint32_t* ticket) {
+    constexpr int bits = kBits;
     extern __shared__ __align__(16) unsigned char s_raw[];
     K* s_keys = reinterpret_cast<K*>(s_raw);                                          // [kSortChunk]
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw + sizeof(K) * kSortChunk);   // [kSortChunk]
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict
     __shared__ uint32_t s_warp[kBlk / 32 + 1];
     __shared__ uint32_t s_b;
 
-    const int bins = 1 << bits;
+    constexpr int bins = 1 << kBits;
     const uint32_t n = n_ptr ? effective_n(n_ptr, cap) : n_host;
     if (threadIdx.x == 0) s_b = atomicAdd(ticket, 1u);
     for (int d = threadIdx.x; d < bins * kSortWarps; d += kBlk) s_cnt[d] = 0;
@@ -265,12 +266,10 @@ __global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict
         const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
         unsigned peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-        for (int bit = 0; bit < 8; ++bit) {
-            if (bit < bits) {
-                const bool one = (d >> bit) & 1u;
-                const unsigned bal = __ballot_sync(0xffffffffu, one);
-                peers &= one ? bal : ~bal;
-            }
+        for (int bit = 0; bit < kBits; ++bit) {
+            const bool one = (d >> bit) & 1u;
+            const unsigned bal = __ballot_sync(0xffffffffu, one);
+            peers &= one ? bal : ~bal;
         }
         const int leader = __ffs(peers) - 1;
         uint32_t prior = 0;
@@ -297,7 +296,7 @@ __global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict
     const uint32_t gstart = block_excl_scan(gh, s_warp, total);   // global start of digit d
     if ((int)threadIdx.x < bins) {
         // decoupled look-back, kWin predecessors per round trip
-        constexpr int kWin = 8;
+        constexpr int kWin = 16;
         uint32_t excl = 0;
         int prev = (int)b - 1;
         bool done = (b == 0);
@@ -454,9 +453,41 @@ int higher_msb(uint32_t n) {  // number of bits needed to represent values < n (
 void tile_sort_plan(int tile_bits, int& passes, int& bits) {
     passes = (tile_bits + 7) / 8;
     bits = (tile_bits + passes - 1) / passes;
+    if (bits < 4) bits = 4;
 }
 
 size_t chunks_of(size_t n) { return (n + kSortChunk - 1) / kSortChunk; }
+
+// Tile-bit passes are instantiated for 4..8-bit digits (the digit width is a compile-time constant so
+// the ballot ranking unrolls without predicate spills).
+template <int kBits>
+void launch_tile_pass_bits(unsigned grid, size_t smem, cudaStream_t s, const uint64_t* kin, const uint32_t* vin,
+                           uint64_t* kout, uint32_t* vout, const uint32_t* r_ptr, uint32_t cap, int shift,
+                           const uint32_t* hist, uint32_t* status, uint32_t* ticket) {
+    radix_pass_kernel<uint64_t, false, kBits><<<grid, kBlk, smem, s>>>(kin, vin, kout, vout, r_ptr, 0u, cap, shift, hist,
+                                                                      status, ticket);
+}
+void launch_tile_pass(int bits, unsigned grid, size_t smem, cudaStream_t s, const uint64_t* kin, const uint32_t* vin,
+                      uint64_t* kout, uint32_t* vout, const uint32_t* r_ptr, uint32_t cap, int shift,
+                      const uint32_t* hist, uint32_t* status, uint32_t* ticket) {
+    switch (bits) {
+        case 4: launch_tile_pass_bits<4>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+        case 5: launch_tile_pass_bits<5>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+        case 6: launch_tile_pass_bits<6>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+        case 7: launch_tile_pass_bits<7>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+        default: launch_tile_pass_bits<8>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+    }
+}
+cudaError_t set_tile_pass_attributes() {
+    cudaError_t e = cudaSuccess;
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 4>, attr, (int)radix_pass_smem<uint64_t>(4));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 5>, attr, (int)radix_pass_smem<uint64_t>(5));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 6>, attr, (int)radix_pass_smem<uint64_t>(6));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 7>, attr, (int)radix_pass_smem<uint64_t>(7));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 8>, attr, (int)radix_pass_smem<uint64_t>(8));
+    return e;
+}
 
 }  // namespace
 
@@ -474,8 +505,7 @@ size_t tile_sort_ctl_entries(size_t cap) { return kCtlHeader + (size_t)kMaxPasse
 int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
     static bool attr_set = false;  // idempotent; racing threads set the same value
     if (!attr_set) {
-        GSR_CUDA(cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)radix_pass_smem<uint64_t>(8)));
+        GSR_CUDA(set_tile_pass_attributes());
         attr_set = true;
     }
     const size_t nchunk = chunks_of((size_t)P);
@@ -500,12 +530,12 @@ int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
         uint32_t* vout = gv.order_alt;
         for (int pass = 0; pass < 4; ++pass) {
             if (pass == 0)
-                radix_pass_kernel<uint32_t, true><<<(unsigned)nchunk, kBlk, smem, s>>>(
-                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, 8, hist + pass * kMaxBins,
+                radix_pass_kernel<uint32_t, true, 8><<<(unsigned)nchunk, kBlk, smem, s>>>(
+                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, hist + pass * kMaxBins,
                     status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
             else
-                radix_pass_kernel<uint32_t, false><<<(unsigned)nchunk, kBlk, smem, s>>>(
-                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, 8, hist + pass * kMaxBins,
+                radix_pass_kernel<uint32_t, false, 8><<<(unsigned)nchunk, kBlk, smem, s>>>(
+                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, hist + pass * kMaxBins,
                     status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
             GSR_AFTER_LAUNCH(s, debug);
             kin = kout;
@@ -564,9 +594,8 @@ int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinV
         for (int pass = 0; pass < passes; ++pass) {
             uint64_t* kout = to_main ? bv.keys : bv.keys_alt;
             uint32_t* vout = to_main ? bv.point_list : bv.vals_alt;
-            radix_pass_kernel<uint64_t, false><<<(unsigned)nchunk, kBlk, smem, s>>>(
-                kin, vin, kout, vout, r_ptr, 0u, cap, 32 + pass * bits, bits, hist + pass * kMaxBins,
-                status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
+            launch_tile_pass(bits, (unsigned)nchunk, smem, s, kin, vin, kout, vout, r_ptr, cap, 32 + pass * bits,
+                             hist + pass * kMaxBins, status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
             GSR_AFTER_LAUNCH(s, debug);
             kin = kout;
             vin = vout;
