@@ -240,12 +240,28 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
         if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;  // float4 pieces per row (row start is 16B aligned)
             const int total = nvis * vpr;
-            for (int j = lane; j < total; j += 32) {
-                const int v = j / vpr, part = j - v * vpr;
-                const int src_lane = __fns(vis, 0, v + 1);
-                const float4 val = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_base + src_lane) * row) + part);
-                float* d = tile + src_lane * kShStride + 4 * part;
-                d[0] = val.x; d[1] = val.y; d[2] = val.z; d[3] = val.w;
+            const int my_src = __fns(vis, 0, lane + 1);  // lane of the (lane+1)-th surviving Gaussian
+            // four independent 16-byte loads in flight per lane before the first shared store
+            for (int jb = 0; jb < total; jb += 128) {  // warp-uniform trip count (shuffles inside)
+                const int j0 = jb + (int)lane;
+                float4 val[4];
+                int dst[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int j = j0 + 32 * u;
+                    const int v = min(j, total - 1) / vpr, part = min(j, total - 1) - v * vpr;
+                    const int src_lane = __shfl_sync(0xffffffffu, my_src, v);
+                    dst[u] = src_lane * kShStride + 4 * part;
+                    if (j < total)
+                        val[u] = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_base + src_lane) * row) + part);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (j0 + 32 * u < total) {
+                        float* d = tile + dst[u];
+                        d[0] = val[u].x; d[1] = val[u].y; d[2] = val[u].z; d[3] = val[u].w;
+                    }
+                }
             }
         } else {
             const int total = nvis * need;
