@@ -134,17 +134,49 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
     const int row = 3 * p.M;
     const int need = 3 * (p.D + 1) * (p.D + 1);
 
+    // ---- per-Gaussian operands: issued before the SH fetch so their latency overlaps it ----
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, con = a0, q = make_float4(1.f, 0.f, 0.f, 0.f);
+    float mx = 0.f, my = 0.f, mz = 0.f, rs0 = 0.f, rs1 = 0.f, rs2 = 0.f;
+    uint32_t clamped_bits = 0;
+    if (vis) {
+        const float4* accp = reinterpret_cast<const float4*>(p.gv.grad_accum + (size_t)idx * 12);
+        a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
+        con = p.gv.conic_opacity[idx];
+        mx = p.means3D[3 * (size_t)idx]; my = p.means3D[3 * (size_t)idx + 1]; mz = p.means3D[3 * (size_t)idx + 2];
+        if (!p.cov3D_precomp) {
+            q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+            rs0 = p.scales[3 * (size_t)idx]; rs1 = p.scales[3 * (size_t)idx + 1]; rs2 = p.scales[3 * (size_t)idx + 2];
+        }
+        if (do_sh) clamped_bits = __float_as_uint(p.gv.rgb[idx].w);
+    }
+
     // ---- fetch the SH rows of the visible Gaussians of this warp ----
     if (do_sh && vmask) {
         const int nvis = __popc(vmask);
         if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;
-            for (int j = lane; j < nvis * vpr; j += 32) {
-                const int v = j / vpr, part = j - v * vpr;
-                const int src = __fns(vmask, 0, v + 1);
-                const float4 val = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_base + src) * row) + part);
-                float* d = tile + src * kShStride + 4 * part;
-                d[0] = val.x; d[1] = val.y; d[2] = val.z; d[3] = val.w;
+            const int total = nvis * vpr;
+            const int my_src = __fns(vmask, 0, lane + 1);  // lane of the (lane+1)-th visible Gaussian
+            for (int jb = 0; jb < total; jb += 128) {  // warp-uniform trip count (shuffles inside)
+                float4 val[4];
+                int dsto[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int j = jb + (int)lane + 32 * u;
+                    const int jc = min(j, total - 1);
+                    const int v = jc / vpr, part = jc - v * vpr;
+                    const int src = __shfl_sync(0xffffffffu, my_src, v);
+                    dsto[u] = src * kShStride + 4 * part;
+                    if (j < total)
+                        val[u] = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_base + src) * row) + part);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (jb + (int)lane + 32 * u < total) {
+                        float* d = tile + dsto[u];
+                        d[0] = val[u].x; d[1] = val[u].y; d[2] = val[u].z; d[3] = val[u].w;
+                    }
+                }
             }
         } else {
             for (int j = lane; j < nvis * need; j += 32) {
@@ -161,9 +193,6 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
     float g2d[2] = {0.f, 0.f}, gcol[3] = {0.f, 0.f, 0.f}, gop = 0.f;
 
     if (vis) {
-        const float4* accp = reinterpret_cast<const float4*>(p.gv.grad_accum + (size_t)idx * 12);
-        const float4 a0 = accp[0], a1 = accp[1], a2 = accp[2];
-        const float4 con = p.gv.conic_opacity[idx];
         const float S1 = a0.x, S2 = a0.y;
         // true partials of the conic (A,B,C) and the NDC-scaled mean2D gradient
         const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
@@ -172,17 +201,14 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
         gop = a1.y;
         gcol[0] = a1.z; gcol[1] = a1.w; gcol[2] = a2.x;
 
-        const float mx = p.means3D[3 * (size_t)idx], my = p.means3D[3 * (size_t)idx + 1], mz = p.means3D[3 * (size_t)idx + 2];
         float c6[6], R[3][3], s[3] = {0.f, 0.f, 0.f};
-        float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
         if (p.cov3D_precomp) {
 #pragma unroll
             for (int k = 0; k < 6; ++k) c6[k] = p.cov3D_precomp[6 * (size_t)idx + k];
         } else {
-            q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
-            s[0] = p.scale_modifier * p.scales[3 * (size_t)idx];
-            s[1] = p.scale_modifier * p.scales[3 * (size_t)idx + 1];
-            s[2] = p.scale_modifier * p.scales[3 * (size_t)idx + 2];
+            s[0] = p.scale_modifier * rs0;
+            s[1] = p.scale_modifier * rs1;
+            s[2] = p.scale_modifier * rs2;
             cov3d(s[0], s[1], s[2], q, R, c6);
         }
 
@@ -267,7 +293,7 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
         }
         // ---- colour -> SH + view direction ----
         if (do_sh) {
-            const uint32_t clamped = __float_as_uint(p.gv.rgb[idx].w);
+            const uint32_t clamped = clamped_bits;
             float g3[3];
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch) g3[ch] = (clamped >> ch) & 1u ? 0.f : gcol[ch];
@@ -338,10 +364,12 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
                 float* dst = p.dL_dsh + (size_t)warp_base * row;
                 if ((row & 3) == 0) {
                     const int vpr = row >> 2;
-                    for (int j = lane; j < nrows * vpr; j += 32) {
+                    const int total = nrows * vpr;
+#pragma unroll 4
+                    for (int j = lane; j < total; j += 32) {
                         const int r = j / vpr, part = j - r * vpr;
                         const float* sp = tile + r * kShStride + 4 * part;
-                        reinterpret_cast<float4*>(dst)[j] = make_float4(sp[0], sp[1], sp[2], sp[3]);
+                        __stcs(reinterpret_cast<float4*>(dst) + j, make_float4(sp[0], sp[1], sp[2], sp[3]));
                     }
                 } else {
                     for (int j = lane; j < nrows * row; j += 32) {
