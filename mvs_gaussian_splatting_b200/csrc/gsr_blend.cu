@@ -133,9 +133,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, float* __restrict__ out_color, float* __restrict__ final_T,
     uint32_t* __restrict__ n_contrib, unsigned long long* __restrict__ counters) {
-    __shared__ float4 s_a[kBlendThreads];    // x, y, a2, b2
-    __shared__ float4 s_b[kBlendThreads];    // c2, opacity, tau2, list position (1-based, int bits)
-    __shared__ float4 s_col[kBlendThreads];  // r, g, b, -
+    // staged entry j = s_e[3j..3j+2]: (x, y, a2, b2) (c2, opacity, tau2, list position 1-based) (r, g, b, -)
+    // one base address per entry; 48-byte stride keeps the lane-per-entry 16-byte reads conflict-free
+    __shared__ float4 s_e[3 * kBlendThreads];
     __shared__ int s_wcount[kBlendWarps];
 
     const TileCtx c = tile_ctx(gx, W, H);
@@ -167,9 +167,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
         const int slot = compact_slot(keep, s_wcount, total);
         if (keep) {
             const float4 col = __ldg(rgb + gid);
-            s_a[slot] = make_float4(m.x, m.y, a2, b2);
-            s_b[slot] = make_float4(c2, op, tau2, __int_as_float(p + 1));
-            s_col[slot] = col;
+            s_e[3 * slot] = make_float4(m.x, m.y, a2, b2);
+            s_e[3 * slot + 1] = make_float4(c2, op, tau2, __int_as_float(p + 1));
+            s_e[3 * slot + 2] = col;
         }
         __syncthreads();
 
@@ -178,16 +178,16 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
             const int jt = cb + (int)lane;
             bool hit = false;
             if (jt < total) {
-                const float4 ta = s_a[jt];
-                const float4 tb = s_b[jt];
+                const float4 ta = s_e[3 * jt];
+                const float4 tb = s_e[3 * jt + 1];
                 hit = splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
             }
             unsigned mask = __ballot_sync(0xffffffffu, hit);
             while (mask) {
                 const int j = cb + __ffs(mask) - 1;
                 mask &= mask - 1;
-                const float4 g = s_a[j];
-                const float4 cc = s_b[j];
+                const float4 g = s_e[3 * j];
+                const float4 cc = s_e[3 * j + 1];
                 const float dx = g.x - fx, dy = g.y - fy;
                 const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
                 const float alpha = fminf(0.99f, cc.y * ex2_approx(pw));
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
                     continue;
                 }
                 if (kCount) ++n_blended;
-                const float4 col = s_col[j];
+                const float4 col = s_e[3 * j + 2];
                 const float wgt = alpha * T;
                 C0 = fmaf(col.x, wgt, C0);
                 C1 = fmaf(col.y, wgt, C1);
@@ -292,9 +292,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, float* __restrict__ grad_accum) {
-    __shared__ float4 s_a[kBlendThreads];    // x, y, a2, b2
-    __shared__ float4 s_b[kBlendThreads];    // c2, opacity, tau2, list position (1-based, int bits)
-    __shared__ float4 s_col[kBlendThreads];  // r, g, b, gaussian id (uint bits)
+    // staged entry j = s_e[3j..3j+2]: (x, y, a2, b2) (c2, opacity, tau2, list position 1-based) (r, g, b, gaussian id)
+    __shared__ float4 s_e[3 * kBlendThreads];
     __shared__ __align__(16) float s_part[kBlendWarps][32][12];  // per-warp parked sums of one 32-entry chunk
     __shared__ uint32_t s_gid[kBlendWarps][32];
     __shared__ int s_wcount[kBlendWarps];
@@ -348,9 +347,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
         const int slot = compact_slot(keep, s_wcount, total);
         if (keep) {
             const float4 col = __ldg(rgb + gid);
-            s_a[slot] = make_float4(mm.x, mm.y, a2, b2);
-            s_b[slot] = make_float4(c2, op, tau2, __int_as_float(p + 1));
-            s_col[slot] = make_float4(col.x, col.y, col.z, __uint_as_float(gid));
+            s_e[3 * slot] = make_float4(mm.x, mm.y, a2, b2);
+            s_e[3 * slot + 1] = make_float4(c2, op, tau2, __int_as_float(p + 1));
+            s_e[3 * slot + 2] = make_float4(col.x, col.y, col.z, __uint_as_float(gid));
         }
         __syncthreads();
         if (wmax == 0) continue;  // warp-uniform: block outside the image or nothing blended
@@ -359,8 +358,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
             const int jt = cb + (int)lane;
             bool hit = false;
             if (jt < total) {
-                const float4 ta = s_a[jt];
-                const float4 tb = s_b[jt];
+                const float4 ta = s_e[3 * jt];
+                const float4 tb = s_e[3 * jt + 1];
                 hit = ((uint32_t)__float_as_int(tb.w) <= wmax) &&
                       splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
             }
@@ -369,22 +368,21 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
             while (mask) {
                 const int j = cb + __ffs(mask) - 1;
                 mask &= mask - 1;
-                const float4 g = s_a[j];
-                const float4 cc = s_b[j];
+                const float4 g = s_e[3 * j];
+                const float4 cc = s_e[3 * j + 1];
                 const float dx = g.x - fx, dy = g.y - fy;
                 const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
                 const float G = ex2_approx(pw);
                 const float alpha = fminf(0.99f, cc.y * G);
                 const bool ok = ((uint32_t)__float_as_int(cc.w) <= last) && !(pw > 0.0f) && !(alpha < kAlphaMin);
                 if (!__any_sync(0xffffffffu, ok)) continue;
-                const float4 col = s_col[j];
-                float v[9];
-#pragma unroll
-                for (int k = 0; k < 9; ++k) v[k] = 0.0f;
+                const float4 col = s_e[3 * j + 2];
+                // the 9 sums are products of three per-pair scalars; lanes that do not blend keep zeros
+                float h = 0.0f, gdl = 0.0f, wgt = 0.0f;
                 if (ok) {
                     const float ra = rcp_approx(1.0f - alpha);
                     T *= ra;
-                    const float wgt = alpha * T;
+                    wgt = alpha * T;
                     bh0 = last_alpha * lc0 + (1.0f - last_alpha) * bh0;
                     bh1 = last_alpha * lc1 + (1.0f - last_alpha) * bh1;
                     bh2 = last_alpha * lc2 + (1.0f - last_alpha) * bh2;
@@ -393,12 +391,14 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
                     dL_dalpha *= T;
                     last_alpha = alpha;
                     dL_dalpha -= Tfin * ra * bgdot;
-                    const float h = cc.y * dL_dalpha * G;  // dL/dG * G
-                    const float hx = h * dx, hy = h * dy;
-                    v[0] = hx; v[1] = hy; v[2] = hx * dx; v[3] = hx * dy; v[4] = hy * dy;
-                    v[5] = G * dL_dalpha;
-                    v[6] = wgt * g0; v[7] = wgt * g1; v[8] = wgt * g2;
+                    gdl = G * dL_dalpha;
+                    h = cc.y * gdl;  // dL/dG * G
                 }
+                const float hx = h * dx, hy = h * dy;
+                float v[9];
+                v[0] = hx; v[1] = hy; v[2] = hx * dx; v[3] = hx * dy; v[4] = hy * dy;
+                v[5] = gdl;
+                v[6] = wgt * g0; v[7] = wgt * g1; v[8] = wgt * g2;
                 const float r = warp_reduce9(v, lane);
                 if (my_slot >= 0) s_part[warp][nh][my_slot] = r;
                 if (lane == 0) s_gid[warp][nh] = __float_as_uint(col.w);
