@@ -4,6 +4,7 @@
 #   gpurun --timeout 1500 -- 'bash tools/gpu_profile.sh [tag]'
 set -u
 TAG=${1:-r01}
+LPS=${2:-16}   # kernel launches of libgsrast_b200.so per fwd+bwd step
 OUT=gpurun_out
 mkdir -p $OUT
 BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
@@ -20,10 +21,10 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
     --log-file $OUT/${TAG}_launches.csv $BENCH > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launch list exit $?"
 
-# kernels of OUR library only; skip the 3 warm-up steps (34 matching launches per step)
+# kernels of OUR library only; skip the 3 warm-up steps (LPS matching launches per step)
 $BENCH > $OUT/${TAG}_plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on \
-    -k regex:'blend_|sort_|preprocess|emit_keys|tile_ranges|scan_' -s 102 -c 34 \
+    -k regex:'blend_|radix_|preprocess|emit_keys|tile_ranges|scan_|publish_' -s $((3*LPS)) -c $LPS \
     -f -o $OUT/${TAG}_full $BENCH > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $OUT

@@ -44,3 +44,37 @@ def main(rep, out):
 
 if __name__ == "__main__":
     main(sys.argv[1], sys.argv[2])
+
+
+# ---- profiles/traffic.json: measured DRAM bytes per launch of each bench stage -----------------
+STAGE_OF = [("preprocess_backward", "preprocess_backward"), ("preprocess_kernel", "preprocess"),
+            ("radix_hist_kernel<unsigned int", "depth_sort"), ("radix_pass_kernel<unsigned int", "depth_sort"),
+            ("scan_sorted_tiles", "scan"), ("emit_keys", "emit_keys"),
+            ("radix_hist_kernel<unsigned long", "radix_sort"), ("radix_pass_kernel<unsigned long", "radix_sort"),
+            ("tile_ranges", "tile_ranges"), ("blend_forward", "blend_forward"), ("blend_backward", "blend_backward")]
+
+
+def traffic(rep, out):
+    """Sum dram__bytes_read.sum + dram__bytes_write.sum over the kernels of each stage of ONE step."""
+    import json
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    col = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    acc = {}
+    for r in data:
+        name = r[col["Kernel Name"]]
+        stage = next((s for pat, s in STAGE_OF if pat in name), None)
+        if stage is None:
+            continue
+        b = 0.0
+        for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            b += float(r[col[m]].replace(",", "")) * scale[units[col[m]]]
+        acc[stage] = acc.get(stage, 0.0) + b
+    json.dump({k: round(v) for k, v in acc.items()}, open(out, "w"), indent=1)
+    print(acc)
+
+
+if __name__ == "__main__" and len(sys.argv) > 3 and sys.argv[3] == "traffic":
+    traffic(sys.argv[1], sys.argv[4])
