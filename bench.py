@@ -202,7 +202,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def arm_estimate(cal, stride, gy):
@@ -384,7 +384,7 @@ def run_b200_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -413,20 +413,50 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     gt_host = torch.from_numpy((0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)).pin_memory()
     params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
 
+    # Per-step host inputs are prefetched one step ahead on a copy stream (double-buffered), as a data
+    # loader does; the loss is copied to pinned memory asynchronously and read one step late, so the
+    # host never stalls the launch queue.  Every copy still happens inside the timed region, once per step.
+    copy_stream = torch.cuda.Stream(device=dev)
+    main = torch.cuda.current_stream(dev)
+    slots = [dict(block=torch.empty_like(cam_host, device=dev), gt=torch.empty_like(gt_host, device=dev),
+                  ready=torch.cuda.Event(), free=torch.cuda.Event(), loss=torch.zeros(1).pin_memory(),
+                  loss_ready=torch.cuda.Event()) for _ in range(2)]
+    for sl in slots:
+        sl["free"].record(main)
+    state = {"k": 0, "pending": None}
+
+    def prefetch(sl):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(sl["free"])          # the step that last used this slot is done with it
+            sl["block"].copy_(cam_host, non_blocking=True)
+            sl["gt"].copy_(gt_host, non_blocking=True)
+            sl["ready"].record(copy_stream)
+
+    prefetch(slots[0])
+
     def step():
-        block = cam_host.to(dev, non_blocking=True)
-        gt = gt_host.to(dev, non_blocking=True)
-        rs = settings_from(block)
+        sl = slots[state["k"] & 1]
+        prefetch(slots[(state["k"] + 1) & 1])           # next step's inputs travel while this step computes
+        main.wait_event(sl["ready"])
+        rs = settings_from(sl["block"])
         means2D = torch.zeros_like(params["means3D"], requires_grad=True)
         color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
                                               opacities=params["opacities"], scales=params["scales"],
                                               rotations=params["rotations"])
-        loss = (color - gt).abs().mean()
+        loss = (color - sl["gt"]).abs().mean()
         loss.backward()
         if world > 1:
             for p in params.values():
                 dist.all_reduce(p.grad)
-        val = loss.item()                                   # D2H read of the step's result
+        sl["loss"].copy_(loss.detach().reshape(1), non_blocking=True)   # D2H read of the step's result
+        sl["loss_ready"].record(main)
+        sl["free"].record(main)
+        val = None
+        if state["pending"] is not None:                 # previous step's loss, now on the host
+            state["pending"]["loss_ready"].synchronize()
+            val = float(state["pending"]["loss"][0])
+        state["pending"] = sl
+        state["k"] += 1
         for p in params.values():
             p.grad = None                                   # train.py:142 zero_grad(set_to_none=True)
         return val
@@ -449,7 +479,8 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     return {"value": world * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
             "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4,
             "api": "GaussianRasterizer(settings)(...) + L1 loss + backward(), camera + ground-truth image from "
-                   "pinned host memory, loss read back; Gaussian parameters resident in HBM (model state)"}
+                   "pinned host memory (prefetched one step ahead on a copy stream), loss copied back to pinned "
+                   "memory every step; Gaussian parameters resident in HBM (model state)"}
 
 
 def run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward, arena):
@@ -477,8 +508,21 @@ def run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward
             "d2h_bytes_per_step": int(grad_host.numel() * 4)}
 
 
+def _emit(line):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version
+    banner, torchrun notices) was diverted to stderr by main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)  # C-level writes to fd 1 (NCCL_DEBUG banners) must not pollute the JSON line
     if args.impl == "reference":
         run_reference_arm(args)
     else:

@@ -14,7 +14,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libgsrast_b200.so")
+# GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
+LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 ABI_VERSION = 2
 

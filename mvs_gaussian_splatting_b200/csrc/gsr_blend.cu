@@ -17,9 +17,10 @@
 //     one MUFU.EX2 (ex2.approx), not an expf() call.
 //   * a warp leaves the loop as soon as all 32 of its pixels are saturated (vote), the CTA leaves
 //     the batch loop when all 256 are.
-//   * backward: per-pair gradients are reduced across the warp with a 12-shuffle transposing
-//     butterfly (9 sums land in 9 different lanes), parked in a per-warp shared buffer, and flushed
-//     once per 32 staged entries as 128-bit vector reductions (RED.E.ADD.F32x4) to L2: three per
+//   * backward: the 9 per-pair gradient terms of a warp's 32 pixels are TRANSPOSED through a per-warp
+//     shared tile (9 conflict-free STS per splat) and summed three splats at a time by 27 lanes that
+//     each add up one 32-entry row (8 LDS.128 + 31 FADD) — a third of the issue slots of a shuffle
+//     butterfly — then flushed as 128-bit vector reductions (RED.E.ADD.F32x4) to L2: three per
 //     (8x4 block, splat) — versus 9 scalar global atomics per contributing (pixel, splat) pair in
 //     the reference.  No CTA-wide barrier inside the walk.
 #include "gsr_internal.cuh"
@@ -241,61 +242,46 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
 }
 
 // ------------------------------------ backward ---------------------------------------------
-// Transposing butterfly: reduces 9 per-lane values over the warp in 12 shuffles.  On return,
-// lanes with an even lane id and slot >= 0 hold the warp total of value `slot` (slots 9..11 are
-// exact zeros used as float4 padding).
-__device__ __forceinline__ int reduce_slot_of_lane(unsigned lane) {
-    const int b4 = (lane >> 4) & 1, k = (lane >> 1) & 7;  // k = b3 b2 b1
-    // within a 5-group: 000->0 001->1 010->2 011->pad 100->3 101->4 110->pad 111->pad
-    // lower half-warp: values 0..4, pads become the zero slots 9,10,11; upper: values 5..8.
-    const uint32_t packed = b4 ? 0xFFF8F765u : 0xBA439210u;
-    const int nib = (int)((packed >> (4 * k)) & 15u);
-    return nib == 15 ? -1 : nib;
+constexpr int kRedSplats = 3;  // splats per transposed-reduction batch: 27 rows <= 32 lanes
+
+// Sums the parked rows of `nb` splats (row r = splat r/9, term r%9; 32 per-pixel entries each) and
+// adds the totals to grad_accum as three 16-byte vector reductions per splat.  Lane r reads its row
+// in 16-byte pieces starting at piece r%8, so the four lanes that share a bank group are the four
+// wavefronts a 512-byte warp read needs anyway.
+__device__ __forceinline__ void flush_parked(int nb, unsigned lane, const float* red, float* tot,
+                                             const uint32_t* gid, float* __restrict__ grad_accum) {
+    __syncwarp();
+    if ((int)lane < 9 * nb) {
+        const float4* row = reinterpret_cast<const float4*>(red) + lane * 8;
+        float4 a = row[lane & 7];
+#pragma unroll
+        for (int j = 1; j < 8; ++j) {
+            const float4 b = row[(lane + j) & 7];
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        const int sp = (int)lane / 9;
+        tot[sp * 12 + ((int)lane - sp * 9)] = (a.x + a.y) + (a.z + a.w);
+    }
+    __syncwarp();
+    if ((int)lane < 3 * nb) {
+        const int e = (int)lane / 3, quad = (int)lane - e * 3;
+        const float4 acc = *reinterpret_cast<const float4*>(tot + e * 12 + quad * 4);
+        if (acc.x != 0.f || acc.y != 0.f || acc.z != 0.f || acc.w != 0.f)
+            atomicAdd(reinterpret_cast<float4*>(grad_accum + (size_t)gid[e] * 12 + quad * 4), acc);
+    }
+    __syncwarp();
 }
 
-__device__ __forceinline__ float warp_reduce9(const float* v, unsigned lane) {
-    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;
-    float u[5], t[3], s[2];
-#pragma unroll
-    for (int i = 0; i < 5; ++i) {
-        const float hi_v = (i < 4) ? v[5 + i] : 0.0f;
-        const float send = h16 ? v[i] : hi_v;
-        const float keep = h16 ? hi_v : v[i];
-        u[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        const float hi_v = (i < 2) ? u[3 + i] : 0.0f;
-        const float send = h8 ? u[i] : hi_v;
-        const float keep = h8 ? hi_v : u[i];
-        t[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const float hi_v = (i < 1) ? t[2] : 0.0f;
-        const float send = h4 ? t[i] : hi_v;
-        const float keep = h4 ? hi_v : t[i];
-        s[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    }
-    float r;
-    {
-        const float send = h2 ? s[0] : s[1];
-        const float keep = h2 ? s[1] : s[0];
-        r = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-    }
-    r += __shfl_xor_sync(0xffffffffu, r, 1);
-    return r;
-}
-
-__global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
+__global__ void __launch_bounds__(kBlendThreads, 4) blend_backward_kernel(
     int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
     const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
     const float* __restrict__ dL_dpix, float* __restrict__ grad_accum) {
     // staged entry j = s_e[3j..3j+2]: (x, y, a2, b2) (c2, opacity, tau2, list position 1-based) (r, g, b, gaussian id)
     __shared__ float4 s_e[3 * kBlendThreads];
-    __shared__ __align__(16) float s_part[kBlendWarps][32][12];  // per-warp parked sums of one 32-entry chunk
-    __shared__ uint32_t s_gid[kBlendWarps][32];
+    __shared__ __align__(16) float s_red[kBlendWarps][kRedSplats * 9][32];  // [warp][splat*9 + term][pixel lane]
+    __shared__ __align__(16) float s_tot[kBlendWarps][kRedSplats][12];      // row totals; [..][9..11] stay zero
+    __shared__ uint32_t s_gid[kBlendWarps][kRedSplats + 1];
     __shared__ int s_wcount[kBlendWarps];
     __shared__ uint32_t s_wmax[kBlendWarps];
 
@@ -304,7 +290,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
     const unsigned lane = lane_id();
     const int warp = threadIdx.x >> 5;
     const float fx = (float)c.px, fy = (float)c.py;
-    const int my_slot = (lane & 1) ? -1 : reduce_slot_of_lane(lane);
+    if (lane < kRedSplats * 3) s_tot[warp][lane / 3][9 + lane % 3] = 0.0f;  // float4 padding of the totals
+    float* const my_red = &s_red[warp][0][lane];
+    int nh = 0;  // parked splats of this warp (carried across chunks and batches)
 
     float Tfin = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
     uint32_t last = 0;
@@ -364,7 +352,6 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
                       splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
             }
             unsigned mask = __ballot_sync(0xffffffffu, hit);
-            int nh = 0;  // parked entries of this chunk (warp-uniform)
             while (mask) {
                 const int j = cb + __ffs(mask) - 1;
                 mask &= mask - 1;
@@ -395,26 +382,25 @@ __global__ void __launch_bounds__(kBlendThreads) blend_backward_kernel(
                     h = cc.y * gdl;  // dL/dG * G
                 }
                 const float hx = h * dx, hy = h * dy;
-                float v[9];
-                v[0] = hx; v[1] = hy; v[2] = hx * dx; v[3] = hx * dy; v[4] = hy * dy;
-                v[5] = gdl;
-                v[6] = wgt * g0; v[7] = wgt * g1; v[8] = wgt * g2;
-                const float r = warp_reduce9(v, lane);
-                if (my_slot >= 0) s_part[warp][nh][my_slot] = r;
+                float* dst = my_red + nh * (9 * 32);
+                dst[0 * 32] = hx;
+                dst[1 * 32] = hy;
+                dst[2 * 32] = hx * dx;
+                dst[3 * 32] = hx * dy;
+                dst[4 * 32] = hy * dy;
+                dst[5 * 32] = gdl;
+                dst[6 * 32] = wgt * g0;
+                dst[7 * 32] = wgt * g1;
+                dst[8 * 32] = wgt * g2;
                 if (lane == 0) s_gid[warp][nh] = __float_as_uint(col.w);
-                ++nh;
+                if (++nh == kRedSplats) {
+                    flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
+                    nh = 0;
+                }
             }
-            __syncwarp();
-            // flush: one lane per (parked entry, float4 quad)
-            for (int t = (int)lane; t < nh * 3; t += 32) {
-                const int e = t / 3, quad = t - e * 3;
-                const float4 acc = *reinterpret_cast<const float4*>(&s_part[warp][e][quad * 4]);
-                if (acc.x != 0.f || acc.y != 0.f || acc.z != 0.f || acc.w != 0.f)
-                    atomicAdd(reinterpret_cast<float4*>(grad_accum + (size_t)s_gid[warp][e] * 12 + quad * 4), acc);
-            }
-            __syncwarp();
         }
     }
+    if (nh) flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
 }
 
 }  // namespace

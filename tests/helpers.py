@@ -92,5 +92,11 @@ def depth_order_emission(pre, binned):
     vis = pre["radii"] > 0
     ids = np.flatnonzero(vis)
     ids = ids[np.argsort(pre["depths"].view(np.uint32)[vis], kind="stable")]
-    idx = np.concatenate([np.arange(starts[i], ends[i]) for i in ids]) if len(ids) else np.zeros(0, np.int64)
+    n = tt[ids]
+    total = int(n.sum())
+    if total == 0:
+        idx = np.zeros(0, np.int64)
+    else:
+        block_first = np.cumsum(n) - n                      # first output slot of each Gaussian's block
+        idx = np.repeat(starts[ids] - block_first, n) + np.arange(total, dtype=np.int64)
     return binned["keys_unsorted"][idx], binned["values_unsorted"][idx]

@@ -43,9 +43,13 @@ def _gpu_forward(cuda, cam, g, bg, D, **kw):
 
 @pytest.mark.parametrize("P,W,H,D,M,seed", CASES)
 def test_forward_bit_exact_lists_and_image(cuda, oracle, P, W, H, D, M, seed):
+    check_forward(cuda, oracle, P, W, H, D, M, seed)
+
+
+def check_forward(cuda, oracle, P, W, H, D, M, seed, threads=8):
     cam, g = Hh.make_case(P, W, H, seed=seed, sh_coeffs=M)
     bg = [0.1, 0.5, 0.9]
-    ref = Hh.run_oracle(oracle, cam, g, bg, D)
+    ref = Hh.run_oracle(oracle, cam, g, bg, D, threads=threads)
     rs, t, color, radii, ctx, _ = _gpu_forward(cuda, cam, g, bg, D)
     pre, binned, fwd = ref["pre"], ref["binned"], ref["fwd"]
 
@@ -97,16 +101,20 @@ def test_forward_bit_exact_lists_and_image(cuda, oracle, P, W, H, D, M, seed):
 
 @pytest.mark.parametrize("P,W,H,D,M,seed", CASES)
 def test_backward_gradients(cuda, oracle, P, W, H, D, M, seed):
+    check_backward(cuda, oracle, P, W, H, D, M, seed)
+
+
+def check_backward(cuda, oracle, P, W, H, D, M, seed, threads=8):
     import torch
     from mvs_gaussian_splatting_b200 import GaussianRasterizer
     cam, g = Hh.make_case(P, W, H, seed=seed, sh_coeffs=M)
     bg = [0.3, 0.2, 0.7]
-    fragile = Hh.run_oracle(oracle, cam, g, bg, D)["fwd"]["fragile"]
+    fragile = Hh.run_oracle(oracle, cam, g, bg, D, threads=threads)["fwd"]["fragile"]
     rng = np.random.default_rng(100 + seed)
     dL = rng.normal(size=(3, H, W)).astype(np.float32)
     dL[:, fragile] = 0.0
-    ref = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL)
-    ref64 = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, dtype=np.float64)
+    ref = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, threads=threads)
+    ref64 = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, dtype=np.float64, threads=threads)
 
     rs = Hh.settings_for(cam, bg, D, cuda)
     t = Hh.to_dev(g, cuda, requires_grad=True)
