@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 2
+#define GSR_ABI_VERSION 3
 
 #if defined(__GNUC__)
 #define GSR_API __attribute__((visibility("default")))
@@ -146,6 +146,50 @@ GSR_API int gsr_backward(int P, int D, int M, int width, int height, const float
                  const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
                  float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots, void* stream,
                  int debug);
+
+/* ---- Gaussian-sharded multi-view entries (no reference equivalent: the reference is single-GPU,
+ * utils/general_utils.py:133).  With N ranks, rank r owns the parameter rows of slice r and renders
+ * view r.  Forward: every rank runs gsr_preprocess_slots for each of the N cameras over ITS slice,
+ * the per-Gaussian geometry rows (depths, means2D, conic_opacity, rgb, tiles_touched, radii) are
+ * exchanged all-to-all (52 B per Gaussian and view instead of 236 B of parameter gradients), then
+ * gsr_depth_order + gsr_forward_render run on the assembled full-P geometry workspace.  Backward:
+ * gsr_blend_backward fills grad_accum[P,12] of the rendered view, its slices are exchanged back
+ * all-to-all (48 B per Gaussian), and gsr_preprocess_backward_slots turns each view's accumulators
+ * of the slice into parameter gradients, summed over the views.  The arithmetic per (view, Gaussian)
+ * is exactly that of gsr_forward_geometry / gsr_backward.
+ *
+ * `geom_ws` is a geometry workspace laid out for `P_ws` rows (gsr_workspace_layout(P_ws, ...));
+ * the call touches rows [slot_offset, slot_offset + Ps) of its per-Gaussian arrays.  Parameter
+ * pointers address the Ps rows of the slice; slot_offset must be a multiple of 4. */
+GSR_API int gsr_preprocess_slots(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                         const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* opacities, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                         const float* projmatrix, const float* campos, float tanfovx, float tanfovy,
+                         int32_t* radii_slots, void* geom_ws, void* stream, int debug);
+
+/* Depth-order sort + prefix sum over a geometry workspace whose per-Gaussian arrays are already
+ * filled (second half of gsr_forward_geometry).  num_visible of the info block is not maintained. */
+GSR_API int gsr_depth_order(int P, int width, int height, void* geom_ws, gsr_forward_info* h_info,
+                            void* stream, int debug);
+
+/* First half of gsr_backward: dL/dpixel -> grad_accum[P,12] of the geometry workspace. */
+GSR_API int gsr_blend_backward(int P, int width, int height, const float* bg, void* geom_ws,
+                               void* binning_ws, int64_t instance_capacity, void* image_ws,
+                               const float* dL_dpix, void* stream, int debug);
+
+/* Second half of gsr_backward over rows [slot_offset, slot_offset + Ps) of a P_ws-row geometry
+ * workspace (conic_opacity, rgb, grad_accum) and `radii_slots` (Ps rows).  dL_dmeans2D (Ps rows,
+ * per view) is always overwritten; with accumulate != 0 the parameter gradients are ADDED to the
+ * output arrays (rows the view does not see are left untouched), otherwise overwritten in full. */
+GSR_API int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int D, int M, int width,
+                         int height, const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                         const float* campos, float tanfovx, float tanfovy, const int32_t* radii_slots,
+                         void* geom_ws, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                         float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                         float* dL_drots, int accumulate, void* stream, int debug);
 
 /* Replaces `_C.mark_visible`: present[i] = 1 iff Gaussian i passes the near-plane test. */
 GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -31,6 +31,7 @@ EXPORTS = (
     "gsr_workspace_layout", "gsr_forward_geometry", "gsr_forward_render", "gsr_backward",
     "gsr_mark_visible", "gsr_launch_count", "gsr_stage_count", "gsr_stage_name",
     "gsr_stage_timing_enable", "gsr_stage_timing_read", "gsr_blend_pair_counts",
+    "gsr_preprocess_slots", "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots",
 )
 
 
@@ -126,6 +127,22 @@ def lib() -> ctypes.CDLL:
             _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{means2D,colors,opacity,means3D,cov3D,sh,scales,rots}
             _vp, _i]                     # stream debug
         L.gsr_mark_visible.argtypes = [_i, _vp, _vp, _vp, _vp, _vp]
+        L.gsr_preprocess_slots.argtypes = [
+            _i, _i, _i, _i, _i, _i, _i,  # P_ws slot_offset Ps D M W H
+            _vp, _vp, _vp, _vp,          # means3D shs colors_precomp opacities (slice rows)
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _vp, _vp, _vp, _f, _f,       # view proj campos tanfovx tanfovy
+            _vp, _vp, _vp, _i]           # radii_slots geom_ws stream debug
+        L.gsr_depth_order.argtypes = [_i, _i, _i, _vp, _vp, _vp, _i]  # P W H geom_ws h_info stream debug
+        L.gsr_blend_backward.argtypes = [_i, _i, _i, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i]
+        L.gsr_preprocess_backward_slots.argtypes = [
+            _i, _i, _i, _i, _i, _i, _i,  # P_ws slot_offset Ps D M W H
+            _vp, _vp, _vp,               # means3D shs colors_precomp (slice rows)
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _vp, _vp, _vp, _f, _f, _vp,  # view proj campos tanfovx tanfovy radii_slots
+            _vp,                         # geom_ws
+            _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{means2D,colors,opacity,means3D,cov3D,sh,scales,rots}
+            _i, _vp, _i]                 # accumulate stream debug
         L.gsr_blend_pair_counts.argtypes = [_i, _i, _i, _vp, _vp, _i64, _vp, _vp, _vp]
         L.gsr_blend_pair_counts.restype = _i
         L.gsr_stage_count.restype = _i
@@ -136,7 +153,8 @@ def lib() -> ctypes.CDLL:
         L.gsr_stage_timing_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(_i64), _i]
         L.gsr_stage_timing_read.restype = _i
         for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",
-                     "gsr_forward_render", "gsr_backward", "gsr_mark_visible"):
+                     "gsr_forward_render", "gsr_backward", "gsr_mark_visible", "gsr_preprocess_slots",
+                     "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots"):
             getattr(L, name).restype = _i
         _lib = L
     return _lib

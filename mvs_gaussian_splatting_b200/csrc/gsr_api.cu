@@ -312,7 +312,104 @@ int gsr_backward(int P, int D, int M, int width, int height, const float* bg, co
     return launch_preprocess_backward(P, D, M, g, means3D, shs, colors_precomp != nullptr, scales, scale_modifier,
                                       rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
                                       radii, gv, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-                                      dL_dsh, dL_dscales, dL_drots, s, debug);
+                                      dL_dsh, dL_dscales, dL_drots, 0, s, debug);
+}
+
+// ---- Gaussian-sharded multi-view entries ---------------------------------------------------
+static int check_slots(int P_ws, int slot_offset, int Ps) {
+    if (P_ws < 0 || Ps < 0 || slot_offset < 0 || (int64_t)slot_offset + Ps > P_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (slot_offset & 3) return GSR_ERR_INVALID_ARGUMENT;  // keeps the 16-byte row alignment of every array
+    return GSR_OK;
+}
+
+int gsr_preprocess_slots(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                         const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* opacities, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                         const float* projmatrix, const float* campos, float tanfovx, float tanfovy,
+                         int32_t* radii_slots, void* geom_ws, void* stream, int debug) {
+    int st = check_dims(P_ws, width, height, 0);
+    if (st == GSR_OK) st = check_slots(P_ws, slot_offset, Ps);
+    if (st != GSR_OK) return st;
+    if (Ps == 0) return GSR_OK;
+    if (!geom_ws || !aligned16(geom_ws)) return GSR_ERR_WORKSPACE;
+    if (!means3D || !opacities || !radii_slots || !viewmatrix || !projmatrix || !campos) return GSR_ERR_INVALID_ARGUMENT;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
+    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+        !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
+        return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P_ws, width, height, 0, &L);
+    const GeomView gv = offset_rows(geom_view(geom_ws, L), (size_t)slot_offset);
+    return launch_preprocess(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp, opacities, scales,
+                             scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx,
+                             tanfovy, radii_slots, gv, static_cast<cudaStream_t>(stream), debug);
+}
+
+int gsr_depth_order(int P, int width, int height, void* geom_ws, gsr_forward_info* h_info, void* stream,
+                    int debug) {
+    int st = check_dims(P, width, height, 0);
+    if (st != GSR_OK) return st;
+    if (!geom_ws || !aligned16(geom_ws)) return GSR_ERR_WORKSPACE;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    gsr_layout L;
+    compute_layout(P, width, height, 0, &L);
+    GeomView gv = geom_view(geom_ws, L);
+    GSR_CUDA(cudaMemsetAsync(gv.info, 0, sizeof(gsr_forward_info), s));
+    if (P > 0) {
+        st = launch_depth_order(P, gv, s, debug);
+        if (st != GSR_OK) return st;
+    }
+    if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));
+    return GSR_OK;
+}
+
+int gsr_blend_backward(int P, int width, int height, const float* bg, void* geom_ws, void* binning_ws,
+                       int64_t instance_capacity, void* image_ws, const float* dL_dpix, void* stream, int debug) {
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    if (P == 0) return GSR_OK;
+    if (!geom_ws || !image_ws || !binning_ws || !aligned16(geom_ws) || !aligned16(image_ws) || !aligned16(binning_ws))
+        return GSR_ERR_WORKSPACE;
+    if (!bg || !dL_dpix) return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P, width, height, instance_capacity, &L);
+    return launch_blend_backward(P, make_grid(width, height), bg, geom_view(geom_ws, L), bin_view(binning_ws, L),
+                                 image_view(image_ws, L), dL_dpix, static_cast<cudaStream_t>(stream), debug);
+}
+
+int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                                  const float* means3D, const float* shs, const float* colors_precomp,
+                                  const float* scales, float scale_modifier, const float* rotations,
+                                  const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                                  const float* campos, float tanfovx, float tanfovy, const int32_t* radii_slots,
+                                  void* geom_ws, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                                  float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                                  float* dL_drots, int accumulate, void* stream, int debug) {
+    int st = check_dims(P_ws, width, height, 0);
+    if (st == GSR_OK) st = check_slots(P_ws, slot_offset, Ps);
+    if (st != GSR_OK) return st;
+    if (Ps == 0) return GSR_OK;
+    if (!geom_ws || !aligned16(geom_ws)) return GSR_ERR_WORKSPACE;
+    if (!means3D || !viewmatrix || !projmatrix || !campos || !radii_slots || !dL_dmeans2D || !dL_dopacity || !dL_dmeans3D)
+        return GSR_ERR_INVALID_ARGUMENT;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
+    if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
+    if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P_ws, width, height, 0, &L);
+    const GeomView gv = offset_rows(geom_view(geom_ws, L), (size_t)slot_offset);
+    return launch_preprocess_backward(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp != nullptr,
+                                      scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix,
+                                      campos, tanfovx, tanfovy, radii_slots, gv, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                                      dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots, accumulate != 0,
+                                      static_cast<cudaStream_t>(stream), debug);
 }
 
 int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,

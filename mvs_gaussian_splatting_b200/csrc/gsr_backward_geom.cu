@@ -21,6 +21,7 @@ constexpr int kShStride = 49;
 
 struct BwdParams {
     int P, D, M, W, H;
+    int accumulate;  // parameter gradients are added to the outputs (rows the view does not see: untouched)
     const float* means3D;
     const float* shs;
     int colors_precomp;
@@ -339,24 +340,38 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
         for (int k = 0; k < row; ++k) rowp[k] = 0.f;
     }
 
-    // ---- outputs (every row written) ----
+    // ---- outputs (every row written; in accumulate mode rows of this view's culled Gaussians are skipped) ----
+    const bool acc = p.accumulate != 0;
     if (valid) {
         const size_t i = (size_t)idx;
         p.dL_dmeans2D[3 * i] = g2d[0]; p.dL_dmeans2D[3 * i + 1] = g2d[1]; p.dL_dmeans2D[3 * i + 2] = 0.f;
-        p.dL_dopacity[i] = gop;
-        p.dL_dmeans3D[3 * i] = gm[0]; p.dL_dmeans3D[3 * i + 1] = gm[1]; p.dL_dmeans3D[3 * i + 2] = gm[2];
-        if (p.dL_dcolors) { p.dL_dcolors[3 * i] = gcol[0]; p.dL_dcolors[3 * i + 1] = gcol[1]; p.dL_dcolors[3 * i + 2] = gcol[2]; }
-        if (p.dL_dcov3D) {
-            float2* o = reinterpret_cast<float2*>(p.dL_dcov3D) + 3 * i;
-            o[0] = make_float2(gc[0], gc[1]); o[1] = make_float2(gc[2], gc[3]); o[2] = make_float2(gc[4], gc[5]);
+    }
+    if (valid && (!acc || vis)) {
+        const size_t i = (size_t)idx;
+        auto put = [acc](float* a, float v) { *a = acc ? *a + v : v; };
+        put(p.dL_dopacity + i, gop);
+        put(p.dL_dmeans3D + 3 * i, gm[0]); put(p.dL_dmeans3D + 3 * i + 1, gm[1]); put(p.dL_dmeans3D + 3 * i + 2, gm[2]);
+        if (p.dL_dcolors) {
+            put(p.dL_dcolors + 3 * i, gcol[0]); put(p.dL_dcolors + 3 * i + 1, gcol[1]); put(p.dL_dcolors + 3 * i + 2, gcol[2]);
         }
-        if (p.dL_dscales) { p.dL_dscales[3 * i] = gs[0]; p.dL_dscales[3 * i + 1] = gs[1]; p.dL_dscales[3 * i + 2] = gs[2]; }
-        if (p.dL_drots) reinterpret_cast<float4*>(p.dL_drots)[i] = make_float4(gq[0], gq[1], gq[2], gq[3]);
+        if (p.dL_dcov3D) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) put(p.dL_dcov3D + 6 * i + k, gc[k]);
+        }
+        if (p.dL_dscales) {
+            put(p.dL_dscales + 3 * i, gs[0]); put(p.dL_dscales + 3 * i + 1, gs[1]); put(p.dL_dscales + 3 * i + 2, gs[2]);
+        }
+        if (p.dL_drots) {
+            float4* o = reinterpret_cast<float4*>(p.dL_drots) + i;
+            float4 v = make_float4(gq[0], gq[1], gq[2], gq[3]);
+            if (acc) { const float4 old = *o; v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w; }
+            *o = v;
+        }
     }
     if (p.dL_dsh) {
         if (p.colors_precomp) {
             // SH not in use: the gradient is identically zero
-            if (valid) for (int k = 0; k < row; ++k) p.dL_dsh[(size_t)idx * row + k] = 0.f;
+            if (valid && !acc) for (int k = 0; k < row; ++k) p.dL_dsh[(size_t)idx * row + k] = 0.f;
         } else {
             __syncwarp();
             const int nrows = min(32, p.P - warp_base);
@@ -369,12 +384,23 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
                     for (int j = lane; j < total; j += 32) {
                         const int r = j / vpr, part = j - r * vpr;
                         const float* sp = tile + r * kShStride + 4 * part;
-                        __stcs(reinterpret_cast<float4*>(dst) + j, make_float4(sp[0], sp[1], sp[2], sp[3]));
+                        float4 v = make_float4(sp[0], sp[1], sp[2], sp[3]);
+                        float4* o = reinterpret_cast<float4*>(dst) + j;
+                        if (acc) {
+                            if (!((vmask >> r) & 1u)) continue;
+                            const float4 old = *o;
+                            v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
+                        }
+                        __stcs(o, v);
                     }
                 } else {
                     for (int j = lane; j < nrows * row; j += 32) {
                         const int r = j / row, part = j - r * row;
-                        dst[j] = tile[r * kShStride + part];
+                        if (acc) {
+                            if ((vmask >> r) & 1u) dst[j] += tile[r * kShStride + part];
+                        } else {
+                            dst[j] = tile[r * kShStride + part];
+                        }
                     }
                 }
             }
@@ -390,8 +416,9 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                const float* proj, const float* campos, float tanfovx, float tanfovy,
                                const int32_t* radii, GeomView gv, float* dL_dmeans2D, float* dL_dcolors,
                                float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscales, float* dL_drots, cudaStream_t s, int debug) {
+                               float* dL_dscales, float* dL_drots, int accumulate, cudaStream_t s, int debug) {
     BwdParams p;
+    p.accumulate = accumulate;
     p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H;
     p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
     p.scale_modifier = scale_modifier; p.rotations = rotations; p.cov3D_precomp = cov3D_precomp;

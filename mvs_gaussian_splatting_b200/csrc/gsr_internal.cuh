@@ -98,6 +98,13 @@ struct ImageView {
     float* final_T;
     uint32_t* n_contrib;
 };
+// View of rows [r, ...) of the per-Gaussian arrays (slot addressing of the sharded entries); the
+// sort/scan arrays and the info block are not per-slot and stay where they are.
+inline GeomView offset_rows(GeomView v, size_t r) {
+    v.depths += r; v.means2D += r; v.conic_opacity += r; v.rgb += r; v.tiles_touched += r;
+    v.grad_accum += 12 * r;
+    return v;
+}
 void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L);
 GeomView geom_view(void* ws, const gsr_layout& L);
 BinView bin_view(void* ws, const gsr_layout& L);
@@ -141,7 +148,7 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                const int32_t* radii, GeomView gv, float* dL_dmeans2D,
                                float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots,
-                               cudaStream_t s, int debug);
+                               int accumulate, cudaStream_t s, int debug);
 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);

@@ -149,6 +149,45 @@ def _settings_tensors(rs: GaussianRasterizationSettings, device):
     return view, proj, campos, bg
 
 
+def _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev_idx, stream, debug):
+    """Binning + blend for a geometry workspace whose depth order is queued on `stream` and whose
+    info block is being copied to the pinned `info` row 0.  Speculates on the instance capacity
+    (see rasterize_forward) and re-runs only this stage on overflow.  Must run inside
+    torch.cuda.device(device)."""
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(device))
+
+    speculative = capacity is None and dev_idx in _capacity_hint
+    if capacity is None:
+        if speculative:
+            capacity = _capacity_hint[dev_idx]
+        else:
+            ev.synchronize()           # first call on this device: size exactly, like the reference
+            capacity = int(info[0, 0])
+    capacity = max(int(capacity), 1)
+
+    def render(cap):
+        _, bb, _ = _native.workspace_bytes(P, W, H, cap)
+        ctx.binning_ws = torch.empty(bb, dtype=torch.uint8, device=device)
+        ctx.capacity = cap
+        _native.check(L.gsr_forward_render(
+            P, W, H, _ptr(bg), _ptr(radii), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws), cap,
+            _ptr(ctx.image_ws), _ptr(color), None, stream, debug), "gsr_forward_render")
+
+    render(capacity)
+    ev.synchronize()                   # waits for the geometry stage only; blend keeps running
+    R, nvis = int(info[0, 0]), int(info[0, 2])
+    if R > capacity:
+        ctx.reruns = 1
+        render(R + R // 8 + 1024)
+    ctx.num_rendered, ctx.num_visible, ctx.radii = R, nvis, radii
+    # speculate next time with 25% head-room over the largest recent count
+    prev = _capacity_hint.get(dev_idx, 0)
+    _capacity_hint[dev_idx] = max(int(prev * 0.97), R + R // 4 + 4096)
+    _last_stats[dev_idx] = dict(num_rendered=R, num_visible=nvis, capacity=ctx.capacity,
+                                reruns=ctx.reruns, speculative=bool(speculative))
+
+
 def rasterize_forward(means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                       raster_settings: GaussianRasterizationSettings, capacity: Optional[int] = None):
     """Forward through the C ABI.  Returns (color[3,H,W], radii[P] int32, RasterContext).
@@ -196,38 +235,7 @@ def rasterize_forward(means3D, shs, colors_precomp, opacities, scales, rotations
             _ptr(scales), float(rs.scale_modifier), _ptr(rotations), _ptr(cov3D_precomp), _ptr(view),
             _ptr(proj), _ptr(campos), float(rs.tanfovx), float(rs.tanfovy), 1 if rs.prefiltered else 0,
             _ptr(radii), _ptr(ctx.geom_ws), info_p0, stream, debug), "gsr_forward_geometry")
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(device))
-
-        speculative = capacity is None and dev_idx in _capacity_hint
-        if capacity is None:
-            if speculative:
-                capacity = _capacity_hint[dev_idx]
-            else:
-                ev.synchronize()           # first call on this device: size exactly, like the reference
-                capacity = int(info[0, 0])
-        capacity = max(int(capacity), 1)
-
-        def render(cap):
-            _, bb, _ = _native.workspace_bytes(P, W, H, cap)
-            ctx.binning_ws = torch.empty(bb, dtype=torch.uint8, device=device)
-            ctx.capacity = cap
-            _native.check(L.gsr_forward_render(
-                P, W, H, _ptr(bg), _ptr(radii), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws), cap,
-                _ptr(ctx.image_ws), _ptr(color), None, stream, debug), "gsr_forward_render")
-
-        render(capacity)
-        ev.synchronize()                   # waits for the geometry stage only; blend keeps running
-        R, nvis = int(info[0, 0]), int(info[0, 2])
-        if R > capacity:
-            ctx.reruns = 1
-            render(R + R // 8 + 1024)
-        ctx.num_rendered, ctx.num_visible, ctx.radii = R, nvis, radii
-        # speculate next time with 25% head-room over the largest recent count
-        prev = _capacity_hint.get(dev_idx, 0)
-        _capacity_hint[dev_idx] = max(int(prev * 0.97), R + R // 4 + 4096)
-        _last_stats[dev_idx] = dict(num_rendered=R, num_visible=nvis, capacity=ctx.capacity,
-                                    reruns=ctx.reruns, speculative=bool(speculative))
+        _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev_idx, stream, debug)
     ctx_inputs = (means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, view, proj, campos, bg)
     return color, radii, ctx, ctx_inputs
 

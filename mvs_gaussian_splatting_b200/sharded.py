@@ -1,0 +1,222 @@
+"""Gaussian-sharded multi-view step: N ranks, rank r owns parameter slice r and renders view r.
+
+Why.  Replicated-parameter data parallelism (multiview.py) must all-reduce 59 floats = 236 B per
+Gaussian and step; at 3 M Gaussians that is 708 MB against a 2.3 ms step (measured: 1.3 ms at 2
+GPUs, 63 % scaling).  Nothing downstream of `preprocess` reads raw parameters until
+`preprocess_backward`, and both are per-Gaussian.  So the Gaussians are sharded for those two
+stages and the views for everything between them:
+
+    forward   rank r: preprocess(slice r, camera v) for v = 0..N-1   -> geometry rows of slice r per view
+              all-to-all of geometry rows (depths, means2D, conic_opacity, rgb, tiles_touched, radii:
+              52 B per Gaussian and view)                             -> full-P geometry of view r
+              depth order, binning, blend of view r                   (unchanged kernels)
+    backward  blend backward of view r                                -> grad_accum[P,12] of view r
+              all-to-all of grad_accum slices (48 B per Gaussian)     -> accumulators of slice r, all views
+              preprocess_backward(slice r, camera v), summed over v   -> parameter gradients of slice r
+
+Per rank and step 100 B x P x (N-1)/N cross NVLink instead of ~2 x 236 B x P x (N-1)/N, no rank
+holds more than its slice of parameters, gradients and optimizer state, and the per-(view, Gaussian)
+arithmetic is exactly that of the single-GPU path (same kernels, row offsets only), so images,
+radii, key lists and per-view gradients are unchanged; the sum over views runs in view order.
+
+`ShardPlan` and `all_to_all_rows` are device-agnostic (exercised on CPU with gloo in
+tests/test_sharded_gloo.py); `ShardedViewRasterizer` drives the C ABI and needs CUDA.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+from .rasterizer import (GaussianRasterizationSettings, RasterContext, _dense, _pinned_info, _ptr, _render_stage,
+                         _settings_tensors)
+
+__all__ = ["ShardPlan", "all_to_all_rows", "ShardedViewRasterizer", "GEOMETRY_ARRAYS"]
+
+SLICE_ALIGN = 128  # rows; keeps every per-Gaussian array of a slice 16-byte aligned (needs a multiple of 4)
+
+# per-Gaussian arrays of the geometry workspace that travel in the forward exchange
+GEOMETRY_ARRAYS = ("depths", "means2D", "conic_opacity", "rgb", "tiles_touched")
+
+
+class ShardPlan:
+    """Contiguous slices of P Gaussians over `world` ranks; every slice but the last is a multiple of
+    SLICE_ALIGN rows, so global index order is slice order (the depth sort's tie-break stays by index)."""
+
+    def __init__(self, P: int, world: int):
+        if P < 0 or world < 1:
+            raise ValueError("P >= 0 and world >= 1 required")
+        per = -(-P // world)
+        per = -(-per // SLICE_ALIGN) * SLICE_ALIGN
+        self.P, self.world = P, world
+        self.starts = [min(P, r * per) for r in range(world)]
+        self.sizes = [min(P, (r + 1) * per) - self.starts[r] for r in range(world)]
+
+    def rows(self, rank: int) -> slice:
+        return slice(self.starts[rank], self.starts[rank] + self.sizes[rank])
+
+    def slot_stride(self, rank: int) -> int:
+        """Row stride between the per-view slots of rank's send workspace."""
+        return max(SLICE_ALIGN, -(-self.sizes[rank] // SLICE_ALIGN) * SLICE_ALIGN)
+
+
+def all_to_all_rows(pairs: Sequence, group=None) -> None:
+    """pairs = [(send_views, recv_views), ...]; for each pair send_views[j] goes to rank j and
+    recv_views[j] is filled from rank j (contiguous tensors, sizes agreed by construction).  All
+    arrays travel in ONE batched group of point-to-point operations (one NCCL launch); the local
+    chunk is a device copy.  Empty chunks are skipped on both sides."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    ops = []
+    for send, recv in pairs:
+        if len(send) != world or len(recv) != world:
+            raise ValueError("one send and one receive view per rank required")
+        recv[rank].copy_(send[rank])
+        for j in range(world):
+            if j == rank:
+                continue
+            peer = dist.get_global_rank(group, j) if group is not None else j
+            if send[j].numel():
+                ops.append(dist.P2POp(dist.isend, send[j], peer, group))
+            if recv[j].numel():
+                ops.append(dist.P2POp(dist.irecv, recv[j], peer, group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+
+def _ws_arrays(ws: torch.Tensor, L: _native.Layout, P: int) -> Dict[str, torch.Tensor]:
+    """Typed [P, k] views of the per-Gaussian arrays of a geometry workspace."""
+    def v(off, dt, k):
+        n = P * k * 4
+        return ws[off:off + n].view(dt).view(P, k)
+    return dict(depths=v(L.g_depths, torch.float32, 1), means2D=v(L.g_means2D, torch.float32, 2),
+                conic_opacity=v(L.g_conic_opacity, torch.float32, 4), rgb=v(L.g_rgb, torch.float32, 4),
+                tiles_touched=v(L.g_tiles_touched, torch.int32, 1), grad_accum=v(L.g_grad_accum, torch.float32, 12))
+
+
+class ShardedViewRasterizer:
+    """One instance per rank.  `forward` takes THIS rank's parameter slice and the N cameras of the
+    step and returns the image and radii of view `rank`; `backward` takes dL/dpixel of that image and
+    returns the parameter gradients of the slice summed over all N views, plus the per-view
+    dL/dmeans2D rows of the slice ([N, Ps, 3], for the densification statistics of
+    scene/gaussian_model.py:775-777).  SH + scale/rotation inputs (the training configuration)."""
+
+    def __init__(self, P: int, M: int, width: int, height: int, device, group=None):
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("torch.distributed must be initialised (one process per GPU)")
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.P, self.M, self.W, self.H = P, M, width, height
+        self.plan = ShardPlan(P, self.world)
+        self.Ps = self.plan.sizes[self.rank]
+        self.stride = self.plan.slot_stride(self.rank)
+        self.P_send = self.world * self.stride
+        self.lib = _native.lib()
+        dev = self.device
+        gb_send, _, _ = _native.workspace_bytes(self.P_send, width, height, 0)
+        self.send_ws = torch.empty(gb_send, dtype=torch.uint8, device=dev)
+        self.send_radii = torch.zeros(self.P_send, dtype=torch.int32, device=dev)
+        self.L_send = _native.workspace_layout(self.P_send, width, height, 0)
+        self.send = _ws_arrays(self.send_ws, self.L_send, self.P_send)
+        self.L_full = _native.workspace_layout(P, width, height, 0)
+        # parameter gradients of the slice (summed over views) and per-view dL/dmeans2D
+        f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        Ps = max(self.Ps, 1)
+        self.grads = dict(means3D=f(Ps, 3), shs=f(Ps, M, 3), opacities=f(Ps, 1), scales=f(Ps, 3), rotations=f(Ps, 4))
+        self.grad_means2D = f(self.world, Ps, 3)
+        self._state = None
+
+    # ------------------------------------------------------------------------------------------
+    def _slot(self, v: int) -> slice:
+        return slice(v * self.stride, v * self.stride + self.Ps)
+
+    def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
+        """params: means3D [Ps,3], shs [Ps,M,3], opacities [Ps,1], scales [Ps,3], rotations [Ps,4] of
+        slice `rank` (ShardPlan.rows).  cameras[v]: settings of view v (same image size, sh_degree,
+        scale_modifier on every rank).  Returns (color [3,H,W], radii [P] int32 of view `rank`)."""
+        N, r, dev, L = self.world, self.rank, self.device, self.lib
+        if len(cameras) != N:
+            raise ValueError("one camera per rank required")
+        P, Ps, W, H, M = self.P, self.Ps, self.W, self.H, self.M
+        rs = cameras[r]
+        if int(rs.image_width) != W or int(rs.image_height) != H:
+            raise ValueError("camera image size does not match this rasterizer")
+        p = {k: _dense(params[k], dev) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        if Ps and (p["means3D"] is None or p["means3D"].shape[0] != Ps or p["shs"].shape[1] != M):
+            raise ValueError("parameter slice does not match ShardPlan.rows(rank)")
+        debug = 1 if rs.debug else 0
+        D = int(rs.sh_degree)
+        cams = [_settings_tensors(c, dev) for c in cameras]   # (view, proj, campos, bg) per view
+        dev_idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        ctx = RasterContext()
+        ctx.P, ctx.D, ctx.M, ctx.W, ctx.H, ctx.reruns = P, D, M, W, H, 0
+        with torch.cuda.device(dev):
+            stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            gb, _, ib = _native.workspace_bytes(P, W, H, 0)
+            ctx.geom_ws = torch.empty(gb, dtype=torch.uint8, device=dev)
+            ctx.image_ws = torch.empty(ib, dtype=torch.uint8, device=dev)
+            radii = torch.empty(P, dtype=torch.int32, device=dev)
+            color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+            full = _ws_arrays(ctx.geom_ws, self.L_full, P)
+            for v in range(N):
+                view, proj, campos, _ = cams[v]
+                c = cameras[v]
+                _native.check(L.gsr_preprocess_slots(
+                    self.P_send, v * self.stride, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None,
+                    _ptr(p["opacities"]), _ptr(p["scales"]), float(c.scale_modifier), _ptr(p["rotations"]), None,
+                    _ptr(view), _ptr(proj), _ptr(campos), float(c.tanfovx), float(c.tanfovy),
+                    ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride), _ptr(self.send_ws),
+                    stream, debug), "gsr_preprocess_slots")
+            pairs = []
+            for name in GEOMETRY_ARRAYS:
+                pairs.append(([self.send[name][self._slot(v)] for v in range(N)],
+                              [full[name][self.plan.rows(j)] for j in range(N)]))
+            pairs.append(([self.send_radii[self._slot(v)] for v in range(N)],
+                          [radii[self.plan.rows(j)] for j in range(N)]))
+            all_to_all_rows(pairs, self.group)
+            info = _pinned_info(dev_idx)
+            _native.check(L.gsr_depth_order(P, W, H, _ptr(ctx.geom_ws), ctypes.c_void_p(info.data_ptr()), stream,
+                                            debug), "gsr_depth_order")
+            bg = cams[r][3]
+            _render_stage(L, ctx, P, W, H, bg, radii, color, info, None, dev, dev_idx, stream, debug)
+        self._state = (ctx, p, cams, [(float(c.scale_modifier), float(c.tanfovx), float(c.tanfovy)) for c in cameras],
+                       D, debug, full)
+        return color, radii
+
+    def backward(self, dL_dpix: torch.Tensor):
+        """Returns (grads, grad_means2D): grads[name] = dL/d(parameter rows of this slice) summed over
+        the N views (buffers owned by this object, overwritten by the next call); grad_means2D [N,Ps,3]."""
+        if self._state is None:
+            raise RuntimeError("backward() needs a preceding forward()")
+        ctx, p, cams, scal, D, debug, full = self._state
+        N, r, dev, L = self.world, self.rank, self.device, self.lib
+        P, Ps, W, H, M = self.P, self.Ps, self.W, self.H, self.M
+        g = _dense(dL_dpix, dev)
+        if g is None or tuple(g.shape) != (3, H, W):
+            raise RuntimeError("dL_dpix must be [3,H,W]")
+        with torch.cuda.device(dev):
+            stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            _native.check(L.gsr_blend_backward(P, W, H, _ptr(cams[r][3]), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws),
+                                               ctx.capacity, _ptr(ctx.image_ws), _ptr(g), stream, debug),
+                          "gsr_blend_backward")
+            all_to_all_rows([([full["grad_accum"][self.plan.rows(j)] for j in range(N)],
+                              [self.send["grad_accum"][self._slot(v)] for v in range(N)])], self.group)
+            G = self.grads
+            for v in range(N):
+                view, proj, campos, _ = cams[v]
+                mod, tfx, tfy = scal[v]
+                _native.check(L.gsr_preprocess_backward_slots(
+                    self.P_send, v * self.stride, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None,
+                    _ptr(p["scales"]), mod, _ptr(p["rotations"]), None, _ptr(view), _ptr(proj), _ptr(campos), tfx, tfy,
+                    ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride), _ptr(self.send_ws),
+                    _ptr(self.grad_means2D[v]), None, _ptr(G["opacities"]), _ptr(G["means3D"]), None, _ptr(G["shs"]),
+                    _ptr(G["scales"]), _ptr(G["rotations"]), 1 if v > 0 else 0, stream, debug),
+                    "gsr_preprocess_backward_slots")
+        return G, self.grad_means2D
