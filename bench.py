@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--multi", default="sharded", choices=["sharded", "sharded-nccl", "allreduce"],
+                    help="N > 1: 'sharded' = Gaussian-sharded step (all-to-all of 100 B/Gaussian), "
+                         "'allreduce' = replicated parameters + one 236 B/Gaussian gradient all-reduce")
     ap.add_argument("--cpu-budget-s", type=float, default=200.0,
                     help="--impl reference: wall-clock budget the K+W CPU steps are sized for")
     return ap.parse_args()
@@ -302,8 +305,30 @@ def run_b200_arm(args):
     dL_np = rng.normal(size=(3, H, W)).astype(np.float32)
     dL = torch.from_numpy(dL_np).to(dev)
     arena = GradientArena(P, M, dev)
+    sharded = world > 1 and args.multi.startswith("sharded")
+    sr = cams_all = slices = None
+    if sharded:
+        from mvs_gaussian_splatting_b200.sharded import ShardedViewRasterizer
+        sr = ShardedViewRasterizer(P, M, W, H, dev, exchange="nccl" if args.multi == "sharded-nccl" else "peer")
+        rows = sr.plan.rows(rank)
+        slices = {k: t[k][rows].contiguous() for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+        cams_all = []
+        for v in range(world):
+            kv = S.settings_kwargs(bench_camera(v, W, H), [0.0, 0.0, 0.0], D)
+            for k in ("bg", "viewmatrix", "projmatrix", "campos"):
+                kv[k] = torch.from_numpy(np.ascontiguousarray(kv[k])).to(dev)
+            cams_all.append(GaussianRasterizationSettings(**kv))
+        blocks = []
+        for v in range(world):
+            kv = S.settings_kwargs(bench_camera(v, W, H), [0.0, 0.0, 0.0], D)
+            blocks += [kv["viewmatrix"].ravel(), kv["projmatrix"].ravel(), kv["campos"].ravel(), kv["bg"].ravel()]
+        cam_host_all = torch.from_numpy(np.concatenate(blocks).astype(np.float32)).pin_memory()
 
     def step():
+        if sharded:
+            sr.forward(slices, cams_all)
+            sr.backward(dL)
+            return sr._state[0]
         color, radii, ctx, inp = rasterize_forward(t["means3D"], t["shs"], None, t["opacities"], t["scales"],
                                                    t["rotations"], None, rs)
         rasterize_backward(ctx, inp, rs, dL, arena=arena)
@@ -347,10 +372,12 @@ def run_b200_arm(args):
     st = last_forward_stats(dev)
     ev, bl, ev_ours, warp_iters = blend_pair_counts(ctx)
     gx, gy = (W + 15) // 16, (H + 15) // 16
+    if sharded:
+        st["num_visible"] = int((ctx.radii > 0).sum().item())
     counts = dict(P=P, P_visible=st["num_visible"], R=st["num_rendered"], tiles=gx * gy, pairs_evaluated=ev,
                   pairs_blended=bl, pairs_evaluated_after_culling=ev_ours, warp_splat_iterations=warp_iters,
                   sum_n_contrib=int(ctx.array("n_contrib").long().sum().item()))
-    stage_ms = {k: v[0] / max(v[1], 1) for k, v in stages.items() if v[1]}
+    stage_ms = {k: v[0] / max(args.steps, 1) for k, v in stages.items() if v[1]}   # per step (a stage may launch N times)
     peaks = load_peaks()
     roofs = stage_rooflines(stage_ms, counts, peaks, clocks)
     traffic = load_traffic()
@@ -359,7 +386,8 @@ def run_b200_arm(args):
     dominant = max(stage_ms, key=stage_ms.get)
 
     # ---- e2e: the public autograd API with host-side per-step inputs ----
-    e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer)
+    e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer,
+                  sharded=(sr, slices, rank, cam_host_all) if sharded else None)
     e2e_hp = run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward,
                                  arena) if world == 1 else None
 
@@ -368,7 +396,9 @@ def run_b200_arm(args):
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, 1 view per GPU per step"
-                               + (", + NCCL all-reduce of 59 f32/Gaussian gradients" if world > 1 else ""),
+                               + (f", Gaussian-sharded ({sr.exchange} exchange): all-to-all of 52 B (fwd) + 48 B (bwd) per Gaussian and view, "
+                                  "gradients of each rank's parameter slice summed over the views" if sharded else
+                                  ", + NCCL all-reduce of 59 f32/Gaussian gradients" if world > 1 else ""),
                    "baseline_config": "BASELINE.json configs[2]", "l2": "inputs (708 MB) larger than L2, no flush",
                    "parallelism": f"views x{world}", "counts": counts},
         "gpu_launches": int(launches),
@@ -403,7 +433,7 @@ def cpu_baseline(g, cam, D, dL_np, budget_s=30.0):
             "ms_per_view": 1e3 * t}
 
 
-def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer):
+def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer, sharded=None):
     """The call a user of the reference makes (gaussian_renderer/__init__.py:257-265 + train.py:95-113):
     per step the camera block and the ground-truth image come from PINNED HOST memory, the image is
     rendered through GaussianRasterizer (autograd), an L1 loss is formed, backward() runs, and the
@@ -412,6 +442,10 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     H, W = args.height, args.width
     gt_host = torch.from_numpy((0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)).pin_memory()
     params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    if sharded is not None:
+        # Gaussian-sharded step: the host block carries the cameras of ALL N views of the step (38 floats each)
+        sr, slices, my_rank, cam_host = sharded
+        params = None
 
     # Per-step host inputs are prefetched one step ahead on a copy stream (double-buffered), as a data
     # loader does; the loss is copied to pinned memory asynchronously and read one step late, so the
@@ -438,16 +472,23 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         sl = slots[state["k"] & 1]
         prefetch(slots[(state["k"] + 1) & 1])           # next step's inputs travel while this step computes
         main.wait_event(sl["ready"])
-        rs = settings_from(sl["block"])
-        means2D = torch.zeros_like(params["means3D"], requires_grad=True)
-        color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
-                                              opacities=params["opacities"], scales=params["scales"],
-                                              rotations=params["rotations"])
-        loss = (color - sl["gt"]).abs().mean()
-        loss.backward()
-        if world > 1:
-            for p in params.values():
-                dist.all_reduce(p.grad)
+        if sharded is not None:
+            cams = [settings_from(sl["block"][38 * v:38 * v + 38]) for v in range(world)]
+            color, radii = sr.forward(slices, cams)
+            diff = color - sl["gt"]
+            loss = diff.abs().mean()
+            sr.backward(torch.sign(diff) / diff.numel())      # dL/dpixel of the L1 loss
+        else:
+            rs = settings_from(sl["block"])
+            means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+            color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
+                                                  opacities=params["opacities"], scales=params["scales"],
+                                                  rotations=params["rotations"])
+            loss = (color - sl["gt"]).abs().mean()
+            loss.backward()
+            if world > 1:
+                for p in params.values():
+                    dist.all_reduce(p.grad)
         sl["loss"].copy_(loss.detach().reshape(1), non_blocking=True)   # D2H read of the step's result
         sl["loss_ready"].record(main)
         sl["free"].record(main)
@@ -457,8 +498,9 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
             val = float(state["pending"]["loss"][0])
         state["pending"] = sl
         state["k"] += 1
-        for p in params.values():
-            p.grad = None                                   # train.py:142 zero_grad(set_to_none=True)
+        if params is not None:
+            for p in params.values():
+                p.grad = None                               # train.py:142 zero_grad(set_to_none=True)
         return val
 
     for _ in range(3):
@@ -480,7 +522,8 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
             "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4,
             "api": "GaussianRasterizer(settings)(...) + L1 loss + backward(), camera + ground-truth image from "
                    "pinned host memory (prefetched one step ahead on a copy stream), loss copied back to pinned "
-                   "memory every step; Gaussian parameters resident in HBM (model state)"}
+                   "memory every step; Gaussian parameters resident in HBM (model state)"
+                   + ("; N > 1: ShardedViewRasterizer.forward/backward on each rank's parameter slice" if sharded else "")}
 
 
 def run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward, arena):

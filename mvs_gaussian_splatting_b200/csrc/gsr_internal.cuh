@@ -103,6 +103,7 @@ struct ImageView {
 inline GeomView offset_rows(GeomView v, size_t r) {
     v.depths += r; v.means2D += r; v.conic_opacity += r; v.rgb += r; v.tiles_touched += r;
     v.grad_accum += 12 * r;
+    v.info = nullptr;  // slot calls do not maintain num_visible (the workspace may be a peer's)
     return v;
 }
 void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L);

@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
             p.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
         }
     }
-    if (lane == 0 && vis) atomicAdd(&p.gv.info->num_visible, __popc(vis));
+    if (lane == 0 && vis && p.gv.info) atomicAdd(&p.gv.info->num_visible, __popc(vis));
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,

@@ -19,6 +19,15 @@ holds more than its slice of parameters, gradients and optimizer state, and the 
 arithmetic is exactly that of the single-GPU path (same kernels, row offsets only), so images,
 radii, key lists and per-view gradients are unchanged; the sum over views runs in view order.
 
+Two transports.  exchange="peer" (default): every rank's geometry workspace lives in symmetric
+memory (torch.distributed._symmetric_memory: peer-mapped over NVLink); the preprocess kernel of rank
+r writes view v's rows STRAIGHT INTO rank v's workspace (remote stores, no staging, no copy kernel)
+and preprocess_backward reads view v's accumulators straight from rank v's workspace (remote loads),
+so each exchange is fused into the kernel that produces / consumes the data; three device-side
+barriers per step order the phases.  exchange="nccl": staged rows + one batched group of NCCL
+point-to-point operations per exchange (measured 0.43 + 0.27 ms at 2 GPUs against 0.17 ms of peer
+copies, hence not the default).
+
 `ShardPlan` and `all_to_all_rows` are device-agnostic (exercised on CPU with gloo in
 tests/test_sharded_gloo.py); `ShardedViewRasterizer` drives the C ABI and needs CUDA.
 """
@@ -98,6 +107,8 @@ def _ws_arrays(ws: torch.Tensor, L: _native.Layout, P: int) -> Dict[str, torch.T
                 tiles_touched=v(L.g_tiles_touched, torch.int32, 1), grad_accum=v(L.g_grad_accum, torch.float32, 12))
 
 
+
+
 class ShardedViewRasterizer:
     """One instance per rank.  `forward` takes THIS rank's parameter slice and the N cameras of the
     step and returns the image and radii of view `rank`; `backward` takes dL/dpixel of that image and
@@ -105,27 +116,43 @@ class ShardedViewRasterizer:
     dL/dmeans2D rows of the slice ([N, Ps, 3], for the densification statistics of
     scene/gaussian_model.py:775-777).  SH + scale/rotation inputs (the training configuration)."""
 
-    def __init__(self, P: int, M: int, width: int, height: int, device, group=None):
+    def __init__(self, P: int, M: int, width: int, height: int, device, group=None, exchange: str = "peer"):
         if not (dist.is_available() and dist.is_initialized()):
             raise RuntimeError("torch.distributed must be initialised (one process per GPU)")
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
-        self.group = group
+        if exchange not in ("peer", "nccl"):
+            raise ValueError("exchange must be 'peer' or 'nccl'")
+        self.group, self.exchange = group, exchange
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.P, self.M, self.W, self.H = P, M, width, height
         self.plan = ShardPlan(P, self.world)
         self.Ps = self.plan.sizes[self.rank]
-        self.stride = self.plan.slot_stride(self.rank)
-        self.P_send = self.world * self.stride
+        self.start = self.plan.starts[self.rank]
         self.lib = _native.lib()
         dev = self.device
-        gb_send, _, _ = _native.workspace_bytes(self.P_send, width, height, 0)
-        self.send_ws = torch.empty(gb_send, dtype=torch.uint8, device=dev)
-        self.send_radii = torch.zeros(self.P_send, dtype=torch.int32, device=dev)
-        self.L_send = _native.workspace_layout(self.P_send, width, height, 0)
-        self.send = _ws_arrays(self.send_ws, self.L_send, self.P_send)
         self.L_full = _native.workspace_layout(P, width, height, 0)
+        self.geom_bytes, _, self.image_bytes = _native.workspace_bytes(P, width, height, 0)
+        if exchange == "peer":
+            import torch.distributed._symmetric_memory as symm_mem
+            self.radii_off = (self.geom_bytes + 255) // 256 * 256
+            nbytes = self.radii_off + 4 * max(P, 1)
+            self.symm = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+            self.hdl = symm_mem.rendezvous(self.symm, group if group is not None else dist.group.WORLD)
+            self.peer_base = [int(x) for x in self.hdl.buffer_ptrs]
+            self.geom_ws = self.symm[:self.geom_bytes]
+            self.radii_ws = self.symm[self.radii_off:self.radii_off + 4 * P].view(torch.int32)
+        else:
+            self.stride = self.plan.slot_stride(self.rank)
+            self.P_send = self.world * self.stride
+            gb_send, _, _ = _native.workspace_bytes(self.P_send, width, height, 0)
+            self.send_ws = torch.empty(gb_send, dtype=torch.uint8, device=dev)
+            self.send_radii = torch.zeros(self.P_send, dtype=torch.int32, device=dev)
+            self.send = _ws_arrays(self.send_ws, _native.workspace_layout(self.P_send, width, height, 0), self.P_send)
+            self.geom_ws = torch.empty(self.geom_bytes, dtype=torch.uint8, device=dev)
+            self.radii_ws = torch.empty(P, dtype=torch.int32, device=dev)
+        self.full = _ws_arrays(self.geom_ws, self.L_full, P)
         # parameter gradients of the slice (summed over views) and per-view dL/dmeans2D
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         Ps = max(self.Ps, 1)
@@ -136,6 +163,19 @@ class ShardedViewRasterizer:
     # ------------------------------------------------------------------------------------------
     def _slot(self, v: int) -> slice:
         return slice(v * self.stride, v * self.stride + self.Ps)
+
+    def _view_order(self):
+        """Views starting at the rank's own, so that at any moment the ranks address different peers."""
+        return [(self.rank + k) % self.world for k in range(self.world)]
+
+    def _target(self, v: int):
+        """(geom_ws pointer, rows in it, first row, radii pointer) a slot call for view v addresses."""
+        if self.exchange == "peer":
+            base = self.peer_base[v]
+            return (ctypes.c_void_p(base), self.P, self.start,
+                    ctypes.c_void_p(base + self.radii_off + 4 * self.start))
+        return (_ptr(self.send_ws), self.P_send, v * self.stride,
+                ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride))
 
     def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
         """params: means3D [Ps,3], shs [Ps,M,3], opacities [Ps,1], scales [Ps,3], rotations [Ps,4] of
@@ -157,37 +197,38 @@ class ShardedViewRasterizer:
         dev_idx = dev.index if dev.index is not None else torch.cuda.current_device()
         ctx = RasterContext()
         ctx.P, ctx.D, ctx.M, ctx.W, ctx.H, ctx.reruns = P, D, M, W, H, 0
+        peer = self.exchange == "peer"
         with torch.cuda.device(dev):
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            gb, _, ib = _native.workspace_bytes(P, W, H, 0)
-            ctx.geom_ws = torch.empty(gb, dtype=torch.uint8, device=dev)
-            ctx.image_ws = torch.empty(ib, dtype=torch.uint8, device=dev)
-            radii = torch.empty(P, dtype=torch.int32, device=dev)
+            ctx.geom_ws = self.geom_ws
+            ctx.image_ws = torch.empty(self.image_bytes, dtype=torch.uint8, device=dev)
             color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
-            full = _ws_arrays(ctx.geom_ws, self.L_full, P)
-            for v in range(N):
+            if peer:
+                self.hdl.barrier(channel=0)   # every rank is done reading the previous step's workspaces
+            for v in self._view_order():
                 view, proj, campos, _ = cams[v]
                 c = cameras[v]
+                ws_ptr, P_ws, row0, radii_ptr = self._target(v)
                 _native.check(L.gsr_preprocess_slots(
-                    self.P_send, v * self.stride, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None,
-                    _ptr(p["opacities"]), _ptr(p["scales"]), float(c.scale_modifier), _ptr(p["rotations"]), None,
-                    _ptr(view), _ptr(proj), _ptr(campos), float(c.tanfovx), float(c.tanfovy),
-                    ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride), _ptr(self.send_ws),
-                    stream, debug), "gsr_preprocess_slots")
-            pairs = []
-            for name in GEOMETRY_ARRAYS:
-                pairs.append(([self.send[name][self._slot(v)] for v in range(N)],
-                              [full[name][self.plan.rows(j)] for j in range(N)]))
-            pairs.append(([self.send_radii[self._slot(v)] for v in range(N)],
-                          [radii[self.plan.rows(j)] for j in range(N)]))
-            all_to_all_rows(pairs, self.group)
+                    P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["opacities"]),
+                    _ptr(p["scales"]), float(c.scale_modifier), _ptr(p["rotations"]), None, _ptr(view), _ptr(proj),
+                    _ptr(campos), float(c.tanfovx), float(c.tanfovy), radii_ptr, ws_ptr, stream, debug),
+                    "gsr_preprocess_slots")
+            if peer:
+                self.hdl.barrier(channel=1)   # all slices of this rank's view have landed
+            else:
+                pairs = [([self.send[name][self._slot(v)] for v in range(N)],
+                          [self.full[name][self.plan.rows(j)] for j in range(N)]) for name in GEOMETRY_ARRAYS]
+                pairs.append(([self.send_radii[self._slot(v)] for v in range(N)],
+                              [self.radii_ws[self.plan.rows(j)] for j in range(N)]))
+                all_to_all_rows(pairs, self.group)
             info = _pinned_info(dev_idx)
             _native.check(L.gsr_depth_order(P, W, H, _ptr(ctx.geom_ws), ctypes.c_void_p(info.data_ptr()), stream,
                                             debug), "gsr_depth_order")
-            bg = cams[r][3]
-            _render_stage(L, ctx, P, W, H, bg, radii, color, info, None, dev, dev_idx, stream, debug)
+            _render_stage(L, ctx, P, W, H, cams[r][3], self.radii_ws, color, info, None, dev, dev_idx, stream, debug)
+            radii = self.radii_ws.clone()     # the workspace copy is overwritten by the next step
         self._state = (ctx, p, cams, [(float(c.scale_modifier), float(c.tanfovx), float(c.tanfovy)) for c in cameras],
-                       D, debug, full)
+                       D, debug)
         return color, radii
 
     def backward(self, dL_dpix: torch.Tensor):
@@ -195,7 +236,7 @@ class ShardedViewRasterizer:
         the N views (buffers owned by this object, overwritten by the next call); grad_means2D [N,Ps,3]."""
         if self._state is None:
             raise RuntimeError("backward() needs a preceding forward()")
-        ctx, p, cams, scal, D, debug, full = self._state
+        ctx, p, cams, scal, D, debug = self._state
         N, r, dev, L = self.world, self.rank, self.device, self.lib
         P, Ps, W, H, M = self.P, self.Ps, self.W, self.H, self.M
         g = _dense(dL_dpix, dev)
@@ -206,17 +247,20 @@ class ShardedViewRasterizer:
             _native.check(L.gsr_blend_backward(P, W, H, _ptr(cams[r][3]), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws),
                                                ctx.capacity, _ptr(ctx.image_ws), _ptr(g), stream, debug),
                           "gsr_blend_backward")
-            all_to_all_rows([([full["grad_accum"][self.plan.rows(j)] for j in range(N)],
-                              [self.send["grad_accum"][self._slot(v)] for v in range(N)])], self.group)
+            if self.exchange == "peer":
+                self.hdl.barrier(channel=2)   # every view's accumulators are complete
+            else:
+                all_to_all_rows([([self.full["grad_accum"][self.plan.rows(j)] for j in range(N)],
+                                  [self.send["grad_accum"][self._slot(v)] for v in range(N)])], self.group)
             G = self.grads
-            for v in range(N):
+            for n, v in enumerate(self._view_order()):
                 view, proj, campos, _ = cams[v]
                 mod, tfx, tfy = scal[v]
+                ws_ptr, P_ws, row0, radii_ptr = self._target(v)
                 _native.check(L.gsr_preprocess_backward_slots(
-                    self.P_send, v * self.stride, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None,
-                    _ptr(p["scales"]), mod, _ptr(p["rotations"]), None, _ptr(view), _ptr(proj), _ptr(campos), tfx, tfy,
-                    ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride), _ptr(self.send_ws),
+                    P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["scales"]), mod,
+                    _ptr(p["rotations"]), None, _ptr(view), _ptr(proj), _ptr(campos), tfx, tfy, radii_ptr, ws_ptr,
                     _ptr(self.grad_means2D[v]), None, _ptr(G["opacities"]), _ptr(G["means3D"]), None, _ptr(G["shs"]),
-                    _ptr(G["scales"]), _ptr(G["rotations"]), 1 if v > 0 else 0, stream, debug),
+                    _ptr(G["scales"]), _ptr(G["rotations"]), 1 if n > 0 else 0, stream, debug),
                     "gsr_preprocess_backward_slots")
         return G, self.grad_means2D

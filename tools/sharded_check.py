@@ -69,7 +69,8 @@ def main():
             m2d.append(cur["means2D"].clone())
 
     # ---- sharded ----
-    sr = ShardedViewRasterizer(P, M, W, H, dev)
+    exchange = os.environ.get("GSR_EXCHANGE", "peer")
+    sr = ShardedViewRasterizer(P, M, W, H, dev, exchange=exchange)
     rows = sr.plan.rows(rank)
     sl = {k: t[k][rows] for k in ("means3D", "shs", "opacities", "scales", "rotations")}
     for it in range(2):  # second pass exercises buffer reuse + capacity speculation
@@ -103,7 +104,7 @@ def main():
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
-        print(f"sharded_check world={world} P={P} {W}x{H}: {'OK' if flag.item() == 0 else 'FAILED'} "
+        print(f"sharded_check[{exchange}] world={world} P={P} {W}x{H}: {'OK' if flag.item() == 0 else 'FAILED'} "
               f"(worst gradient rel_l1 {worst:.2e})", flush=True)
     dist.barrier()
     dist.destroy_process_group()
