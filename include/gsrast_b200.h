@@ -36,6 +36,7 @@ extern "C" {
 #endif
 
 #define GSR_ABI_VERSION 3
+#define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
 #define GSR_API __attribute__((visibility("default")))
@@ -190,6 +191,34 @@ GSR_API int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int
                          void* geom_ws, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
                          float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                          float* dL_drots, int accumulate, void* stream, int debug);
+
+/* Multi-view forms of the two slot entries: ONE call (and, for the backward, ONE kernel that reads the
+ * slice's parameters and SH rows once and loops over the views, accumulating in registers / shared
+ * memory) for all n_views <= GSR_MAX_VIEWS views of the step.  `views` is a HOST array; its pointers are
+ * device pointers.  Every view uses the same P_ws / slot_offset / Ps. */
+typedef struct gsr_view_slot {
+    const float* viewmatrix;   /* [16] */
+    const float* projmatrix;   /* [16] */
+    const float* campos;       /* [3]  */
+    float tanfovx, tanfovy;
+    void* geom_ws;             /* P_ws-row geometry workspace of this view (may be a peer GPU's) */
+    int32_t* radii_slots;      /* radii rows [slot_offset, slot_offset + Ps) of this view */
+    float* dL_dmeans2D;        /* backward only: [Ps,3] of this view, always overwritten */
+} gsr_view_slot;
+
+GSR_API int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                         const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* opacities, const float* scales, float scale_modifier,
+                         const float* rotations, const float* cov3D_precomp, int n_views,
+                         const gsr_view_slot* views, void* stream, int debug);
+
+GSR_API int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int M, int width,
+                         int height, const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, int n_views, const gsr_view_slot* views,
+                         float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                         float* dL_dsh, float* dL_dscales, float* dL_drots, int accumulate, void* stream,
+                         int debug);
 
 /* Replaces `_C.mark_visible`: present[i] = 1 iff Gaussian i passes the near-plane test. */
 GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,

@@ -32,7 +32,16 @@ EXPORTS = (
     "gsr_mark_visible", "gsr_launch_count", "gsr_stage_count", "gsr_stage_name",
     "gsr_stage_timing_enable", "gsr_stage_timing_read", "gsr_blend_pair_counts",
     "gsr_preprocess_slots", "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots",
+    "gsr_preprocess_views", "gsr_preprocess_backward_views",
 )
+MAX_VIEWS = 16
+
+
+class ViewSlot(ctypes.Structure):
+    """gsr_view_slot of include/gsrast_b200.h."""
+    _fields_ = [("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p),
+                ("tanfovx", ctypes.c_float), ("tanfovy", ctypes.c_float), ("geom_ws", ctypes.c_void_p),
+                ("radii_slots", ctypes.c_void_p), ("dL_dmeans2D", ctypes.c_void_p)]
 
 
 class ForwardInfo(ctypes.Structure):
@@ -152,6 +161,20 @@ def lib() -> ctypes.CDLL:
         L.gsr_stage_timing_enable.restype = _i
         L.gsr_stage_timing_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(_i64), _i]
         L.gsr_stage_timing_read.restype = _i
+        L.gsr_preprocess_views.argtypes = [
+            _i, _i, _i, _i, _i, _i, _i,  # P_ws slot_offset Ps D M W H
+            _vp, _vp, _vp, _vp,          # means3D shs colors_precomp opacities
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _i, ctypes.POINTER(ViewSlot), _vp, _i]  # n_views views stream debug
+        L.gsr_preprocess_backward_views.argtypes = [
+            _i, _i, _i, _i, _i, _i, _i,  # P_ws slot_offset Ps D M W H
+            _vp, _vp, _vp,               # means3D shs colors_precomp
+            _vp, _f, _vp, _vp,           # scales scale_modifier rotations cov3D_precomp
+            _i, ctypes.POINTER(ViewSlot),
+            _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{colors,opacity,means3D,cov3D,sh,scales,rots}
+            _i, _vp, _i]                 # accumulate stream debug
+        L.gsr_preprocess_views.restype = _i
+        L.gsr_preprocess_backward_views.restype = _i
         for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",
                      "gsr_forward_render", "gsr_backward", "gsr_mark_visible", "gsr_preprocess_slots",
                      "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots"):

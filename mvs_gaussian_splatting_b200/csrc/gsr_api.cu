@@ -412,6 +412,62 @@ int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int D, int 
                                       static_cast<cudaStream_t>(stream), debug);
 }
 
+int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                         const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* opacities, const float* scales, float scale_modifier, const float* rotations,
+                         const float* cov3D_precomp, int n_views, const gsr_view_slot* views, void* stream,
+                         int debug) {
+    if (!views || n_views < 1 || n_views > GSR_MAX_VIEWS) return GSR_ERR_INVALID_ARGUMENT;
+    for (int v = 0; v < n_views; ++v) {
+        const gsr_view_slot& a = views[v];
+        int st = gsr_preprocess_slots(P_ws, slot_offset, Ps, D, M, width, height, means3D, shs, colors_precomp,
+                                      opacities, scales, scale_modifier, rotations, cov3D_precomp, a.viewmatrix,
+                                      a.projmatrix, a.campos, a.tanfovx, a.tanfovy, a.radii_slots, a.geom_ws, stream,
+                                      debug);
+        if (st != GSR_OK) return st;
+    }
+    return GSR_OK;
+}
+
+int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
+                                  const float* means3D, const float* shs, const float* colors_precomp,
+                                  const float* scales, float scale_modifier, const float* rotations,
+                                  const float* cov3D_precomp, int n_views, const gsr_view_slot* views,
+                                  float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                                  float* dL_dsh, float* dL_dscales, float* dL_drots, int accumulate, void* stream,
+                                  int debug) {
+    if (!views || n_views < 1 || n_views > GSR_MAX_VIEWS) return GSR_ERR_INVALID_ARGUMENT;
+    int st = check_dims(P_ws, width, height, 0);
+    if (st == GSR_OK) st = check_slots(P_ws, slot_offset, Ps);
+    if (st != GSR_OK) return st;
+    if (Ps == 0) return GSR_OK;
+    if (!means3D || !dL_dopacity || !dL_dmeans3D) return GSR_ERR_INVALID_ARGUMENT;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
+    if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
+    if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P_ws, width, height, 0, &L);
+    BackwardViewArgs args[GSR_MAX_VIEWS];
+    for (int v = 0; v < n_views; ++v) {
+        const gsr_view_slot& a = views[v];
+        if (!a.viewmatrix || !a.projmatrix || !a.campos || !a.geom_ws || !a.radii_slots || !a.dL_dmeans2D)
+            return GSR_ERR_INVALID_ARGUMENT;
+        if (!aligned16(a.geom_ws)) return GSR_ERR_WORKSPACE;
+        args[v].view = a.viewmatrix; args[v].proj = a.projmatrix; args[v].campos = a.campos;
+        args[v].tanfovx = a.tanfovx; args[v].tanfovy = a.tanfovy;
+        args[v].radii = a.radii_slots;
+        args[v].gv = offset_rows(geom_view(a.geom_ws, L), (size_t)slot_offset);
+        args[v].dL_dmeans2D = a.dL_dmeans2D;
+    }
+    return launch_preprocess_backward_views(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp != nullptr,
+                                            scales, scale_modifier, rotations, cov3D_precomp, n_views, args, dL_dcolors,
+                                            dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots,
+                                            accumulate != 0, static_cast<cudaStream_t>(stream), debug);
+}
+
 int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
                            int64_t instance_capacity, void* image_ws, uint64_t* d_counters, void* stream) {
     int st = check_dims(P, width, height, instance_capacity);

@@ -19,9 +19,26 @@ constexpr int kBwdThreads = 128;
 constexpr int kBwdWarps = kBwdThreads / 32;
 constexpr int kShStride = 49;
 
+constexpr int kMaxViews = GSR_MAX_VIEWS;
+
+// What differs from view to view: the camera, and where that view's forward rows and blend
+// accumulators of these Gaussians live (possibly a peer GPU's workspace).
+struct BwdView {
+    const float* view;
+    const float* proj;
+    const float* campos;
+    float tanfovx, tanfovy, focal_x, focal_y;
+    const int32_t* radii;
+    const float* grad_accum;
+    const float4* conic_opacity;
+    const float4* rgb;
+    float* dL_dmeans2D;
+};
+
 struct BwdParams {
     int P, D, M, W, H;
-    int accumulate;  // parameter gradients are added to the outputs (rows the view does not see: untouched)
+    int accumulate;  // parameter gradients are added to the outputs (rows no view sees: untouched)
+    int n_views;
     const float* means3D;
     const float* shs;
     int colors_precomp;
@@ -29,13 +46,8 @@ struct BwdParams {
     float scale_modifier;
     const float* rotations;
     const float* cov3D_precomp;
-    const float* view;
-    const float* proj;
-    const float* campos;
-    float tanfovx, tanfovy, focal_x, focal_y;
-    const int32_t* radii;
-    GeomView gv;
-    float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drots;
+    float *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drots;
+    BwdView v[kMaxViews];
 };
 
 __device__ __forceinline__ void cov3d(float s0, float s1, float s2, float4 q, float R[3][3], float* c6) {
@@ -56,9 +68,11 @@ __device__ __forceinline__ void cov3d(float s0, float s1, float s2, float4 q, fl
     c6[5] = Mm[0][2] * Mm[0][2] + Mm[1][2] * Mm[1][2] + Mm[2][2] * Mm[2][2];
 }
 
-// SH backward for one Gaussian: writes dL/dsh into the shared row (in place over the SH values)
-// and returns dL/d(direction).  Coefficients above the active degree are zeroed.
-__device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, float z, float* row,
+// SH backward for one Gaussian: reads the SH values from `row`, writes dL/dsh to `out` and returns
+// dL/d(direction).  kAcc = false: out may alias row (in place), coefficients above the active degree
+// are zeroed.  kAcc = true (multi-view): out is a separate, pre-zeroed row that is added to.
+template <bool kAcc>
+__device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, float z, const float* row, float* out,
                                             const float* g3, float* gdir) {
     const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
     const float C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f,
@@ -72,28 +86,29 @@ __device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, fl
         const float g = g3[ch];
         float ddx = 0.f, ddy = 0.f, ddz = 0.f;
 #define ROW(k) row[3 * (k) + ch]
-        ROW(0) = C0 * g;
+#define PUT(k, val) do { float& o_ = out[3 * (k) + ch]; o_ = kAcc ? o_ + (val) : (val); } while (0)
+        PUT(0, C0 * g);
         if (deg > 0) {
             const float s1 = ROW(1), s2 = ROW(2), s3 = ROW(3);
-            ROW(1) = -C1 * y * g; ROW(2) = C1 * z * g; ROW(3) = -C1 * x * g;
+            PUT(1, -C1 * y * g); PUT(2, C1 * z * g); PUT(3, -C1 * x * g);
             ddx = -C1 * s3; ddy = -C1 * s1; ddz = C1 * s2;
             if (deg > 1) {
                 const float s4 = ROW(4), s5 = ROW(5), s6 = ROW(6), s7 = ROW(7), s8 = ROW(8);
-                ROW(4) = C2[0] * xy * g; ROW(5) = C2[1] * yz * g; ROW(6) = C2[2] * (2.f * zz - xx - yy) * g;
-                ROW(7) = C2[3] * xz * g; ROW(8) = C2[4] * (xx - yy) * g;
+                PUT(4, C2[0] * xy * g); PUT(5, C2[1] * yz * g); PUT(6, C2[2] * (2.f * zz - xx - yy) * g);
+                PUT(7, C2[3] * xz * g); PUT(8, C2[4] * (xx - yy) * g);
                 ddx += C2[0] * y * s4 + C2[2] * 2.f * -x * s6 + C2[3] * z * s7 + C2[4] * 2.f * x * s8;
                 ddy += C2[0] * x * s4 + C2[1] * z * s5 + C2[2] * 2.f * -y * s6 + C2[4] * 2.f * -y * s8;
                 ddz += C2[1] * y * s5 + C2[2] * 4.f * z * s6 + C2[3] * x * s7;
                 if (deg > 2) {
                     const float s9 = ROW(9), s10 = ROW(10), s11 = ROW(11), s12 = ROW(12), s13 = ROW(13),
                                 s14 = ROW(14), s15 = ROW(15);
-                    ROW(9) = C3[0] * y * (3.f * xx - yy) * g;
-                    ROW(10) = C3[1] * xy * z * g;
-                    ROW(11) = C3[2] * y * (4.f * zz - xx - yy) * g;
-                    ROW(12) = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy) * g;
-                    ROW(13) = C3[4] * x * (4.f * zz - xx - yy) * g;
-                    ROW(14) = C3[5] * z * (xx - yy) * g;
-                    ROW(15) = C3[6] * x * (xx - 3.f * yy) * g;
+                    PUT(9, C3[0] * y * (3.f * xx - yy) * g);
+                    PUT(10, C3[1] * xy * z * g);
+                    PUT(11, C3[2] * y * (4.f * zz - xx - yy) * g);
+                    PUT(12, C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy) * g);
+                    PUT(13, C3[4] * x * (4.f * zz - xx - yy) * g);
+                    PUT(14, C3[5] * z * (xx - yy) * g);
+                    PUT(15, C3[6] * x * (xx - 3.f * yy) * g);
                     ddx += C3[0] * s9 * 6.f * xy + C3[1] * s10 * yz + C3[2] * s11 * -2.f * xy +
                            C3[3] * s12 * -6.f * xz + C3[4] * s13 * (-3.f * xx + 4.f * zz - yy) +
                            C3[5] * s14 * 2.f * xz + C3[6] * s15 * 3.f * (xx - yy);
@@ -106,49 +121,54 @@ __device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, fl
             }
         }
         const int used = (deg + 1) * (deg + 1);
-        for (int k = used; k < M; ++k) ROW(k) = 0.f;
+        if (!kAcc) for (int k = used; k < M; ++k) out[3 * k + ch] = 0.f;
+#undef PUT
 #undef ROW
         gdir[0] += ddx * g; gdir[1] += ddy * g; gdir[2] += ddz * g;
     }
 }
 
-__global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const BwdParams p) {
-    __shared__ float s_sh[kBwdWarps][32 * kShStride];
-    __shared__ float s_cam[35];
-    if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(p.view + threadIdx.x);
-    else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(p.proj + threadIdx.x - 16);
-    else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(p.campos + threadIdx.x - 32);
-    __syncthreads();
-    const float* view = s_cam;
-    const float* proj = s_cam + 16;
-    const float* campos = s_cam + 32;
+// kMulti = false: one view, the dL/dsh row is formed in place over the SH values (one shared tile).
+// kMulti = true: the Gaussian's parameters and SH row are read ONCE and the views are looped over;
+// scalar gradients accumulate in registers, dL/dsh in a second shared tile; outputs written once.
+template <bool kMulti>
+__global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 5) preprocess_backward_kernel(const BwdParams p) {
+    extern __shared__ __align__(16) float s_dyn[];
+    float* s_cam = s_dyn;                                   // view[16] proj[16] campos[3]
+    float* tile_in = s_dyn + 36 + (threadIdx.x >> 5) * (32 * kShStride);
+    float* tile = kMulti ? tile_in + kBwdWarps * 32 * kShStride : tile_in;   // dL/dsh rows of this warp
 
     const int idx = blockIdx.x * kBwdThreads + threadIdx.x;
     const unsigned lane = lane_id();
     const int warp = threadIdx.x >> 5;
     const int warp_base = blockIdx.x * kBwdThreads + warp * 32;
     const bool valid = idx < p.P;
-    const bool vis = valid && p.radii[idx] > 0;
-    const unsigned vmask = __ballot_sync(0xffffffffu, vis);
+    uint32_t visbits = 0;  // bit v: view v sees this Gaussian
+    for (int v = 0; v < p.n_views; ++v)
+        if (valid && p.v[v].radii[idx] > 0) visbits |= 1u << v;
+    const bool vis_any = visbits != 0;
+    const unsigned vmask = __ballot_sync(0xffffffffu, vis_any);
     const bool do_sh = (p.dL_dsh != nullptr) && !p.colors_precomp;
-    float* tile = s_sh[warp];
     const int row = 3 * p.M;
     const int need = 3 * (p.D + 1) * (p.D + 1);
 
     // ---- per-Gaussian operands: issued before the SH fetch so their latency overlaps it ----
-    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, con = a0, q = make_float4(1.f, 0.f, 0.f, 0.f);
+    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
     float mx = 0.f, my = 0.f, mz = 0.f, rs0 = 0.f, rs1 = 0.f, rs2 = 0.f;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, con = a0;
     uint32_t clamped_bits = 0;
-    if (vis) {
-        const float4* accp = reinterpret_cast<const float4*>(p.gv.grad_accum + (size_t)idx * 12);
-        a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
-        con = p.gv.conic_opacity[idx];
+    if (vis_any) {
         mx = p.means3D[3 * (size_t)idx]; my = p.means3D[3 * (size_t)idx + 1]; mz = p.means3D[3 * (size_t)idx + 2];
         if (!p.cov3D_precomp) {
             q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
             rs0 = p.scales[3 * (size_t)idx]; rs1 = p.scales[3 * (size_t)idx + 1]; rs2 = p.scales[3 * (size_t)idx + 2];
         }
-        if (do_sh) clamped_bits = __float_as_uint(p.gv.rgb[idx].w);
+        if (!kMulti) {  // the single view's accumulators travel with the operands
+            const float4* accp = reinterpret_cast<const float4*>(p.v[0].grad_accum + (size_t)idx * 12);
+            a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
+            con = p.v[0].conic_opacity[idx];
+            if (do_sh) clamped_bits = __float_as_uint(p.v[0].rgb[idx].w);
+        }
     }
 
     // ---- fetch the SH rows of the visible Gaussians of this warp ----
@@ -174,7 +194,7 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     if (jb + (int)lane + 32 * u < total) {
-                        float* d = tile + dsto[u];
+                        float* d = tile_in + dsto[u];
                         d[0] = val[u].x; d[1] = val[u].y; d[2] = val[u].z; d[3] = val[u].w;
                     }
                 }
@@ -183,26 +203,21 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
             for (int j = lane; j < nvis * need; j += 32) {
                 const int v = j / need, part = j - v * need;
                 const int src = __fns(vmask, 0, v + 1);
-                tile[src * kShStride + part] = __ldg(p.shs + (size_t)(warp_base + src) * row + part);
+                tile_in[src * kShStride + part] = __ldg(p.shs + (size_t)(warp_base + src) * row + part);
             }
         }
-        __syncwarp();
     }
+    if (kMulti && do_sh)
+        for (int j = lane; j < 32 * kShStride; j += 32) tile[j] = 0.f;
+    __syncwarp();
 
     float gm[3] = {0.f, 0.f, 0.f}, gc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
-    float g2d[2] = {0.f, 0.f}, gcol[3] = {0.f, 0.f, 0.f}, gop = 0.f;
+    float gcol[3] = {0.f, 0.f, 0.f}, gop = 0.f;
 
-    if (vis) {
-        const float S1 = a0.x, S2 = a0.y;
-        // true partials of the conic (A,B,C) and the NDC-scaled mean2D gradient
-        const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
-        g2d[0] = (-con.x * S1 - con.y * S2) * (0.5f * (float)p.W);
-        g2d[1] = (-con.z * S2 - con.y * S1) * (0.5f * (float)p.H);
-        gop = a1.y;
-        gcol[0] = a1.z; gcol[1] = a1.w; gcol[2] = a2.x;
-
-        float c6[6], R[3][3], s[3] = {0.f, 0.f, 0.f};
+    // view-independent: 3D covariance from scale / rotation
+    float c6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, R[3][3] = {{0.f}}, s[3] = {0.f, 0.f, 0.f};
+    if (vis_any) {
         if (p.cov3D_precomp) {
 #pragma unroll
             for (int k = 0; k < 6; ++k) c6[k] = p.cov3D_precomp[6 * (size_t)idx + k];
@@ -212,141 +227,178 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
             s[2] = p.scale_modifier * rs2;
             cov3d(s[0], s[1], s[2], q, R, c6);
         }
+    }
 
-        // ---- EWA projection (forward values) ----
-        float t[3];
-        t[0] = view[0] * mx + view[4] * my + view[8] * mz + view[12];
-        t[1] = view[1] * mx + view[5] * my + view[9] * mz + view[13];
-        t[2] = view[2] * mx + view[6] * my + view[10] * mz + view[14];
-        const float limx = 1.3f * p.tanfovx, limy = 1.3f * p.tanfovy;
-        const float txtz = t[0] / t[2], tytz = t[1] / t[2];
-        const float gmulx = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
-        const float gmuly = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
-        t[0] = fminf(limx, fmaxf(-limx, txtz)) * t[2];
-        t[1] = fminf(limy, fmaxf(-limy, tytz)) * t[2];
-        const float fx = p.focal_x, fy = p.focal_y;
-        const float j00 = fx / t[2], j11 = fy / t[2];
-        const float j02 = -(fx * t[0]) / (t[2] * t[2]), j12 = -(fy * t[1]) / (t[2] * t[2]);
-        float M0[3], M1[3];
+    for (int vi = 0; vi < p.n_views; ++vi) {
+        const BwdView& V = p.v[vi];
+        if (kMulti || vi == 0) {
+            if (kMulti) __syncthreads();  // the previous view's camera is no longer read
+            if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(V.view + threadIdx.x);
+            else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(V.proj + threadIdx.x - 16);
+            else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(V.campos + threadIdx.x - 32);
+            __syncthreads();
+        }
+        const float* view = s_cam;
+        const float* proj = s_cam + 16;
+        const float* campos = s_cam + 32;
+        const bool vis = (visbits >> vi) & 1u;
+        float g2d[2] = {0.f, 0.f};
+
+        if (vis) {
+            if (kMulti) {
+                const float4* accp = reinterpret_cast<const float4*>(V.grad_accum + (size_t)idx * 12);
+                a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
+                con = V.conic_opacity[idx];
+                if (do_sh) clamped_bits = __float_as_uint(V.rgb[idx].w);
+            }
+            const float S1 = a0.x, S2 = a0.y;
+            // true partials of the conic (A,B,C) and the NDC-scaled mean2D gradient
+            const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
+            g2d[0] = (-con.x * S1 - con.y * S2) * (0.5f * (float)p.W);
+            g2d[1] = (-con.z * S2 - con.y * S1) * (0.5f * (float)p.H);
+            gop += a1.y;
+            const float vcol[3] = {a1.z, a1.w, a2.x};
+            gcol[0] += vcol[0]; gcol[1] += vcol[1]; gcol[2] += vcol[2];
+
+            // ---- EWA projection (forward values) ----
+            float t[3];
+            t[0] = view[0] * mx + view[4] * my + view[8] * mz + view[12];
+            t[1] = view[1] * mx + view[5] * my + view[9] * mz + view[13];
+            t[2] = view[2] * mx + view[6] * my + view[10] * mz + view[14];
+            const float limx = 1.3f * V.tanfovx, limy = 1.3f * V.tanfovy;
+            const float txtz = t[0] / t[2], tytz = t[1] / t[2];
+            const float gmulx = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+            const float gmuly = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+            t[0] = fminf(limx, fmaxf(-limx, txtz)) * t[2];
+            t[1] = fminf(limy, fmaxf(-limy, tytz)) * t[2];
+            const float fx = V.focal_x, fy = V.focal_y;
+            const float j00 = fx / t[2], j11 = fy / t[2];
+            const float j02 = -(fx * t[0]) / (t[2] * t[2]), j12 = -(fy * t[1]) / (t[2] * t[2]);
+            float M0[3], M1[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                M0[k] = view[4 * k + 0] * j00 + view[4 * k + 2] * j02;
+                M1[k] = view[4 * k + 1] * j11 + view[4 * k + 2] * j12;
+            }
+            const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+            float SM0[3], SM1[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                SM0[k] = S[k][0] * M0[0] + S[k][1] * M0[1] + S[k][2] * M0[2];
+                SM1[k] = S[k][0] * M1[0] + S[k][1] * M1[1] + S[k][2] * M1[2];
+            }
+            const float a = M0[0] * SM0[0] + M0[1] * SM0[1] + M0[2] * SM0[2] + 0.3f;
+            const float b = M1[0] * SM0[0] + M1[1] * SM0[1] + M1[2] * SM0[2];
+            const float c = M1[0] * SM1[0] + M1[1] * SM1[1] + M1[2] * SM1[2] + 0.3f;
+            const float det = a * c - b * b;
+            const float d2inv = 1.f / (det * det + 0.0000001f);
+            float dLa = 0.f, dLb = 0.f, dLc = 0.f;
+            if (d2inv != 0.f) {
+                dLa = d2inv * (-c * c * gA + b * c * gB + (det - a * c) * gC);
+                dLc = d2inv * (-a * a * gC + a * b * gB + (det - a * c) * gA);
+                dLb = d2inv * (2.f * b * c * gA - (det + 2.f * b * b) * gB + 2.f * a * b * gC);
+                gc[0] += M0[0] * M0[0] * dLa + M0[0] * M1[0] * dLb + M1[0] * M1[0] * dLc;
+                gc[3] += M0[1] * M0[1] * dLa + M0[1] * M1[1] * dLb + M1[1] * M1[1] * dLc;
+                gc[5] += M0[2] * M0[2] * dLa + M0[2] * M1[2] * dLb + M1[2] * M1[2] * dLc;
+                gc[1] += 2.f * M0[0] * M0[1] * dLa + (M0[0] * M1[1] + M0[1] * M1[0]) * dLb + 2.f * M1[0] * M1[1] * dLc;
+                gc[2] += 2.f * M0[0] * M0[2] * dLa + (M0[0] * M1[2] + M0[2] * M1[0]) * dLb + 2.f * M1[0] * M1[2] * dLc;
+                gc[4] += 2.f * M0[2] * M0[1] * dLa + (M0[1] * M1[2] + M0[2] * M1[1]) * dLb + 2.f * M1[1] * M1[2] * dLc;
+            }
+            float vm[3];  // this view's dL/dmean3D
+            {
+                float dM0[3], dM1[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    dM0[k] = 2.f * SM0[k] * dLa + SM1[k] * dLb;
+                    dM1[k] = 2.f * SM1[k] * dLc + SM0[k] * dLb;
+                }
+                float dj00 = 0.f, dj02 = 0.f, dj11 = 0.f, dj12 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    dj00 += view[4 * k + 0] * dM0[k];
+                    dj02 += view[4 * k + 2] * dM0[k];
+                    dj11 += view[4 * k + 1] * dM1[k];
+                    dj12 += view[4 * k + 2] * dM1[k];
+                }
+                const float tz = 1.f / t[2], tz2 = tz * tz, tz3 = tz2 * tz;
+                const float dtx = gmulx * -fx * tz2 * dj02;
+                const float dty = gmuly * -fy * tz2 * dj12;
+                const float dtz = -fx * tz2 * dj00 - fy * tz2 * dj11 + (2.f * fx * t[0]) * tz3 * dj02 +
+                                  (2.f * fy * t[1]) * tz3 * dj12;
+                vm[0] = view[0] * dtx + view[1] * dty + view[2] * dtz;
+                vm[1] = view[4] * dtx + view[5] * dty + view[6] * dtz;
+                vm[2] = view[8] * dtx + view[9] * dty + view[10] * dtz;
+            }
+            // ---- mean2D -> mean3D through the perspective divide ----
+            {
+                const float hx = proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12];
+                const float hy = proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13];
+                const float hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
+                const float mw = 1.f / (hw + 0.0000001f);
+                const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+                vm[0] += (proj[0] * mw - proj[3] * mul1) * g2d[0] + (proj[1] * mw - proj[3] * mul2) * g2d[1];
+                vm[1] += (proj[4] * mw - proj[7] * mul1) * g2d[0] + (proj[5] * mw - proj[7] * mul2) * g2d[1];
+                vm[2] += (proj[8] * mw - proj[11] * mul1) * g2d[0] + (proj[9] * mw - proj[11] * mul2) * g2d[1];
+            }
+            // ---- colour -> SH + view direction ----
+            if (do_sh) {
+                float g3[3];
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) g3[ch] = (clamped_bits >> ch) & 1u ? 0.f : vcol[ch];
+                const float d0 = mx - campos[0], d1 = my - campos[1], d2 = mz - campos[2];
+                const float s2 = d0 * d0 + d1 * d1 + d2 * d2;
+                const float len = sqrtf(s2);
+                float gdir[3];
+                sh_backward<kMulti>(p.D, p.M, d0 / len, d1 / len, d2 / len, tile_in + lane * kShStride,
+                                    tile + lane * kShStride, g3, gdir);
+                const float inv32 = 1.f / sqrtf(s2 * s2 * s2);
+                const float vd = d0 * gdir[0] + d1 * gdir[1] + d2 * gdir[2];
+                vm[0] += (s2 * gdir[0] - d0 * vd) * inv32;
+                vm[1] += (s2 * gdir[1] - d1 * vd) * inv32;
+                vm[2] += (s2 * gdir[2] - d2 * vd) * inv32;
+            }
+            gm[0] += vm[0]; gm[1] += vm[1]; gm[2] += vm[2];
+        }
+        if (valid) {  // per-view output: always overwritten
+            const size_t i = (size_t)idx;
+            V.dL_dmeans2D[3 * i] = g2d[0]; V.dL_dmeans2D[3 * i + 1] = g2d[1]; V.dL_dmeans2D[3 * i + 2] = 0.f;
+        }
+    }
+
+    // ---- cov3D -> scale, quaternion: linear in dL/dcov3D and view-independent, so applied once ----
+    if (vis_any && !p.cov3D_precomp) {
+        const float Gs[3][3] = {{gc[0], 0.5f * gc[1], 0.5f * gc[2]},
+                                {0.5f * gc[1], gc[3], 0.5f * gc[4]},
+                                {0.5f * gc[2], 0.5f * gc[4], gc[5]}};
+        float GR[3][3], dR[3][3];
+#pragma unroll
+        for (int a2 = 0; a2 < 3; ++a2)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) GR[a2][k] = Gs[a2][0] * R[0][k] + Gs[a2][1] * R[1][k] + Gs[a2][2] * R[2][k];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            M0[k] = view[4 * k + 0] * j00 + view[4 * k + 2] * j02;
-            M1[k] = view[4 * k + 1] * j11 + view[4 * k + 2] * j12;
+            const float rgr = R[0][k] * GR[0][k] + R[1][k] * GR[1][k] + R[2][k] * GR[2][k];
+            gs[k] = 2.f * s[k] * rgr;
+#pragma unroll
+            for (int a2 = 0; a2 < 3; ++a2) dR[a2][k] = 2.f * GR[a2][k] * s[k] * s[k];
         }
-        const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
-        float SM0[3], SM1[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            SM0[k] = S[k][0] * M0[0] + S[k][1] * M0[1] + S[k][2] * M0[2];
-            SM1[k] = S[k][0] * M1[0] + S[k][1] * M1[1] + S[k][2] * M1[2];
-        }
-        const float a = M0[0] * SM0[0] + M0[1] * SM0[1] + M0[2] * SM0[2] + 0.3f;
-        const float b = M1[0] * SM0[0] + M1[1] * SM0[1] + M1[2] * SM0[2];
-        const float c = M1[0] * SM1[0] + M1[1] * SM1[1] + M1[2] * SM1[2] + 0.3f;
-        const float det = a * c - b * b;
-        const float d2inv = 1.f / (det * det + 0.0000001f);
-        float dLa = 0.f, dLb = 0.f, dLc = 0.f;
-        if (d2inv != 0.f) {
-            dLa = d2inv * (-c * c * gA + b * c * gB + (det - a * c) * gC);
-            dLc = d2inv * (-a * a * gC + a * b * gB + (det - a * c) * gA);
-            dLb = d2inv * (2.f * b * c * gA - (det + 2.f * b * b) * gB + 2.f * a * b * gC);
-            gc[0] = M0[0] * M0[0] * dLa + M0[0] * M1[0] * dLb + M1[0] * M1[0] * dLc;
-            gc[3] = M0[1] * M0[1] * dLa + M0[1] * M1[1] * dLb + M1[1] * M1[1] * dLc;
-            gc[5] = M0[2] * M0[2] * dLa + M0[2] * M1[2] * dLb + M1[2] * M1[2] * dLc;
-            gc[1] = 2.f * M0[0] * M0[1] * dLa + (M0[0] * M1[1] + M0[1] * M1[0]) * dLb + 2.f * M1[0] * M1[1] * dLc;
-            gc[2] = 2.f * M0[0] * M0[2] * dLa + (M0[0] * M1[2] + M0[2] * M1[0]) * dLb + 2.f * M1[0] * M1[2] * dLc;
-            gc[4] = 2.f * M0[2] * M0[1] * dLa + (M0[1] * M1[2] + M0[2] * M1[1]) * dLb + 2.f * M1[1] * M1[2] * dLc;
-        }
-        {
-            float dM0[3], dM1[3];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                dM0[k] = 2.f * SM0[k] * dLa + SM1[k] * dLb;
-                dM1[k] = 2.f * SM1[k] * dLc + SM0[k] * dLb;
-            }
-            float dj00 = 0.f, dj02 = 0.f, dj11 = 0.f, dj12 = 0.f;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                dj00 += view[4 * k + 0] * dM0[k];
-                dj02 += view[4 * k + 2] * dM0[k];
-                dj11 += view[4 * k + 1] * dM1[k];
-                dj12 += view[4 * k + 2] * dM1[k];
-            }
-            const float tz = 1.f / t[2], tz2 = tz * tz, tz3 = tz2 * tz;
-            const float dtx = gmulx * -fx * tz2 * dj02;
-            const float dty = gmuly * -fy * tz2 * dj12;
-            const float dtz = -fx * tz2 * dj00 - fy * tz2 * dj11 + (2.f * fx * t[0]) * tz3 * dj02 +
-                              (2.f * fy * t[1]) * tz3 * dj12;
-            gm[0] = view[0] * dtx + view[1] * dty + view[2] * dtz;
-            gm[1] = view[4] * dtx + view[5] * dty + view[6] * dtz;
-            gm[2] = view[8] * dtx + view[9] * dty + view[10] * dtz;
-        }
-        // ---- mean2D -> mean3D through the perspective divide ----
-        {
-            const float hx = proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12];
-            const float hy = proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13];
-            const float hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
-            const float mw = 1.f / (hw + 0.0000001f);
-            const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
-            gm[0] += (proj[0] * mw - proj[3] * mul1) * g2d[0] + (proj[1] * mw - proj[3] * mul2) * g2d[1];
-            gm[1] += (proj[4] * mw - proj[7] * mul1) * g2d[0] + (proj[5] * mw - proj[7] * mul2) * g2d[1];
-            gm[2] += (proj[8] * mw - proj[11] * mul1) * g2d[0] + (proj[9] * mw - proj[11] * mul2) * g2d[1];
-        }
-        // ---- colour -> SH + view direction ----
-        if (do_sh) {
-            const uint32_t clamped = clamped_bits;
-            float g3[3];
-#pragma unroll
-            for (int ch = 0; ch < 3; ++ch) g3[ch] = (clamped >> ch) & 1u ? 0.f : gcol[ch];
-            const float d0 = mx - campos[0], d1 = my - campos[1], d2 = mz - campos[2];
-            const float s2 = d0 * d0 + d1 * d1 + d2 * d2;
-            const float len = sqrtf(s2);
-            float gdir[3];
-            sh_backward(p.D, p.M, d0 / len, d1 / len, d2 / len, tile + lane * kShStride, g3, gdir);
-            const float inv32 = 1.f / sqrtf(s2 * s2 * s2);
-            const float vd = d0 * gdir[0] + d1 * gdir[1] + d2 * gdir[2];
-            gm[0] += (s2 * gdir[0] - d0 * vd) * inv32;
-            gm[1] += (s2 * gdir[1] - d1 * vd) * inv32;
-            gm[2] += (s2 * gdir[2] - d2 * vd) * inv32;
-        }
-        // ---- cov3D -> scale, quaternion ----
-        if (!p.cov3D_precomp) {
-            const float Gs[3][3] = {{gc[0], 0.5f * gc[1], 0.5f * gc[2]},
-                                    {0.5f * gc[1], gc[3], 0.5f * gc[4]},
-                                    {0.5f * gc[2], 0.5f * gc[4], gc[5]}};
-            float GR[3][3], dR[3][3];
-#pragma unroll
-            for (int a2 = 0; a2 < 3; ++a2)
-#pragma unroll
-                for (int k = 0; k < 3; ++k) GR[a2][k] = Gs[a2][0] * R[0][k] + Gs[a2][1] * R[1][k] + Gs[a2][2] * R[2][k];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float rgr = R[0][k] * GR[0][k] + R[1][k] * GR[1][k] + R[2][k] * GR[2][k];
-                gs[k] = 2.f * s[k] * rgr;
-#pragma unroll
-                for (int a2 = 0; a2 < 3; ++a2) dR[a2][k] = 2.f * GR[a2][k] * s[k] * s[k];
-            }
-            const float r = q.x, x = q.y, y = q.z, z = q.w;
-            gq[0] = 2.f * (z * (dR[1][0] - dR[0][1]) + y * (dR[0][2] - dR[2][0]) + x * (dR[2][1] - dR[1][2]));
-            gq[1] = 2.f * (y * (dR[0][1] + dR[1][0]) + z * (dR[0][2] + dR[2][0]) + r * (dR[2][1] - dR[1][2])) -
-                    4.f * x * (dR[1][1] + dR[2][2]);
-            gq[2] = 2.f * (x * (dR[0][1] + dR[1][0]) + r * (dR[0][2] - dR[2][0]) + z * (dR[1][2] + dR[2][1])) -
-                    4.f * y * (dR[0][0] + dR[2][2]);
-            gq[3] = 2.f * (r * (dR[1][0] - dR[0][1]) + x * (dR[0][2] + dR[2][0]) + y * (dR[1][2] + dR[2][1])) -
-                    4.f * z * (dR[0][0] + dR[1][1]);
-        }
-    } else if (do_sh && valid) {
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        gq[0] = 2.f * (z * (dR[1][0] - dR[0][1]) + y * (dR[0][2] - dR[2][0]) + x * (dR[2][1] - dR[1][2]));
+        gq[1] = 2.f * (y * (dR[0][1] + dR[1][0]) + z * (dR[0][2] + dR[2][0]) + r * (dR[2][1] - dR[1][2])) -
+                4.f * x * (dR[1][1] + dR[2][2]);
+        gq[2] = 2.f * (x * (dR[0][1] + dR[1][0]) + r * (dR[0][2] - dR[2][0]) + z * (dR[1][2] + dR[2][1])) -
+                4.f * y * (dR[0][0] + dR[2][2]);
+        gq[3] = 2.f * (r * (dR[1][0] - dR[0][1]) + x * (dR[0][2] + dR[2][0]) + y * (dR[1][2] + dR[2][1])) -
+                4.f * z * (dR[0][0] + dR[1][1]);
+    }
+    if (!kMulti && do_sh && valid && !vis_any) {  // in-place tile: culled rows carry zeros
         float* rowp = tile + lane * kShStride;
         for (int k = 0; k < row; ++k) rowp[k] = 0.f;
     }
 
-    // ---- outputs (every row written; in accumulate mode rows of this view's culled Gaussians are skipped) ----
+    // ---- outputs (every row written; in accumulate mode rows no view sees are skipped) ----
     const bool acc = p.accumulate != 0;
-    if (valid) {
-        const size_t i = (size_t)idx;
-        p.dL_dmeans2D[3 * i] = g2d[0]; p.dL_dmeans2D[3 * i + 1] = g2d[1]; p.dL_dmeans2D[3 * i + 2] = 0.f;
-    }
-    if (valid && (!acc || vis)) {
+    if (valid && (!acc || vis_any)) {
         const size_t i = (size_t)idx;
         auto put = [acc](float* a, float v) { *a = acc ? *a + v : v; };
         put(p.dL_dopacity + i, gop);
@@ -408,7 +460,52 @@ __global__ void __launch_bounds__(kBwdThreads) preprocess_backward_kernel(const 
     }
 }
 
+constexpr size_t bwd_smem_bytes(bool multi) {
+    return sizeof(float) * (36 + (size_t)(multi ? 2 : 1) * kBwdWarps * 32 * kShStride);
+}
+
 }  // namespace
+
+int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                                     int colors_precomp, const float* scales, float scale_modifier,
+                                     const float* rotations, const float* cov3D_precomp, int n_views,
+                                     const BackwardViewArgs* views, float* dL_dcolors, float* dL_dopacity,
+                                     float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                                     float* dL_drots, int accumulate, cudaStream_t s, int debug) {
+    if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
+    static bool attr_set = false;  // idempotent; racing threads set the same value
+    if (!attr_set) {
+        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)bwd_smem_bytes(true)));
+        attr_set = true;
+    }
+    BwdParams p;
+    p.accumulate = accumulate;
+    p.n_views = n_views;
+    p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H;
+    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
+    p.scale_modifier = scale_modifier; p.rotations = rotations; p.cov3D_precomp = cov3D_precomp;
+    p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity; p.dL_dmeans3D = dL_dmeans3D; p.dL_dcov3D = dL_dcov3D;
+    p.dL_dsh = dL_dsh; p.dL_dscales = dL_dscales; p.dL_drots = dL_drots;
+    for (int v = 0; v < n_views; ++v) {
+        const BackwardViewArgs& a = views[v];
+        BwdView& o = p.v[v];
+        o.view = a.view; o.proj = a.proj; o.campos = a.campos;
+        o.tanfovx = a.tanfovx; o.tanfovy = a.tanfovy;
+        o.focal_x = (float)g.W / (2.0f * a.tanfovx);
+        o.focal_y = (float)g.H / (2.0f * a.tanfovy);
+        o.radii = a.radii; o.grad_accum = a.gv.grad_accum; o.conic_opacity = a.gv.conic_opacity; o.rgb = a.gv.rgb;
+        o.dL_dmeans2D = a.dL_dmeans2D;
+    }
+    StageScope scope(kStagePreprocessBwd, s);
+    const unsigned blocks = (unsigned)((P + kBwdThreads - 1) / kBwdThreads);
+    if (n_views == 1)
+        preprocess_backward_kernel<false><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
+    else
+        preprocess_backward_kernel<true><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
+    GSR_AFTER_LAUNCH(s, debug);
+    return GSR_OK;
+}
 
 int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                                int colors_precomp, const float* scales, float scale_modifier,
@@ -417,22 +514,12 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                const int32_t* radii, GeomView gv, float* dL_dmeans2D, float* dL_dcolors,
                                float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
                                float* dL_dscales, float* dL_drots, int accumulate, cudaStream_t s, int debug) {
-    BwdParams p;
-    p.accumulate = accumulate;
-    p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H;
-    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
-    p.scale_modifier = scale_modifier; p.rotations = rotations; p.cov3D_precomp = cov3D_precomp;
-    p.view = view; p.proj = proj; p.campos = campos; p.tanfovx = tanfovx; p.tanfovy = tanfovy;
-    p.focal_x = (float)g.W / (2.0f * tanfovx);
-    p.focal_y = (float)g.H / (2.0f * tanfovy);
-    p.radii = radii; p.gv = gv;
-    p.dL_dmeans2D = dL_dmeans2D; p.dL_dcolors = dL_dcolors; p.dL_dopacity = dL_dopacity;
-    p.dL_dmeans3D = dL_dmeans3D; p.dL_dcov3D = dL_dcov3D; p.dL_dsh = dL_dsh; p.dL_dscales = dL_dscales;
-    p.dL_drots = dL_drots;
-    StageScope scope(kStagePreprocessBwd, s);
-    preprocess_backward_kernel<<<(P + kBwdThreads - 1) / kBwdThreads, kBwdThreads, 0, s>>>(p);
-    GSR_AFTER_LAUNCH(s, debug);
-    return GSR_OK;
+    BackwardViewArgs a;
+    a.view = view; a.proj = proj; a.campos = campos; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
+    a.radii = radii; a.gv = gv; a.dL_dmeans2D = dL_dmeans2D;
+    return launch_preprocess_backward_views(P, D, M, g, means3D, shs, colors_precomp, scales, scale_modifier, rotations,
+                                            cov3D_precomp, 1, &a, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
+                                            dL_dsh, dL_dscales, dL_drots, accumulate, s, debug);
 }
 
 }  // namespace gsr

@@ -151,6 +151,23 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots,
                                int accumulate, cudaStream_t s, int debug);
 
+// Multi-view form: the Gaussians' parameters are read once, `views` (host array, n_views <= GSR_MAX_VIEWS)
+// says per view where the camera, the forward rows (conic_opacity, rgb), radii and blend accumulators of
+// THESE P Gaussians live and where that view's dL/dmeans2D goes; parameter gradients are summed over views.
+struct BackwardViewArgs {
+    const float* view; const float* proj; const float* campos;
+    float tanfovx, tanfovy;
+    const int32_t* radii;
+    GeomView gv;
+    float* dL_dmeans2D;
+};
+int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                                     int colors_precomp, const float* scales, float scale_modifier,
+                                     const float* rotations, const float* cov3D_precomp, int n_views,
+                                     const BackwardViewArgs* views, float* dL_dcolors, float* dL_dopacity,
+                                     float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
+                                     float* dL_drots, int accumulate, cudaStream_t s, int debug);
+
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);
 

@@ -168,6 +168,19 @@ class ShardedViewRasterizer:
         """Views starting at the rank's own, so that at any moment the ranks address different peers."""
         return [(self.rank + k) % self.world for k in range(self.world)]
 
+    def _view_slots(self, chunk, cams, cameras, scal):
+        """gsr_view_slot array for the views of `chunk` (+ the workspace row count and first row, which
+        are the same for every view of a transport)."""
+        arr = (_native.ViewSlot * len(chunk))()
+        P_ws = row0 = 0
+        for n, v in enumerate(chunk):
+            view, proj, campos, _ = cams[v]
+            ws_ptr, P_ws, row0, radii_ptr = self._target(v)
+            tfx, tfy = (float(cameras[v].tanfovx), float(cameras[v].tanfovy)) if cameras is not None else scal[v][1:]
+            arr[n] = _native.ViewSlot(view.data_ptr(), proj.data_ptr(), campos.data_ptr(), tfx, tfy, ws_ptr.value,
+                                      radii_ptr.value, self.grad_means2D[v].data_ptr())
+        return arr, P_ws, row0
+
     def _target(self, v: int):
         """(geom_ws pointer, rows in it, first row, radii pointer) a slot call for view v addresses."""
         if self.exchange == "peer":
@@ -205,15 +218,15 @@ class ShardedViewRasterizer:
             color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
             if peer:
                 self.hdl.barrier(channel=0)   # every rank is done reading the previous step's workspaces
-            for v in self._view_order():
-                view, proj, campos, _ = cams[v]
-                c = cameras[v]
-                ws_ptr, P_ws, row0, radii_ptr = self._target(v)
-                _native.check(L.gsr_preprocess_slots(
+            order = self._view_order()
+            step = _native.MAX_VIEWS if peer else 1   # staged (nccl) slots sit at different rows: one view per call
+            for c0 in range(0, N, step):
+                chunk = order[c0:c0 + step]
+                slots, P_ws, row0 = self._view_slots(chunk, cams, cameras, None)
+                _native.check(L.gsr_preprocess_views(
                     P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["opacities"]),
-                    _ptr(p["scales"]), float(c.scale_modifier), _ptr(p["rotations"]), None, _ptr(view), _ptr(proj),
-                    _ptr(campos), float(c.tanfovx), float(c.tanfovy), radii_ptr, ws_ptr, stream, debug),
-                    "gsr_preprocess_slots")
+                    _ptr(p["scales"]), float(rs.scale_modifier), _ptr(p["rotations"]), None, len(chunk), slots,
+                    stream, debug), "gsr_preprocess_views")
             if peer:
                 self.hdl.barrier(channel=1)   # all slices of this rank's view have landed
             else:
@@ -253,14 +266,14 @@ class ShardedViewRasterizer:
                 all_to_all_rows([([self.full["grad_accum"][self.plan.rows(j)] for j in range(N)],
                                   [self.send["grad_accum"][self._slot(v)] for v in range(N)])], self.group)
             G = self.grads
-            for n, v in enumerate(self._view_order()):
-                view, proj, campos, _ = cams[v]
-                mod, tfx, tfy = scal[v]
-                ws_ptr, P_ws, row0, radii_ptr = self._target(v)
-                _native.check(L.gsr_preprocess_backward_slots(
-                    P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["scales"]), mod,
-                    _ptr(p["rotations"]), None, _ptr(view), _ptr(proj), _ptr(campos), tfx, tfy, radii_ptr, ws_ptr,
-                    _ptr(self.grad_means2D[v]), None, _ptr(G["opacities"]), _ptr(G["means3D"]), None, _ptr(G["shs"]),
-                    _ptr(G["scales"]), _ptr(G["rotations"]), 1 if n > 0 else 0, stream, debug),
-                    "gsr_preprocess_backward_slots")
+            order = self._view_order()
+            step = _native.MAX_VIEWS if self.exchange == "peer" else 1
+            for c0 in range(0, N, step):
+                chunk = order[c0:c0 + step]
+                slots, P_ws, row0 = self._view_slots(chunk, cams, None, scal)
+                _native.check(L.gsr_preprocess_backward_views(
+                    P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["scales"]),
+                    scal[r][0], _ptr(p["rotations"]), None, len(chunk), slots, None, _ptr(G["opacities"]),
+                    _ptr(G["means3D"]), None, _ptr(G["shs"]), _ptr(G["scales"]), _ptr(G["rotations"]),
+                    1 if c0 > 0 else 0, stream, debug), "gsr_preprocess_backward_views")
         return G, self.grad_means2D
