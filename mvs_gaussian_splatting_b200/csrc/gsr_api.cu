@@ -418,15 +418,33 @@ int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int wi
                          const float* cov3D_precomp, int n_views, const gsr_view_slot* views, void* stream,
                          int debug) {
     if (!views || n_views < 1 || n_views > GSR_MAX_VIEWS) return GSR_ERR_INVALID_ARGUMENT;
+    int st = check_dims(P_ws, width, height, 0);
+    if (st == GSR_OK) st = check_slots(P_ws, slot_offset, Ps);
+    if (st != GSR_OK) return st;
+    if (Ps == 0) return GSR_OK;
+    if (!means3D || !opacities) return GSR_ERR_INVALID_ARGUMENT;
+    if ((shs == nullptr) == (colors_precomp == nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    const bool has_sr = scales != nullptr && rotations != nullptr;
+    if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
+    if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
+    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+        !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
+        return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P_ws, width, height, 0, &L);
+    ForwardViewArgs args[GSR_MAX_VIEWS];
     for (int v = 0; v < n_views; ++v) {
         const gsr_view_slot& a = views[v];
-        int st = gsr_preprocess_slots(P_ws, slot_offset, Ps, D, M, width, height, means3D, shs, colors_precomp,
-                                      opacities, scales, scale_modifier, rotations, cov3D_precomp, a.viewmatrix,
-                                      a.projmatrix, a.campos, a.tanfovx, a.tanfovy, a.radii_slots, a.geom_ws, stream,
-                                      debug);
-        if (st != GSR_OK) return st;
+        if (!a.viewmatrix || !a.projmatrix || !a.campos || !a.geom_ws || !a.radii_slots) return GSR_ERR_INVALID_ARGUMENT;
+        if (!aligned16(a.geom_ws)) return GSR_ERR_WORKSPACE;
+        args[v].view = a.viewmatrix; args[v].proj = a.projmatrix; args[v].campos = a.campos;
+        args[v].tanfovx = a.tanfovx; args[v].tanfovy = a.tanfovy;
+        args[v].radii = a.radii_slots;
+        args[v].gv = offset_rows(geom_view(a.geom_ws, L), (size_t)slot_offset);
     }
-    return GSR_OK;
+    return launch_preprocess_views(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp, opacities, scales,
+                                   scale_modifier, rotations, cov3D_precomp, n_views, args,
+                                   static_cast<cudaStream_t>(stream), debug);
 }
 
 int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,

@@ -151,6 +151,17 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots,
                                int accumulate, cudaStream_t s, int debug);
 
+struct ForwardViewArgs {
+    const float* view; const float* proj; const float* campos;
+    float tanfovx, tanfovy;
+    int32_t* radii;
+    GeomView gv;
+};
+int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                            const float* colors_precomp, const float* opacities, const float* scales,
+                            float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
+                            const ForwardViewArgs* views, cudaStream_t s, int debug);
+
 // Multi-view form: the Gaussians' parameters are read once, `views` (host array, n_views <= GSR_MAX_VIEWS)
 // says per view where the camera, the forward rows (conic_opacity, rgb), radii and blend accumulators of
 // THESE P Gaussians live and where that view's dL/dmeans2D goes; parameter gradients are summed over views.

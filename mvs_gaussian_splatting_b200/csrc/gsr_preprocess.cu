@@ -25,9 +25,23 @@ __constant__ float c_SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f,  -0.4
                                  0.3731763325901154f,  -0.4570457994644658f, 1.445305721320277f,
                                  -0.5900435899266435f};
 
+constexpr int kMaxViews = GSR_MAX_VIEWS;
+
+// What differs from view to view: the camera and where the rows of that view go (possibly a peer
+// GPU's workspace, written with plain remote stores).
+struct PreView {
+    const float* view;
+    const float* proj;
+    const float* campos;
+    float tanfovx, tanfovy, focal_x, focal_y;
+    int32_t* radii;
+    GeomView gv;
+};
+
 struct PreParams {
     int P, D, M;
     int W, H, gx, gy;
+    int n_views;
     const float* means3D;
     const float* shs;
     const float* colors_precomp;
@@ -36,12 +50,7 @@ struct PreParams {
     float scale_modifier;
     const float* rotations;
     const float* cov3D_precomp;
-    const float* view;
-    const float* proj;
-    const float* campos;
-    float tanfovx, tanfovy, focal_x, focal_y;
-    int32_t* radii;
-    GeomView gv;
+    PreView v[kMaxViews];
 };
 
 // Stage a [n,3] f32 array slice for this CTA into shared memory with float4 loads.
@@ -158,6 +167,9 @@ __device__ __forceinline__ void sh_to_rgb(int deg, float dx, float dy, float dz,
     }
 }
 
+// kMulti = true: means / scales / rotation / opacity and the SH rows of the CTA are read ONCE and the
+// views are looped over (SH rows are fetched when the first view that sees the Gaussian needs them).
+template <bool kMulti>
 __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams p) {
     __shared__ float s_mean[3 * kPreThreads];
     __shared__ float s_scale[3 * kPreThreads];
@@ -169,14 +181,21 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
     const unsigned lane = lane_id();
     const int warp = threadIdx.x >> 5;
 
-    if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(p.view + threadIdx.x);
-    else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(p.proj + threadIdx.x - 16);
-    else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(p.campos + threadIdx.x - 32);
     stage_xyz(p.means3D, p.P, base, s_mean);
     if (p.scales) stage_xyz(p.scales, p.P, base, s_scale);
-    __syncthreads();
     const float* view = s_cam;
     const float* proj = s_cam + 16;
+    unsigned fetched = 0;      // SH rows of this warp already in the shared tile
+    bool have_c6 = false;      // 3D covariance (view-independent) already formed
+    float c6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+
+  for (int vi = 0; vi < p.n_views; ++vi) {
+    const PreView& V = p.v[vi];
+    if (kMulti && vi > 0) __syncthreads();  // the previous view's camera is no longer read
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(V.view + threadIdx.x);
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(V.proj + threadIdx.x - 16);
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(V.campos + threadIdx.x - 32);
+    __syncthreads();
 
     bool alive = idx < p.P;
     float mx = 0, my = 0, mz = 0, depth = 0, px = 0, py = 0, ca = 0, cb = 0, cc = 0, det_inv = 0;
@@ -194,17 +213,19 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
             const float hw = xform_row_rn(proj, 3, mx, my, mz);
             const float pw = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
             const float ndcx = __fmul_rn(hx, pw), ndcy = __fmul_rn(hy, pw);
-            float c6[6];
-            if (p.cov3D_precomp) {
-                const float2* cp = reinterpret_cast<const float2*>(p.cov3D_precomp) + 3 * (size_t)idx;
-                float2 u0 = __ldg(cp), u1 = __ldg(cp + 1), u2 = __ldg(cp + 2);
-                c6[0] = u0.x; c6[1] = u0.y; c6[2] = u1.x; c6[3] = u1.y; c6[4] = u2.x; c6[5] = u2.y;
-            } else {
-                const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
-                cov3d_from_scale_rot(s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1],
-                                     s_scale[3 * threadIdx.x + 2], p.scale_modifier, q, c6);
+            if (!have_c6) {
+                if (p.cov3D_precomp) {
+                    const float2* cp = reinterpret_cast<const float2*>(p.cov3D_precomp) + 3 * (size_t)idx;
+                    float2 u0 = __ldg(cp), u1 = __ldg(cp + 1), u2 = __ldg(cp + 2);
+                    c6[0] = u0.x; c6[1] = u0.y; c6[2] = u1.x; c6[3] = u1.y; c6[4] = u2.x; c6[5] = u2.y;
+                } else {
+                    const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                    cov3d_from_scale_rot(s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1],
+                                         s_scale[3 * threadIdx.x + 2], p.scale_modifier, q, c6);
+                }
+                have_c6 = kMulti;  // single view: nothing to keep
             }
-            cov2d_project(tx, ty, depth, p.focal_x, p.focal_y, p.tanfovx, p.tanfovy, c6, view, ca, cb, cc);
+            cov2d_project(tx, ty, depth, V.focal_x, V.focal_y, V.tanfovx, V.tanfovy, c6, view, ca, cb, cc);
             const float det = __fmaf_rn(ca, cc, -__fmul_rn(cb, cb));
             alive = det != 0.0f;
             if (alive) {
@@ -236,11 +257,13 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
         const int row = 3 * p.M;                      // floats per Gaussian in global memory
         const int need = 3 * (p.D + 1) * (p.D + 1);   // floats of the active degree
         const int warp_base = base + warp * 32;
-        const int nvis = __popc(vis);
+        const unsigned want = vis & ~fetched;   // rows this view needs that are not in the tile yet
+        fetched |= kMulti ? vis : 0u;
+        const int nvis = __popc(want);
         if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;  // float4 pieces per row (row start is 16B aligned)
             const int total = nvis * vpr;
-            const int my_src = __fns(vis, 0, lane + 1);  // lane of the (lane+1)-th surviving Gaussian
+            const int my_src = __fns(want, 0, lane + 1);  // lane of the (lane+1)-th row to fetch
             // four independent 16-byte loads in flight per lane before the first shared store
             for (int jb = 0; jb < total; jb += 128) {  // warp-uniform trip count (shuffles inside)
                 const int j0 = jb + (int)lane;
@@ -267,7 +290,7 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
             const int total = nvis * need;
             for (int j = lane; j < total; j += 32) {
                 const int v = j / need, part = j - v * need;
-                const int src_lane = __fns(vis, 0, v + 1);
+                const int src_lane = __fns(want, 0, v + 1);
                 tile[src_lane * kShStride + part] = __ldg(p.shs + (size_t)(warp_base + src_lane) * row + part);
             }
         }
@@ -279,18 +302,19 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams
     }
 
     if (idx < p.P) {
-        p.radii[idx] = alive ? rad : 0;
-        p.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
+        V.radii[idx] = alive ? rad : 0;
+        V.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
         // the depth array doubles as the key of the per-Gaussian depth sort: culled rows sink to the end
-        p.gv.depths[idx] = alive ? depth : __uint_as_float(0xFFFFFFFFu);
+        V.gv.depths[idx] = alive ? depth : __uint_as_float(0xFFFFFFFFu);
         if (alive) {
-            p.gv.means2D[idx] = make_float2(px, py);
-            p.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
+            V.gv.means2D[idx] = make_float2(px, py);
+            V.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
                                                   __fmul_rn(ca, det_inv), __ldg(p.opacities + idx));
-            p.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
+            V.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
         }
     }
-    if (lane == 0 && vis && p.gv.info) atomicAdd(&p.gv.info->num_visible, __popc(vis));
+    if (lane == 0 && vis && V.gv.info) atomicAdd(&V.gv.info->num_visible, __popc(vis));
+  }  // views
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
@@ -307,25 +331,44 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
 
 }  // namespace
 
+int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
+                            const float* colors_precomp, const float* opacities, const float* scales,
+                            float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
+                            const ForwardViewArgs* views, cudaStream_t s, int debug) {
+    if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
+    PreParams p;
+    p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H; p.gx = g.gx; p.gy = g.gy;
+    p.n_views = n_views;
+    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.opacities = opacities;
+    p.scales = scales; p.scale_modifier = scale_modifier; p.rotations = rotations;
+    p.cov3D_precomp = cov3D_precomp;
+    for (int v = 0; v < n_views; ++v) {
+        const ForwardViewArgs& a = views[v];
+        PreView& o = p.v[v];
+        o.view = a.view; o.proj = a.proj; o.campos = a.campos;
+        o.tanfovx = a.tanfovx; o.tanfovy = a.tanfovy;
+        o.focal_x = (float)g.W / (2.0f * a.tanfovx);
+        o.focal_y = (float)g.H / (2.0f * a.tanfovy);
+        o.radii = a.radii; o.gv = a.gv;
+    }
+    const int blocks = (P + kPreThreads - 1) / kPreThreads;
+    StageScope scope(kStagePreprocess, s);
+    if (n_views == 1) preprocess_kernel<false><<<blocks, kPreThreads, 0, s>>>(p);
+    else preprocess_kernel<true><<<blocks, kPreThreads, 0, s>>>(p);
+    GSR_AFTER_LAUNCH(s, debug);
+    return GSR_OK;
+}
+
 int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                       const float* colors_precomp, const float* opacities, const float* scales,
                       float scale_modifier, const float* rotations, const float* cov3D_precomp,
                       const float* view, const float* proj, const float* campos, float tanfovx,
                       float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug) {
-    PreParams p;
-    p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H; p.gx = g.gx; p.gy = g.gy;
-    p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.opacities = opacities;
-    p.scales = scales; p.scale_modifier = scale_modifier; p.rotations = rotations;
-    p.cov3D_precomp = cov3D_precomp; p.view = view; p.proj = proj; p.campos = campos;
-    p.tanfovx = tanfovx; p.tanfovy = tanfovy;
-    p.focal_x = (float)g.W / (2.0f * tanfovx);
-    p.focal_y = (float)g.H / (2.0f * tanfovy);
-    p.radii = radii; p.gv = gv;
-    const int blocks = (P + kPreThreads - 1) / kPreThreads;
-    StageScope scope(kStagePreprocess, s);
-    preprocess_kernel<<<blocks, kPreThreads, 0, s>>>(p);
-    GSR_AFTER_LAUNCH(s, debug);
-    return GSR_OK;
+    ForwardViewArgs a;
+    a.view = view; a.proj = proj; a.campos = campos; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
+    a.radii = radii; a.gv = gv;
+    return launch_preprocess_views(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
+                                   rotations, cov3D_precomp, 1, &a, s, debug);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
