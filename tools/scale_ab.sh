@@ -1,7 +1,7 @@
 # usage: bash tools/scale_ab.sh N tag mode...   (scratch: N-GPU parity check + bench per multi-GPU mode)
 N=$1; TAG=$2; shift 2
 for ex in peer nccl; do
-GSR_EXCHANGE=$ex timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 tools/sharded_check.py 2>&1 | grep "sharded_check\|FAIL\|Error\|error" | head -8
+GSR_EXCHANGE=$ex timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 tools/sharded_check.py > gpurun_out/${TAG}_check${N}_$ex.log 2>&1; grep "sharded_check\|FAIL" gpurun_out/${TAG}_check${N}_$ex.log | head -12
 done
 for m in "$@"; do
 if [ "$m" = "single" ]; then

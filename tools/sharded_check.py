@@ -7,7 +7,8 @@ Every rank renders ITS view with the ordinary single-GPU entry points on the ful
 (the reference-shaped path, itself checked against the oracle by tests/test_gpu_*.py) and with
 ShardedViewRasterizer on its slice.  Checked: image / radii / sorted key list bit-exact (same
 kernels, same geometry rows), slice gradients = sum over views of the single-GPU per-view
-gradients within 1e-5 relative (blend-backward atomics commute only up to rounding).
+gradients within 5e-5 relative L1 (north_star bar: 1e-4; blend-backward atomics and the sum over
+views commute only up to fp32 rounding).
 """
 import os
 import sys
@@ -96,11 +97,11 @@ def main():
         a, b = grads[k].double(), want[k][rows].double()
         rel = float((a - b).abs().sum() / b.abs().sum().clamp_min(1e-30))
         worst = max(worst, rel)
-        check(f"grad {k} rel_l1 {rel:.2e}", rel <= 1e-5)
+        check(f"grad {k} rel_l1 {rel:.2e}", rel <= 5e-5)
     for v in range(world):
         a, b = gm2d[v].double(), m2d[v][rows].double()
         rel = float((a - b).abs().sum() / b.abs().sum().clamp_min(1e-30))
-        check(f"means2D grad of view {v} rel_l1 {rel:.2e}", rel <= 1e-5)
+        check(f"means2D grad of view {v} rel_l1 {rel:.2e}", rel <= 5e-5)
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     if rank == 0:
