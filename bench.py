@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--forward-only", action="store_true",
+                    help="render.py path (BASELINE.json configs[4]): forward only, frames/s; combine with "
+                         "--points 6000000 --width 3840 --height 2160 [--sh-degree 0]")
     ap.add_argument("--multi", default="sharded", choices=["sharded", "sharded-nccl", "allreduce"],
                     help="N > 1: 'sharded' = Gaussian-sharded step (all-to-all of 100 B/Gaussian), "
                          "'allreduce' = replicated parameters + one 236 B/Gaussian gradient all-reduce")
@@ -560,6 +563,100 @@ def _emit(line):
 _REAL_STDOUT = 1
 
 
+def run_forward_only(args):
+    """Forward-only render path (render.py:32 -> render() -> rasterizer forward; quantize.py's SH-degree-0
+    variant with --sh-degree 0, which passes [P,1,3] SH).  One rank; frames/s with everything resident,
+    and e2e with the camera block from pinned host memory and the rendered image copied back to pinned
+    host memory every frame (what render.py does before it writes the PNG)."""
+    import torch
+    from mvs_gaussian_splatting_b200 import GaussianRasterizationSettings, _native, last_forward_stats, rasterize_forward
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device")
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+    torch.cuda.set_device(dev)
+    _native.lib()
+    W, H, P, D = args.width, args.height, args.points, args.sh_degree
+    M = (D + 1) ** 2 if D == 0 else 16
+    cam = bench_camera(0, W, H)
+    g = S.make_gaussians(P, cam, sh_coeffs=M, seed=0)
+    t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
+    kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], D)
+    cam_host = torch.from_numpy(np.concatenate([kw["viewmatrix"].ravel(), kw["projmatrix"].ravel(),
+                                                kw["campos"].ravel(), kw["bg"].ravel()]).astype(np.float32)).pin_memory()
+
+    def settings_from(block):
+        k2 = dict(kw)
+        k2.update(viewmatrix=block[0:16].view(4, 4), projmatrix=block[16:32].view(4, 4), campos=block[32:35],
+                  bg=block[35:38])
+        return GaussianRasterizationSettings(**k2)
+
+    rs = settings_from(cam_host.to(dev))
+
+    def frame(settings=rs):
+        return rasterize_forward(t["means3D"], t["shs"], None, t["opacities"], t["scales"], t["rotations"], None,
+                                 settings)[0]
+
+    for _ in range(max(args.warmup, 3)):
+        frame()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(dev.index or 0)
+    sampler.start()
+    _native.stage_timing_enable(True)
+    _native.stage_timing_read()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = _native.launch_count()
+    e0.record()
+    for _ in range(args.steps):
+        frame()
+    e1.record()
+    torch.cuda.synchronize()
+    launches = _native.launch_count() - n0
+    ms = e0.elapsed_time(e1) / args.steps
+    _native.stage_timing_enable(False)
+    stage_ms = {k: v[0] / args.steps for k, v in _native.stage_timing_read().items() if v[1]}
+    clocks = sampler.result()
+    st = last_forward_stats(dev)
+    # e2e: camera H2D + image D2H every frame, double-buffered pinned image
+    img_host = [torch.empty((3, H, W), dtype=torch.float32).pin_memory() for _ in range(2)]
+    done = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def e2e_frame(k):
+        block = cam_host.to(dev, non_blocking=True)
+        color = frame(settings_from(block))
+        done[k & 1].synchronize()                      # the copy that last used this pinned buffer is complete
+        img_host[k & 1].copy_(color, non_blocking=True)
+        done[k & 1].record()
+
+    for k in range(3):
+        e2e_frame(k)
+    torch.cuda.synchronize()
+    n = max(5, min(args.steps, 20))
+    t0 = time.perf_counter()
+    for k in range(n):
+        e2e_frame(k)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    peaks = load_peaks()
+    line = {"metric": "rasterizer_fwd_frames_per_s", "value": 1e3 / ms, "unit": "frames/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{P} Gaussians SH{D} (M={M}) {W}x{H} forward only", "baseline_config":
+                       "BASELINE.json configs[4]", "l2": "inputs larger than L2, no flush",
+                       "counts": {"P": P, "P_visible": st["num_visible"], "R": st["num_rendered"]}},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "stages_ms": stage_ms, "stage_ms_sum": sum(stage_ms.values()),
+            "roofline": {"bound": "hbm", "achieved": (52.0 * P + (67.0 + 12.0 * M) * st["num_visible"]) / (stage_ms.get("preprocess", ms) * 1e-3) / 1e9,
+                         "peak": peaks["hbm_gbs"], "unit": "GB/s", "traffic": None, "stage": "preprocess",
+                         "note": "per-stage times in stages_ms; blend_forward is FP32-issue bound (DESIGN.md 4)"},
+            "e2e": {"value": n / dt, "unit": "frames/s", "ms_per_step": 1e3 * dt / n, "steps": n,
+                    "h2d_bytes_per_step": int(cam_host.numel() * 4), "d2h_bytes_per_step": int(3 * H * W * 4),
+                    "api": "rasterize_forward (GaussianRasterizer forward under no_grad), camera from pinned host "
+                           "memory, image copied to pinned host memory every frame"},
+            "cpu_baseline": None}
+    line["roofline"]["frac"] = line["roofline"]["achieved"] / peaks["hbm_gbs"]
+    _emit(line)
+
+
 def main():
     global _REAL_STDOUT
     args = parse_args()
@@ -568,6 +665,8 @@ def main():
     os.dup2(2, 1)  # C-level writes to fd 1 (NCCL_DEBUG banners) must not pollute the JSON line
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.forward_only:
+        run_forward_only(args)
     else:
         run_b200_arm(args)
 

@@ -138,6 +138,12 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 5) preprocess_backwa
     float* tile_in = s_dyn + 36 + (threadIdx.x >> 5) * (32 * kShStride);
     float* tile = kMulti ? tile_in + kBwdWarps * 32 * kShStride : tile_in;   // dL/dsh rows of this warp
 
+    // camera of the first view: staged before anything else so no CTA barrier follows the SH fetch
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(p.v[0].view + threadIdx.x);
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(p.v[0].proj + threadIdx.x - 16);
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(p.v[0].campos + threadIdx.x - 32);
+    __syncthreads();
+
     const int idx = blockIdx.x * kBwdThreads + threadIdx.x;
     const unsigned lane = lane_id();
     const int warp = threadIdx.x >> 5;
@@ -231,8 +237,8 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 5) preprocess_backwa
 
     for (int vi = 0; vi < p.n_views; ++vi) {
         const BwdView& V = p.v[vi];
-        if (kMulti || vi == 0) {
-            if (kMulti) __syncthreads();  // the previous view's camera is no longer read
+        if (vi > 0) {
+            __syncthreads();  // the previous view's camera is no longer read
             if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(V.view + threadIdx.x);
             else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(V.proj + threadIdx.x - 16);
             else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(V.campos + threadIdx.x - 32);
@@ -432,18 +438,22 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 5) preprocess_backwa
                 if ((row & 3) == 0) {
                     const int vpr = row >> 2;
                     const int total = nrows * vpr;
+                    if (!acc) {  // the common case: pure streaming stores, unrolled
 #pragma unroll 4
-                    for (int j = lane; j < total; j += 32) {
-                        const int r = j / vpr, part = j - r * vpr;
-                        const float* sp = tile + r * kShStride + 4 * part;
-                        float4 v = make_float4(sp[0], sp[1], sp[2], sp[3]);
-                        float4* o = reinterpret_cast<float4*>(dst) + j;
-                        if (acc) {
-                            if (!((vmask >> r) & 1u)) continue;
-                            const float4 old = *o;
-                            v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
+                        for (int j = lane; j < total; j += 32) {
+                            const int r = j / vpr, part = j - r * vpr;
+                            const float* sp = tile + r * kShStride + 4 * part;
+                            __stcs(reinterpret_cast<float4*>(dst) + j, make_float4(sp[0], sp[1], sp[2], sp[3]));
                         }
-                        __stcs(o, v);
+                    } else {
+                        for (int j = lane; j < total; j += 32) {
+                            const int r = j / vpr, part = j - r * vpr;
+                            if (!((vmask >> r) & 1u)) continue;
+                            const float* sp = tile + r * kShStride + 4 * part;
+                            float4* o = reinterpret_cast<float4*>(dst) + j;
+                            const float4 old = *o;
+                            __stcs(o, make_float4(sp[0] + old.x, sp[1] + old.y, sp[2] + old.z, sp[3] + old.w));
+                        }
                     }
                 } else {
                     for (int j = lane; j < nrows * row; j += 32) {
