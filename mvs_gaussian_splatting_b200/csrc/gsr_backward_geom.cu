@@ -132,7 +132,7 @@ __device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, fl
 // kMulti = true: the Gaussian's parameters and SH row are read ONCE and the views are looped over;
 // scalar gradients accumulate in registers, dL/dsh in a second shared tile; outputs written once.
 template <bool kMulti>
-__global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 5) preprocess_backward_kernel(const BwdParams p) {
+__global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backward_kernel(const BwdParams p) {
     extern __shared__ __align__(16) float s_dyn[];
     float* s_cam = s_dyn;                                   // view[16] proj[16] campos[3]
     float* tile_in = s_dyn + 36 + (threadIdx.x >> 5) * (32 * kShStride);

@@ -170,7 +170,7 @@ __device__ __forceinline__ void sh_to_rgb(int deg, float dx, float dy, float dz,
 // kMulti = true: means / scales / rotation / opacity and the SH rows of the CTA are read ONCE and the
 // views are looped over (SH rows are fetched when the first view that sees the Gaussian needs them).
 template <bool kMulti>
-__global__ void __launch_bounds__(kPreThreads) preprocess_kernel(const PreParams p) {
+__global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel(const PreParams p) {
     __shared__ float s_mean[3 * kPreThreads];
     __shared__ float s_scale[3 * kPreThreads];
     __shared__ float s_sh[kPreWarps][32 * kShStride];
