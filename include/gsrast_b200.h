@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 3
+#define GSR_ABI_VERSION 4
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -147,6 +147,38 @@ GSR_API int gsr_backward(int P, int D, int M, int width, int height, const float
                  const float* dL_dpix, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
                  float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots, void* stream,
                  int debug);
+
+/* ---- Raw-parameter entries (no counterpart in `_C`).  The reference activates its
+ * parameters in PyTorch before every rasterizer call (scene/gaussian_model.py:152-183:
+ * scaling = exp(_scaling), rotation = normalize(_rotation), opacity = sigmoid(_opacity),
+ * features = cat(_features_dc, _features_rest)) and autograd walks the same ops backwards: > 1.5 GB of
+ * extra traffic per step at 3 M Gaussians.  These entries take the PRE-activation tensors, apply the
+ * same formulas inside preprocess / preprocess_backward, and return gradients w.r.t. the raw tensors.
+ * features_dc is [P,1,3], features_rest [P,M-1,3] (NULL when M == 1), M = SH coefficients per channel.
+ * Everything else (workspaces, gsr_forward_render, error behaviour) is as for the standard entries.
+ * gsr_activate runs the activations alone with the same device functions (shs [P,M,3], opacities [P],
+ * scales [P,3], rotations [P,4]): feeding its outputs to the standard entries reproduces the raw
+ * entries' results bit for bit (tests/test_gpu_raw.py). */
+GSR_API int gsr_forward_geometry_raw(int P, int D, int M, int width, int height, const float* means3D,
+                         const float* features_dc, const float* features_rest, const float* opacity_raw,
+                         const float* scaling_raw, float scale_modifier, const float* rotation_raw,
+                         const float* viewmatrix, const float* projmatrix, const float* campos,
+                         float tanfovx, float tanfovy, int32_t* radii, void* geom_ws,
+                         gsr_forward_info* h_info, void* stream, int debug);
+
+GSR_API int gsr_backward_raw(int P, int D, int M, int width, int height, const float* bg,
+                         const float* means3D, const float* features_dc, const float* features_rest,
+                         const float* scaling_raw, float scale_modifier, const float* rotation_raw,
+                         const float* viewmatrix, const float* projmatrix, const float* campos,
+                         float tanfovx, float tanfovy, const int32_t* radii, void* geom_ws,
+                         void* binning_ws, int64_t instance_capacity, void* image_ws, const float* dL_dpix,
+                         float* dL_dmeans2D, float* dL_dopacity_raw, float* dL_dmeans3D,
+                         float* dL_dfeatures_dc, float* dL_dfeatures_rest, float* dL_dscaling_raw,
+                         float* dL_drotation_raw, void* stream, int debug);
+
+GSR_API int gsr_activate(int P, int M, const float* features_dc, const float* features_rest,
+                         const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                         float* shs, float* opacities, float* scales, float* rotations, void* stream);
 
 /* ---- Gaussian-sharded multi-view entries (no reference equivalent: the reference is single-GPU,
  * utils/general_utils.py:133).  With N ranks, rank r owns the parameter rows of slice r and renders

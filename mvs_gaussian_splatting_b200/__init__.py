@@ -7,13 +7,14 @@ Drop-in for the one hot path of ChikaYan/mvs_gaussian_splatting: the rasterizer 
 """
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians,
                          rasterize_forward, rasterize_backward, mark_visible, RasterContext,
-                         set_capacity_hint, last_forward_stats, GradientArena, blend_pair_counts)
+                         set_capacity_hint, last_forward_stats, GradientArena, blend_pair_counts,
+                         activate, rasterize_forward_raw, rasterize_backward_raw)
 from . import _native
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
            "rasterize_forward", "rasterize_backward", "mark_visible", "RasterContext",
            "set_capacity_hint", "last_forward_stats", "GradientArena", "blend_pair_counts",
-           "build_native"]
+           "activate", "rasterize_forward_raw", "rasterize_backward_raw", "build_native"]
 
 
 def build_native(verbose: bool = False) -> str:

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -33,6 +33,7 @@ EXPORTS = (
     "gsr_stage_timing_enable", "gsr_stage_timing_read", "gsr_blend_pair_counts",
     "gsr_preprocess_slots", "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots",
     "gsr_preprocess_views", "gsr_preprocess_backward_views",
+    "gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate",
 )
 MAX_VIEWS = 16
 
@@ -173,6 +174,24 @@ def lib() -> ctypes.CDLL:
             _i, ctypes.POINTER(ViewSlot),
             _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{colors,opacity,means3D,cov3D,sh,scales,rots}
             _i, _vp, _i]                 # accumulate stream debug
+        L.gsr_forward_geometry_raw.argtypes = [
+            _i, _i, _i, _i, _i,          # P D M W H
+            _vp, _vp, _vp, _vp,          # means3D features_dc features_rest opacity_raw
+            _vp, _f, _vp,                # scaling_raw scale_modifier rotation_raw
+            _vp, _vp, _vp, _f, _f,       # view proj campos tanfovx tanfovy
+            _vp, _vp, _vp, _vp, _i]      # radii geom_ws h_info stream debug
+        L.gsr_backward_raw.argtypes = [
+            _i, _i, _i, _i, _i, _vp,     # P D M W H bg
+            _vp, _vp, _vp,               # means3D features_dc features_rest
+            _vp, _f, _vp,                # scaling_raw scale_modifier rotation_raw
+            _vp, _vp, _vp, _f, _f, _vp,  # view proj campos tanfovx tanfovy radii
+            _vp, _vp, _i64, _vp,         # geom_ws binning_ws capacity image_ws
+            _vp,                         # dL_dpix
+            _vp, _vp, _vp, _vp, _vp, _vp, _vp,  # dL_d{means2D,opacity_raw,means3D,features_dc,features_rest,scaling_raw,rotation_raw}
+            _vp, _i]                     # stream debug
+        L.gsr_activate.argtypes = [_i, _i] + [_vp] * 10
+        for name in ("gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate"):
+            getattr(L, name).restype = _i
         L.gsr_preprocess_views.restype = _i
         L.gsr_preprocess_backward_views.restype = _i
         for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",

@@ -212,7 +212,7 @@ int gsr_workspace_bytes(int P, int width, int height, int64_t instance_capacity,
     return GSR_OK;
 }
 
-int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D, const float* shs,
+static int forward_geometry_impl(const RawMode& rm, int P, int D, int M, int width, int height, const float* means3D, const float* shs,
                          const float* colors_precomp, const float* opacities, const float* scales,
                          float scale_modifier, const float* rotations, const float* cov3D_precomp,
                          const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
@@ -243,7 +243,7 @@ int gsr_forward_geometry(int P, int D, int M, int width, int height, const float
         const Grid g = make_grid(width, height);
         st = launch_preprocess(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
                                rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii,
-                               gv, s, debug);
+                               gv, s, debug, rm);
         if (st != GSR_OK) return st;
         st = launch_depth_order(P, gv, s, debug);
         if (st != GSR_OK) return st;
@@ -279,7 +279,7 @@ int gsr_forward_render(int P, int width, int height, const float* bg, const int3
     return GSR_OK;
 }
 
-int gsr_backward(int P, int D, int M, int width, int height, const float* bg, const float* means3D,
+static int backward_impl(const RawMode& rm, int P, int D, int M, int width, int height, const float* bg, const float* means3D,
                  const float* shs, const float* colors_precomp, const float* scales, float scale_modifier,
                  const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
                  const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int32_t* radii,
@@ -312,7 +312,88 @@ int gsr_backward(int P, int D, int M, int width, int height, const float* bg, co
     return launch_preprocess_backward(P, D, M, g, means3D, shs, colors_precomp != nullptr, scales, scale_modifier,
                                       rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy,
                                       radii, gv, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-                                      dL_dsh, dL_dscales, dL_drots, 0, s, debug);
+                                      dL_dsh, dL_dscales, dL_drots, 0, s, debug, rm);
+}
+
+int gsr_forward_geometry(int P, int D, int M, int width, int height, const float* means3D, const float* shs,
+                         const float* colors_precomp, const float* opacities, const float* scales,
+                         float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
+                         float tanfovy, int prefiltered, int32_t* radii, void* geom_ws, gsr_forward_info* h_info,
+                         void* stream, int debug) {
+    return forward_geometry_impl(RawMode(), P, D, M, width, height, means3D, shs, colors_precomp, opacities, scales,
+                                 scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx,
+                                 tanfovy, prefiltered, radii, geom_ws, h_info, stream, debug);
+}
+
+int gsr_backward(int P, int D, int M, int width, int height, const float* bg, const float* means3D,
+                 const float* shs, const float* colors_precomp, const float* scales, float scale_modifier,
+                 const float* rotations, const float* cov3D_precomp, const float* viewmatrix,
+                 const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int32_t* radii,
+                 void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws, const float* dL_dpix,
+                 float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
+                 float* dL_dsh, float* dL_dscales, float* dL_drots, void* stream, int debug) {
+    return backward_impl(RawMode(), P, D, M, width, height, bg, means3D, shs, colors_precomp, scales, scale_modifier,
+                         rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii, geom_ws,
+                         binning_ws, instance_capacity, image_ws, dL_dpix, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                         dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots, stream, debug);
+}
+
+// ---- raw-parameter entries -----------------------------------------------------
+static bool raw_args_ok(int M, const float* features_dc, const float* features_rest, const float* opacity_raw,
+                        const float* scaling_raw, const float* rotation_raw) {
+    if (!features_dc || !opacity_raw || !scaling_raw || !rotation_raw) return false;
+    if (M < 1 || M > 16 || (M > 1 && !features_rest)) return false;
+    return aligned16(features_dc) && aligned16(features_rest) && aligned16(scaling_raw) && aligned16(rotation_raw);
+}
+
+int gsr_forward_geometry_raw(int P, int D, int M, int width, int height, const float* means3D,
+                             const float* features_dc, const float* features_rest, const float* opacity_raw,
+                             const float* scaling_raw, float scale_modifier, const float* rotation_raw,
+                             const float* viewmatrix, const float* projmatrix, const float* campos, float tanfovx,
+                             float tanfovy, int32_t* radii, void* geom_ws, gsr_forward_info* h_info, void* stream,
+                             int debug) {
+    if (P > 0 && !raw_args_ok(M, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw))
+        return GSR_ERR_INVALID_ARGUMENT;
+    RawMode rm;
+    rm.raw = 1;
+    rm.sh_rest = M > 1 ? features_rest : features_dc;  // non-null selects the split fetch; unused when M == 1
+    return forward_geometry_impl(rm, P, D, M, width, height, means3D, features_dc, nullptr, opacity_raw, scaling_raw,
+                                 scale_modifier, rotation_raw, nullptr, viewmatrix, projmatrix, campos, tanfovx,
+                                 tanfovy, 0, radii, geom_ws, h_info, stream, debug);
+}
+
+int gsr_backward_raw(int P, int D, int M, int width, int height, const float* bg, const float* means3D,
+                     const float* features_dc, const float* features_rest, const float* scaling_raw,
+                     float scale_modifier, const float* rotation_raw, const float* viewmatrix,
+                     const float* projmatrix, const float* campos, float tanfovx, float tanfovy, const int32_t* radii,
+                     void* geom_ws, void* binning_ws, int64_t instance_capacity, void* image_ws, const float* dL_dpix,
+                     float* dL_dmeans2D, float* dL_dopacity_raw, float* dL_dmeans3D, float* dL_dfeatures_dc,
+                     float* dL_dfeatures_rest, float* dL_dscaling_raw, float* dL_drotation_raw, void* stream,
+                     int debug) {
+    if (P > 0 && (!features_dc || !scaling_raw || !rotation_raw || (M > 1 && !features_rest) || !dL_dfeatures_dc ||
+                  (M > 1 && !dL_dfeatures_rest)))
+        return GSR_ERR_INVALID_ARGUMENT;
+    RawMode rm;
+    rm.raw = 1;
+    rm.sh_rest = M > 1 ? features_rest : features_dc;
+    rm.dL_dsh_rest = M > 1 ? dL_dfeatures_rest : dL_dfeatures_dc;
+    return backward_impl(rm, P, D, M, width, height, bg, means3D, features_dc, nullptr, scaling_raw, scale_modifier,
+                         rotation_raw, nullptr, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii, geom_ws,
+                         binning_ws, instance_capacity, image_ws, dL_dpix, dL_dmeans2D, nullptr, dL_dopacity_raw,
+                         dL_dmeans3D, nullptr, dL_dfeatures_dc, dL_dscaling_raw, dL_drotation_raw, stream, debug);
+}
+
+int gsr_activate(int P, int M, const float* features_dc, const float* features_rest, const float* opacity_raw,
+                 const float* scaling_raw, const float* rotation_raw, float* shs, float* opacities, float* scales,
+                 float* rotations, void* stream) {
+    if (P < 0) return GSR_ERR_INVALID_ARGUMENT;
+    if (P == 0) return GSR_OK;
+    if (!raw_args_ok(M, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw) || !shs || !opacities ||
+        !scales || !rotations)
+        return GSR_ERR_INVALID_ARGUMENT;
+    return launch_activate(P, M, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, shs, opacities,
+                           scales, rotations, static_cast<cudaStream_t>(stream));
 }
 
 // ---- Gaussian-sharded multi-view entries ---------------------------------------------------
@@ -346,7 +427,7 @@ int gsr_preprocess_slots(int P_ws, int slot_offset, int Ps, int D, int M, int wi
     const GeomView gv = offset_rows(geom_view(geom_ws, L), (size_t)slot_offset);
     return launch_preprocess(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp, opacities, scales,
                              scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx,
-                             tanfovy, radii_slots, gv, static_cast<cudaStream_t>(stream), debug);
+                             tanfovy, radii_slots, gv, static_cast<cudaStream_t>(stream), debug, RawMode());
 }
 
 int gsr_depth_order(int P, int width, int height, void* geom_ws, gsr_forward_info* h_info, void* stream,
@@ -409,7 +490,7 @@ int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int D, int 
                                       scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix,
                                       campos, tanfovx, tanfovy, radii_slots, gv, dL_dmeans2D, dL_dcolors, dL_dopacity,
                                       dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots, accumulate != 0,
-                                      static_cast<cudaStream_t>(stream), debug);
+                                      static_cast<cudaStream_t>(stream), debug, RawMode());
 }
 
 int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,

@@ -47,6 +47,9 @@ struct BwdParams {
     const float* rotations;
     const float* cov3D_precomp;
     float *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drots;
+    int raw;               // RawMode: inputs are pre-activation, gradients are w.r.t. them
+    const float* sh_rest;  // RawMode: shs = dc [P,1,3], sh_rest = [P,M-1,3]
+    float* dL_dsh_rest;    // RawMode: dL_dsh = [P,1,3], dL_dsh_rest = [P,M-1,3]
     BwdView v[kMaxViews];
 };
 
@@ -159,7 +162,8 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     const int need = 3 * (p.D + 1) * (p.D + 1);
 
     // ---- per-Gaussian operands: issued before the SH fetch so their latency overlaps it ----
-    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+    float4 q = make_float4(1.f, 0.f, 0.f, 0.f), q_raw = q;
+    float opacity = 0.f;  // activated opacity (RawMode chain rule), from any view that sees the Gaussian
     float mx = 0.f, my = 0.f, mz = 0.f, rs0 = 0.f, rs1 = 0.f, rs2 = 0.f;
     float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, con = a0;
     uint32_t clamped_bits = 0;
@@ -168,6 +172,11 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         if (!p.cov3D_precomp) {
             q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
             rs0 = p.scales[3 * (size_t)idx]; rs1 = p.scales[3 * (size_t)idx + 1]; rs2 = p.scales[3 * (size_t)idx + 2];
+            if (p.raw) {
+                q_raw = q;
+                q = act_rotation(q);
+                rs0 = act_scale(rs0); rs1 = act_scale(rs1); rs2 = act_scale(rs2);
+            }
         }
         if (!kMulti) {  // the single view's accumulators travel with the operands
             const float4* accp = reinterpret_cast<const float4*>(p.v[0].grad_accum + (size_t)idx * 12);
@@ -180,7 +189,9 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     // ---- fetch the SH rows of the visible Gaussians of this warp ----
     if (do_sh && vmask) {
         const int nvis = __popc(vmask);
-        if ((row & 3) == 0) {
+        if (p.sh_rest) {
+            fetch_split_sh(p.shs, p.sh_rest, warp_base, p.M, need, vmask, tile_in, kShStride, lane);
+        } else if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;
             const int total = nvis * vpr;
             const int my_src = __fns(vmask, 0, lane + 1);  // lane of the (lane+1)-th visible Gaussian
@@ -257,6 +268,7 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
                 con = V.conic_opacity[idx];
                 if (do_sh) clamped_bits = __float_as_uint(V.rgb[idx].w);
             }
+            opacity = con.w;
             const float S1 = a0.x, S2 = a0.y;
             // true partials of the conic (A,B,C) and the NDC-scaled mean2D gradient
             const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
@@ -402,6 +414,19 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         for (int k = 0; k < row; ++k) rowp[k] = 0.f;
     }
 
+    // ---- RawMode: chain rules of exp / normalize / sigmoid (scene/gaussian_model.py:28-45) ----
+    if (p.raw && vis_any) {
+        gop *= opacity * (1.0f - opacity);
+        if (!p.cov3D_precomp) {
+            gs[0] *= rs0; gs[1] *= rs1; gs[2] *= rs2;
+            const float n = quat_norm(q_raw);
+            const float dotp = q.x * gq[0] + q.y * gq[1] + q.z * gq[2] + q.w * gq[3];
+            const float inv = 1.0f / n;
+            gq[0] = (gq[0] - q.x * dotp) * inv; gq[1] = (gq[1] - q.y * dotp) * inv;
+            gq[2] = (gq[2] - q.z * dotp) * inv; gq[3] = (gq[3] - q.w * dotp) * inv;
+        }
+    }
+
     // ---- outputs (every row written; in accumulate mode rows no view sees are skipped) ----
     const bool acc = p.accumulate != 0;
     if (valid && (!acc || vis_any)) {
@@ -433,7 +458,28 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         } else {
             __syncwarp();
             const int nrows = min(32, p.P - warp_base);
-            if (nrows > 0) {
+            if (nrows > 0 && p.dL_dsh_rest) {  // RawMode: dc rows -> dL_dsh [P,1,3], the rest -> dL_dsh_rest [P,M-1,3]
+                const int rr = row - 3;
+                float* ddc = p.dL_dsh + 3 * (size_t)warp_base;
+                for (int j = lane; j < 3 * nrows; j += 32) {
+                    const int r = j / 3, k = j - 3 * r;
+                    if (!acc) ddc[j] = tile[r * kShStride + k];
+                    else if ((vmask >> r) & 1u) ddc[j] += tile[r * kShStride + k];
+                }
+                float* drest = p.dL_dsh_rest + (size_t)warp_base * rr;
+                if (!acc) {
+#pragma unroll 4
+                    for (int j = lane; j < nrows * rr; j += 32) {
+                        const int r = j / rr, k = j - r * rr;
+                        __stcs(drest + j, tile[r * kShStride + 3 + k]);
+                    }
+                } else {
+                    for (int j = lane; j < nrows * rr; j += 32) {
+                        const int r = j / rr, k = j - r * rr;
+                        if ((vmask >> r) & 1u) drest[j] += tile[r * kShStride + 3 + k];
+                    }
+                }
+            } else if (nrows > 0) {
                 float* dst = p.dL_dsh + (size_t)warp_base * row;
                 if ((row & 3) == 0) {
                     const int vpr = row >> 2;
@@ -481,7 +527,7 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
                                      const float* rotations, const float* cov3D_precomp, int n_views,
                                      const BackwardViewArgs* views, float* dL_dcolors, float* dL_dopacity,
                                      float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
-                                     float* dL_drots, int accumulate, cudaStream_t s, int debug) {
+                                     float* dL_drots, int accumulate, cudaStream_t s, int debug, const RawMode& rm) {
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
     static bool attr_set = false;  // idempotent; racing threads set the same value
     if (!attr_set) {
@@ -490,6 +536,7 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
         attr_set = true;
     }
     BwdParams p;
+    p.raw = rm.raw; p.sh_rest = rm.sh_rest; p.dL_dsh_rest = rm.dL_dsh_rest;
     p.accumulate = accumulate;
     p.n_views = n_views;
     p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H;
@@ -523,13 +570,14 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                const float* proj, const float* campos, float tanfovx, float tanfovy,
                                const int32_t* radii, GeomView gv, float* dL_dmeans2D, float* dL_dcolors,
                                float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscales, float* dL_drots, int accumulate, cudaStream_t s, int debug) {
+                               float* dL_dscales, float* dL_drots, int accumulate, cudaStream_t s, int debug,
+                               const RawMode& rm) {
     BackwardViewArgs a;
     a.view = view; a.proj = proj; a.campos = campos; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
     a.radii = radii; a.gv = gv; a.dL_dmeans2D = dL_dmeans2D;
     return launch_preprocess_backward_views(P, D, M, g, means3D, shs, colors_precomp, scales, scale_modifier, rotations,
                                             cov3D_precomp, 1, &a, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-                                            dL_dsh, dL_dscales, dL_drots, accumulate, s, debug);
+                                            dL_dsh, dL_dscales, dL_drots, accumulate, s, debug, rm);
 }
 
 }  // namespace gsr

@@ -116,12 +116,14 @@ ImageView image_view(void* ws, const gsr_layout& L);
 size_t depth_sort_ctl_entries(size_t P);
 size_t tile_sort_ctl_entries(size_t cap);
 
+struct RawMode;
 // ---- stage launchers (each returns a gsr_status) ------------------------------------------
 int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                       const float* colors_precomp, const float* opacities, const float* scales,
                       float scale_modifier, const float* rotations, const float* cov3D_precomp,
                       const float* view, const float* proj, const float* campos, float tanfovx,
-                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug);
+                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug,
+                      const struct RawMode& rm);
 
 // Depth-order sort of the P (depth bits, index) pairs + prefix sum of tiles_touched in that order;
 // writes info->num_rendered on the device.
@@ -149,7 +151,18 @@ int launch_preprocess_backward(int P, int D, int M, const Grid& g, const float* 
                                const int32_t* radii, GeomView gv, float* dL_dmeans2D,
                                float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drots,
-                               int accumulate, cudaStream_t s, int debug);
+                               int accumulate, cudaStream_t s, int debug, const struct RawMode& rm);
+
+// Raw-parameter mode: the per-Gaussian inputs are the reference's PRE-activation
+// parameters (scene/gaussian_model.py:152-183): scales = log-scale, rotations = unnormalised quaternion,
+// opacities = logit, shs = _features_dc [P,1,3] and sh_rest = _features_rest [P,M-1,3].  The kernels
+// apply exp / normalize / sigmoid / the dc|rest concatenation in registers and shared memory, and the
+// backward applies their chain rules and writes dL/dsh split the same way.
+struct RawMode {
+    int raw = 0;
+    const float* sh_rest = nullptr;
+    float* dL_dsh_rest = nullptr;
+};
 
 struct ForwardViewArgs {
     const float* view; const float* proj; const float* campos;
@@ -160,7 +173,7 @@ struct ForwardViewArgs {
 int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                             const float* colors_precomp, const float* opacities, const float* scales,
                             float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
-                            const ForwardViewArgs* views, cudaStream_t s, int debug);
+                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm = RawMode());
 
 // Multi-view form: the Gaussians' parameters are read once, `views` (host array, n_views <= GSR_MAX_VIEWS)
 // says per view where the camera, the forward rows (conic_opacity, rgb), radii and blend accumulators of
@@ -177,7 +190,13 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
                                      const float* rotations, const float* cov3D_precomp, int n_views,
                                      const BackwardViewArgs* views, float* dL_dcolors, float* dL_dopacity,
                                      float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
-                                     float* dL_drots, int accumulate, cudaStream_t s, int debug);
+                                     float* dL_drots, int accumulate, cudaStream_t s, int debug,
+                                     const RawMode& rm = RawMode());
+
+// The activations alone (the unfused form of RawMode, same device functions): tests and tools.
+int launch_activate(int P, int M, const float* features_dc, const float* features_rest, const float* opacity_raw,
+                    const float* scaling_raw, const float* rotation_raw, float* shs, float* opacities, float* scales,
+                    float* rotations, cudaStream_t s);
 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);
@@ -205,6 +224,39 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx
     y0 = min(gy, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(py, -rf), 16.0f))));
     x1 = min(gx, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(px, rf), 16.0f), -1.0f), 16.0f))));
     y1 = min(gy, max(0, __float2int_rz(__fdiv_rn(__fadd_rn(__fadd_rn(__fadd_rn(py, rf), 16.0f), -1.0f), 16.0f))));
+}
+
+// ---- activations of the raw-parameter mode: the formulas of torch.exp / torch.sigmoid /
+// torch.nn.functional.normalize(eps = 1e-12) that scene/gaussian_model.py:28-45 installs ----
+__device__ __forceinline__ float act_scale(float r) { return expf(r); }
+__device__ __forceinline__ float act_opacity(float r) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-r))); }
+__device__ __forceinline__ float quat_norm(float4 q) {  // max(||q||, eps)
+    const float n2 = __fmaf_rn(q.w, q.w, __fmaf_rn(q.z, q.z, __fmaf_rn(q.y, q.y, __fmul_rn(q.x, q.x))));
+    return fmaxf(__fsqrt_rn(n2), 1e-12f);
+}
+__device__ __forceinline__ float4 act_rotation(float4 q) {
+    const float n = quat_norm(q);
+    return make_float4(__fdiv_rn(q.x, n), __fdiv_rn(q.y, n), __fdiv_rn(q.z, n), __fdiv_rn(q.w, n));
+}
+
+// Warp-cooperative fetch of SH rows stored split as dc [P,1,3] + rest [P,M-1,3] into the shared tile
+// (row r of the warp at tile + r*stride: [dc | rest]); only rows in `want` and the first `need` floats.
+__device__ __forceinline__ void fetch_split_sh(const float* __restrict__ dc, const float* __restrict__ rest,
+                                               int warp_base, int M, int need, unsigned want, float* tile,
+                                               int stride, unsigned lane) {
+    if ((want >> lane) & 1u) {
+        const float* d = dc + 3 * (size_t)(warp_base + (int)lane);
+        float* t = tile + lane * stride;
+        t[0] = __ldg(d); t[1] = __ldg(d + 1); t[2] = __ldg(d + 2);
+    }
+    const int rr = 3 * (M - 1), nr = need - 3;  // floats per rest row, floats of it that are needed
+    if (nr <= 0) return;
+    const float* base = rest + (size_t)warp_base * rr;
+#pragma unroll 4
+    for (int j = lane; j < 32 * nr; j += 32) {
+        const int r = j / nr, k = j - r * nr;
+        if ((want >> r) & 1u) tile[r * stride + 3 + k] = __ldg(base + r * rr + k);
+    }
 }
 
 __device__ __forceinline__ float ex2_approx(float x) {

@@ -50,6 +50,8 @@ struct PreParams {
     float scale_modifier;
     const float* rotations;
     const float* cov3D_precomp;
+    int raw;               // RawMode: pre-activation scales / rotations / opacities
+    const float* sh_rest;  // RawMode: shs = dc [P,1,3], sh_rest = [P,M-1,3]
     PreView v[kMaxViews];
 };
 
@@ -219,9 +221,13 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
                     float2 u0 = __ldg(cp), u1 = __ldg(cp + 1), u2 = __ldg(cp + 2);
                     c6[0] = u0.x; c6[1] = u0.y; c6[2] = u1.x; c6[3] = u1.y; c6[4] = u2.x; c6[5] = u2.y;
                 } else {
-                    const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
-                    cov3d_from_scale_rot(s_scale[3 * threadIdx.x], s_scale[3 * threadIdx.x + 1],
-                                         s_scale[3 * threadIdx.x + 2], p.scale_modifier, q, c6);
+                    float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                    float sx = s_scale[3 * threadIdx.x], sy = s_scale[3 * threadIdx.x + 1], sz = s_scale[3 * threadIdx.x + 2];
+                    if (p.raw) {
+                        q = act_rotation(q);
+                        sx = act_scale(sx); sy = act_scale(sy); sz = act_scale(sz);
+                    }
+                    cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, q, c6);
                 }
                 have_c6 = kMulti;  // single view: nothing to keep
             }
@@ -260,7 +266,9 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
         const unsigned want = vis & ~fetched;   // rows this view needs that are not in the tile yet
         fetched |= kMulti ? vis : 0u;
         const int nvis = __popc(want);
-        if ((row & 3) == 0) {
+        if (p.sh_rest) {
+            fetch_split_sh(p.shs, p.sh_rest, warp_base, p.M, need, want, tile, kShStride, lane);
+        } else if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;  // float4 pieces per row (row start is 16B aligned)
             const int total = nvis * vpr;
             const int my_src = __fns(want, 0, lane + 1);  // lane of the (lane+1)-th row to fetch
@@ -309,7 +317,8 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
         if (alive) {
             V.gv.means2D[idx] = make_float2(px, py);
             V.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
-                                                  __fmul_rn(ca, det_inv), __ldg(p.opacities + idx));
+                                                  __fmul_rn(ca, det_inv),
+                                                  p.raw ? act_opacity(__ldg(p.opacities + idx)) : __ldg(p.opacities + idx));
             V.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
         }
     }
@@ -329,14 +338,39 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
     present[idx] = xform_row_rn(m, 2, x, y, z) > kNearPlane ? 1 : 0;
 }
 
+__global__ void activate_kernel(int P, int M, const float* __restrict__ dc, const float* __restrict__ rest,
+                                const float* __restrict__ opacity_raw, const float* __restrict__ scaling_raw,
+                                const float* __restrict__ rotation_raw, float* __restrict__ shs,
+                                float* __restrict__ opacities, float* __restrict__ scales, float* __restrict__ rotations) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const size_t i = (size_t)idx;
+    opacities[i] = act_opacity(opacity_raw[i]);
+    for (int k = 0; k < 3; ++k) scales[3 * i + k] = act_scale(scaling_raw[3 * i + k]);
+    reinterpret_cast<float4*>(rotations)[i] = act_rotation(reinterpret_cast<const float4*>(rotation_raw)[i]);
+    float* row = shs + 3 * (size_t)M * i;
+    for (int k = 0; k < 3; ++k) row[k] = dc[3 * i + k];
+    for (int k = 0; k < 3 * (M - 1); ++k) row[3 + k] = rest[3 * (size_t)(M - 1) * i + k];
+}
+
 }  // namespace
+
+int launch_activate(int P, int M, const float* features_dc, const float* features_rest, const float* opacity_raw,
+                    const float* scaling_raw, const float* rotation_raw, float* shs, float* opacities, float* scales,
+                    float* rotations, cudaStream_t s) {
+    activate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, M, features_dc, features_rest, opacity_raw, scaling_raw,
+                                                    rotation_raw, shs, opacities, scales, rotations);
+    GSR_AFTER_LAUNCH(s, 0);
+    return GSR_OK;
+}
 
 int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                             const float* colors_precomp, const float* opacities, const float* scales,
                             float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
-                            const ForwardViewArgs* views, cudaStream_t s, int debug) {
+                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm) {
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
     PreParams p;
+    p.raw = rm.raw; p.sh_rest = rm.sh_rest;
     p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H; p.gx = g.gx; p.gy = g.gy;
     p.n_views = n_views;
     p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.opacities = opacities;
@@ -363,12 +397,12 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
                       const float* colors_precomp, const float* opacities, const float* scales,
                       float scale_modifier, const float* rotations, const float* cov3D_precomp,
                       const float* view, const float* proj, const float* campos, float tanfovx,
-                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug) {
+                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug, const RawMode& rm) {
     ForwardViewArgs a;
     a.view = view; a.proj = proj; a.campos = campos; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
     a.radii = radii; a.gv = gv;
     return launch_preprocess_views(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
-                                   rotations, cov3D_precomp, 1, &a, s, debug);
+                                   rotations, cov3D_precomp, 1, &a, s, debug, rm);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,

@@ -23,7 +23,8 @@ from . import _native
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
            "RasterContext", "rasterize_forward", "rasterize_backward", "mark_visible",
-           "set_capacity_hint", "last_forward_stats", "GradientArena", "blend_pair_counts"]
+           "set_capacity_hint", "last_forward_stats", "GradientArena", "blend_pair_counts",
+           "activate", "rasterize_forward_raw", "rasterize_backward_raw"]
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -240,6 +241,118 @@ def rasterize_forward(means3D, shs, colors_precomp, opacities, scales, rotations
     return color, radii, ctx, ctx_inputs
 
 
+# --------------------------------------------------------------------------------------------
+# raw-parameter entry point: activations fused into preprocess / preprocess_backward
+# --------------------------------------------------------------------------------------------
+def activate(features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw):
+    """The reference's getters (scene/gaussian_model.py:152-183) as ONE call of the library's own
+    activation kernel: returns (shs [P,M,3], opacities [P,1], scales [P,3], rotations [P,4]).  Feeding
+    these to `rasterize_forward` reproduces `rasterize_forward_raw` bit for bit."""
+    device = features_dc.device
+    if device.type != "cuda":
+        raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
+    dc, rest = _dense(features_dc, device), _dense(features_rest, device)
+    op, sc, rot = _dense(opacity_raw, device), _dense(scaling_raw, device), _dense(rotation_raw, device)
+    P = int(features_dc.shape[0])
+    M = 1 + (0 if rest is None else int(rest.shape[1]))
+    e = lambda *s: torch.empty(s, dtype=torch.float32, device=device)
+    shs, opac, scales, rots = e(P, M, 3), e(P, 1), e(P, 3), e(P, 4)
+    if P:
+        with torch.cuda.device(device):
+            stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+            _native.check(_native.lib().gsr_activate(P, M, _ptr(dc), _ptr(rest), _ptr(op), _ptr(sc), _ptr(rot),
+                                                     _ptr(shs), _ptr(opac), _ptr(scales), _ptr(rots), stream),
+                          "gsr_activate")
+    return shs, opac, scales, rots
+
+
+def rasterize_forward_raw(means3D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                          raster_settings: GaussianRasterizationSettings, capacity: Optional[int] = None):
+    """`rasterize_forward` on the reference's PRE-activation parameters (`_xyz, _features_dc [P,1,3],
+    _features_rest [P,M-1,3], _opacity, _scaling, _rotation` of scene/gaussian_model.py:56-61): exp /
+    sigmoid / normalize and the dc|rest concatenation happen inside the preprocess kernel instead of as
+    PyTorch ops around it.  Returns (color, radii, RasterContext, inputs)."""
+    rs = raster_settings
+    device = means3D.device
+    if device.type != "cuda":
+        raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
+    L = _native.lib()
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    P = int(means3D.shape[0])
+    H, W = int(rs.image_height), int(rs.image_width)
+    debug = 1 if rs.debug else 0
+    dev_idx = device.index if device.index is not None else torch.cuda.current_device()
+    means3D = _dense(means3D, device)
+    dc, rest = _dense(features_dc, device), _dense(features_rest, device)
+    op, sc, rot = _dense(opacity_raw, device), _dense(scaling_raw, device), _dense(rotation_raw, device)
+    view, proj, campos, bg = _settings_tensors(rs, device)
+    M = 1 + (0 if rest is None else int(rest.shape[1]))
+    D = int(rs.sh_degree)
+    ctx = RasterContext()
+    ctx.P, ctx.D, ctx.M, ctx.W, ctx.H = P, D, M, W, H
+    ctx.reruns = 0
+    with torch.cuda.device(device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        gb, _, ib = _native.workspace_bytes(P, W, H, 0)
+        ctx.geom_ws = torch.empty(gb, dtype=torch.uint8, device=device)
+        ctx.image_ws = torch.empty(ib, dtype=torch.uint8, device=device)
+        radii = torch.empty(P, dtype=torch.int32, device=device)
+        color = torch.empty((3, H, W), dtype=torch.float32, device=device)
+        info = _pinned_info(dev_idx)
+        _native.check(L.gsr_forward_geometry_raw(
+            P, D, M, W, H, _ptr(means3D), _ptr(dc), _ptr(rest), _ptr(op), _ptr(sc), float(rs.scale_modifier),
+            _ptr(rot), _ptr(view), _ptr(proj), _ptr(campos), float(rs.tanfovx), float(rs.tanfovy), _ptr(radii),
+            _ptr(ctx.geom_ws), ctypes.c_void_p(info.data_ptr()), stream, debug), "gsr_forward_geometry_raw")
+        _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev_idx, stream, debug)
+    return color, radii, ctx, (means3D, dc, rest, sc, rot, view, proj, campos, bg)
+
+
+def rasterize_backward_raw(ctx: RasterContext, ctx_inputs, raster_settings: GaussianRasterizationSettings,
+                           grad_out_color: torch.Tensor):
+    """Backward of `rasterize_forward_raw`: gradients w.r.t. the raw tensors, in the order
+    (means3D, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw)."""
+    rs = raster_settings
+    means3D, dc, rest, sc, rot, view, proj, campos, bg = ctx_inputs
+    device = means3D.device
+    P, M = ctx.P, ctx.M
+    g = _dense(grad_out_color, device)
+    if g is None or tuple(g.shape) != (3, ctx.H, ctx.W):
+        raise RuntimeError("grad_out_color must be [3,H,W]")
+    e = lambda *s: torch.empty(s, dtype=torch.float32, device=device)
+    d_means2D, d_means3D, d_op = e(P, 3), e(P, 3), e(P, 1)
+    d_dc, d_rest = e(P, 1, 3), (e(P, M - 1, 3) if M > 1 else None)
+    d_sc, d_rot = e(P, 3), e(P, 4)
+    with torch.cuda.device(device):
+        stream = ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        _native.check(_native.lib().gsr_backward_raw(
+            P, ctx.D, M, ctx.W, ctx.H, _ptr(bg), _ptr(means3D), _ptr(dc), _ptr(rest), _ptr(sc),
+            float(rs.scale_modifier), _ptr(rot), _ptr(view), _ptr(proj), _ptr(campos), float(rs.tanfovx),
+            float(rs.tanfovy), _ptr(ctx.radii), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws), ctx.capacity,
+            _ptr(ctx.image_ws), _ptr(g), _ptr(d_means2D), _ptr(d_op), _ptr(d_means3D), _ptr(d_dc), _ptr(d_rest),
+            _ptr(d_sc), _ptr(d_rot), stream, 1 if rs.debug else 0), "gsr_backward_raw")
+    return d_means3D, d_means2D, d_dc, d_rest, d_op, d_sc, d_rot
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                raster_settings):
+        color, radii, rctx, inputs = rasterize_forward_raw(means3D, features_dc, features_rest, opacity_raw,
+                                                           scaling_raw, rotation_raw, raster_settings)
+        ctx.raster_settings, ctx.rctx, ctx.inputs = raster_settings, rctx, inputs
+        ctx.has_rest = features_rest is not None and features_rest.numel() > 0
+        ctx.mark_non_differentiable(radii)
+        return color, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii):
+        d_means3D, d_means2D, d_dc, d_rest, d_op, d_sc, d_rot = rasterize_backward_raw(
+            ctx.rctx, ctx.inputs, ctx.raster_settings, grad_out_color)
+        ctx.rctx = ctx.inputs = None
+        return d_means3D, d_means2D, d_dc, (d_rest if ctx.has_rest else None), d_op, d_sc, d_rot, None
+
+
 class GradientArena:
     """One flat float32 buffer holding the parameter gradients of a view back to back
     (means3D [P,3] | shs [P,M,3] | opacities [P,1] | scales [P,3] | rotations [P,4], each segment
@@ -420,3 +533,13 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                    cov3D_precomp, self.raster_settings)
+
+    def forward_raw(self, means3D, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw):
+        """Same result as `forward(means3D, means2D, sigmoid(opacity_raw), shs=cat(features_dc,
+        features_rest), scales=exp(scaling_raw), rotations=normalize(rotation_raw))` — what render() builds
+        from the model's getters (gaussian_renderer/__init__.py:59-86) — with the activations and their
+        backward fused into the rasterizer's kernels; differentiable w.r.t. the raw tensors."""
+        if means3D.shape[0] == 0:
+            raise RuntimeError("forward_raw needs at least one Gaussian")
+        return _RasterizeGaussiansRaw.apply(means3D, means2D, features_dc, features_rest, opacity_raw, scaling_raw,
+                                            rotation_raw, self.raster_settings)

@@ -281,3 +281,37 @@ def rasterize(means3D, opacities, viewmatrix, projmatrix, campos, bg, W, H, tanf
         res["gblend"] = gb
         res["gpre"] = gp
     return res
+
+
+# ---------------------------------------------------------------------------------------------
+# Raw-parameter mode: the getters of scene/gaussian_model.py:152-183 with the
+# activations installed at :28-45 (torch.exp, torch.nn.functional.normalize eps=1e-12,
+# torch.sigmoid, torch.cat along dim 1), and their chain rules.  numpy restatement; pinned against
+# tests/golden/activations.npz, which is produced by the reference's own GaussianModel getters.
+# ---------------------------------------------------------------------------------------------
+def activate(features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw, dtype=np.float32):
+    dt = dtype
+    sc = np.exp(np.asarray(scaling_raw, dt))
+    q = np.asarray(rotation_raw, dt)
+    n = np.maximum(np.sqrt((q * q).sum(1, keepdims=True, dtype=dt)), dt(1e-12))
+    rot = q / n
+    op = dt(1) / (dt(1) + np.exp(-np.asarray(opacity_raw, dt)))
+    dc = np.asarray(features_dc, dt)
+    shs = dc if features_rest is None else np.concatenate([dc, np.asarray(features_rest, dt)], axis=1)
+    return dict(shs=shs, opacities=op.reshape(-1, 1), scales=sc, rotations=rot)
+
+
+def activate_backward(opacity_raw, scaling_raw, rotation_raw, g_shs, g_opacities, g_scales, g_rotations,
+                      dtype=np.float64):
+    """Gradients w.r.t. the raw tensors given gradients w.r.t. the activated ones."""
+    dt = dtype
+    act = activate(np.zeros((len(scaling_raw), 1, 3)), None, opacity_raw, scaling_raw, rotation_raw, dtype=dt)
+    op, sc, qh = act["opacities"], act["scales"], act["rotations"]
+    q = np.asarray(rotation_raw, dt)
+    n = np.maximum(np.sqrt((q * q).sum(1, keepdims=True)), dt(1e-12))
+    gq = np.asarray(g_rotations, dt)
+    g_shs = np.asarray(g_shs, dt)
+    return dict(features_dc=g_shs[:, :1], features_rest=g_shs[:, 1:],
+                opacity_raw=np.asarray(g_opacities, dt).reshape(-1, 1) * op * (1 - op),
+                scaling_raw=np.asarray(g_scales, dt) * sc,
+                rotation_raw=(gq - qh * (qh * gq).sum(1, keepdims=True)) / n)

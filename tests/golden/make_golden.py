@@ -10,6 +10,11 @@ sub-steps plus the camera conventions:
   scene/gaussian_model.py:28-32       Sigma = L L^T                      -> cov3d.npz
   utils/graphics_utils.py:38-71       getWorld2View2, getProjectionMatrix
   scene/cameras.py:54-57              transposes, full_proj, camera_center -> cameras.npz
+  scene/gaussian_model.py:28-45,152-183  the getters the rasterizer's inputs come from (exp, normalize,
+                                         sigmoid, cat of _features_dc | _features_rest) AND their autograd
+                                         gradients                        -> activations.npz
+                                         (scene.gaussian_model imports simple_knn and plyfile, which are
+                                         absent here and unused by the getters: both are stubbed)
 Those helpers hard-code device="cuda"; torch.zeros is patched to ignore the device so they run on
 the CPU unmodified.
 
@@ -119,7 +124,45 @@ def camera_fixture():
     np.savez_compressed(os.path.join(HERE, "cameras.npz"), **out)
 
 
+def activation_fixture():
+    """Raw parameters -> GaussianModel.get_scaling / get_rotation / get_opacity / get_features of the
+    reference, plus the gradients autograd sends back through them for seeded upstream gradients."""
+    import types
+    for name in ("simple_knn", "simple_knn._C", "plyfile"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["simple_knn._C"].distCUDA2 = None
+    sys.modules["plyfile"].PlyData = sys.modules["plyfile"].PlyElement = None
+    from scene.gaussian_model import GaussianModel
+    gm = GaussianModel.__new__(GaussianModel)
+    gm.setup_functions()
+    gen = torch.Generator().manual_seed(11)
+    P = 512
+    gm._scaling = (torch.randn(P, 3, generator=gen) * 1.5 - 3.0).requires_grad_(True)
+    rot = torch.randn(P, 4, generator=gen) * torch.exp(torch.randn(P, 1, generator=gen) * 2.0)
+    rot[0] = torch.tensor([1.0, 0.0, 0.0, 0.0])
+    gm._rotation = rot.requires_grad_(True)
+    gm._opacity = (torch.randn(P, 1, generator=gen) * 4.0).requires_grad_(True)
+    gm._features_dc = torch.randn(P, 1, 3, generator=gen).requires_grad_(True)
+    gm._features_rest = (torch.randn(P, 15, 3, generator=gen) * 0.15).requires_grad_(True)
+    scaling, rotation, opacity, feats = gm.get_scaling, gm.get_rotation, gm.get_opacity, gm.get_features
+    ups = dict(scaling=torch.randn(P, 3, generator=gen), rotation=torch.randn(P, 4, generator=gen),
+               opacity=torch.randn(P, 1, generator=gen), features=torch.randn(P, 16, 3, generator=gen))
+    loss = (scaling * ups["scaling"]).sum() + (rotation * ups["rotation"]).sum() + \
+           (opacity * ups["opacity"]).sum() + (feats * ups["features"]).sum()
+    loss.backward()
+    out = dict(raw_scaling=gm._scaling, raw_rotation=gm._rotation, raw_opacity=gm._opacity,
+               raw_features_dc=gm._features_dc, raw_features_rest=gm._features_rest,
+               scaling=scaling, rotation=rotation, opacity=opacity, features=feats,
+               up_scaling=ups["scaling"], up_rotation=ups["rotation"], up_opacity=ups["opacity"],
+               up_features=ups["features"], grad_scaling=gm._scaling.grad, grad_rotation=gm._rotation.grad,
+               grad_opacity=gm._opacity.grad, grad_features_dc=gm._features_dc.grad,
+               grad_features_rest=gm._features_rest.grad)
+    np.savez_compressed(os.path.join(HERE, "activations.npz"),
+                        **{k: v.detach().numpy() for k, v in out.items()})
+
+
 if __name__ == "__main__":
+    activation_fixture()
     sh_fixture()
     cov_fixture()
     camera_fixture()
