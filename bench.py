@@ -414,6 +414,8 @@ def run_b200_arm(args):
     }
     if e2e_hp is not None:
         line["e2e_host_params"] = e2e_hp
+    if world == 1:
+        line["raw_entry"] = run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
     if rank == 0:
@@ -527,6 +529,53 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
                    "pinned host memory (prefetched one step ahead on a copy stream), loss copied back to pinned "
                    "memory every step; Gaussian parameters resident in HBM (model state)"
                    + ("; N > 1: ShardedViewRasterizer.forward/backward on each rank's parameter slice" if sharded else "")}
+
+
+def run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer):
+    """the step as the reference's render() forms it — PyTorch getters (exp, sigmoid, normalize,
+    cat of _features_dc | _features_rest; scene/gaussian_model.py:152-183) around the rasterizer, autograd
+    through them — against `forward_raw`, which fuses those ops and their backward into the kernels.  Same raw
+    leaf tensors, same dL/dpixel; CUDA events, 10 steps each."""
+    sh = t["shs"]
+    raw = dict(means3D=t["means3D"], features_dc=sh[:, :1].contiguous(), features_rest=sh[:, 1:].contiguous(),
+               opacity_raw=torch.logit(t["opacities"].clamp(1e-6, 1 - 1e-6)), scaling_raw=torch.log(t["scales"]),
+               rotation_raw=t["rotations"] * 1.7)
+    leaves = {k: v.detach().clone().requires_grad_(True) for k, v in raw.items()}
+    R = GaussianRasterizer(rs)
+
+    def torch_step():
+        m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        shs = torch.cat((leaves["features_dc"], leaves["features_rest"]), dim=1)
+        color, _ = R(means3D=leaves["means3D"], means2D=m2, shs=shs, opacities=torch.sigmoid(leaves["opacity_raw"]),
+                     scales=torch.exp(leaves["scaling_raw"]),
+                     rotations=torch.nn.functional.normalize(leaves["rotation_raw"]))
+        color.backward(dL)
+
+    def fused_step():
+        m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, _ = R.forward_raw(leaves["means3D"], m2, leaves["features_dc"], leaves["features_rest"],
+                                 leaves["opacity_raw"], leaves["scaling_raw"], leaves["rotation_raw"])
+        color.backward(dL)
+
+    out = {}
+    for name, fn in (("torch_activations_ms", torch_step), ("fused_raw_ms", fused_step)):
+        for _ in range(3):
+            fn()
+            for p in leaves.values():
+                p.grad = None
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+            for p in leaves.values():
+                p.grad = None
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) / 10
+    out["note"] = ("fwd+bwd of one view from raw leaf parameters: PyTorch getters + autograd around the standard "
+                   "entry vs GaussianRasterizer.forward_raw")
+    return out
 
 
 def run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward, arena):

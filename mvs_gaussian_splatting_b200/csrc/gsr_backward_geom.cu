@@ -134,7 +134,7 @@ __device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, fl
 // kMulti = false: one view, the dL/dsh row is formed in place over the SH values (one shared tile).
 // kMulti = true: the Gaussian's parameters and SH row are read ONCE and the views are looped over;
 // scalar gradients accumulate in registers, dL/dsh in a second shared tile; outputs written once.
-template <bool kMulti>
+template <bool kMulti, bool kRaw>
 __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backward_kernel(const BwdParams p) {
     extern __shared__ __align__(16) float s_dyn[];
     float* s_cam = s_dyn;                                   // view[16] proj[16] campos[3]
@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         if (!p.cov3D_precomp) {
             q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
             rs0 = p.scales[3 * (size_t)idx]; rs1 = p.scales[3 * (size_t)idx + 1]; rs2 = p.scales[3 * (size_t)idx + 2];
-            if (p.raw) {
+            if (kRaw) {
                 q_raw = q;
                 q = act_rotation(q);
                 rs0 = act_scale(rs0); rs1 = act_scale(rs1); rs2 = act_scale(rs2);
@@ -189,8 +189,12 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     // ---- fetch the SH rows of the visible Gaussians of this warp ----
     if (do_sh && vmask) {
         const int nvis = __popc(vmask);
-        if (p.sh_rest) {
-            fetch_split_sh(p.shs, p.sh_rest, warp_base, p.M, need, vmask, tile_in, kShStride, lane);
+        if (kRaw) {  // split layout: dc [P,1,3] | rest [P,M-1,3]
+            const int nr_ = min(32, p.P - warp_base);
+            fetch_rows_f4(p.shs + 3 * (size_t)warp_base, nr_, 3, 3, 0, vmask, tile_in, kShStride, lane);
+            if (need > 3)
+                fetch_rows_f4(p.sh_rest + (size_t)warp_base * (row - 3), nr_, row - 3, need - 3, 3, vmask, tile_in,
+                              kShStride, lane);
         } else if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;
             const int total = nvis * vpr;
@@ -268,7 +272,7 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
                 con = V.conic_opacity[idx];
                 if (do_sh) clamped_bits = __float_as_uint(V.rgb[idx].w);
             }
-            opacity = con.w;
+            if (kRaw) opacity = con.w;
             const float S1 = a0.x, S2 = a0.y;
             // true partials of the conic (A,B,C) and the NDC-scaled mean2D gradient
             const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
@@ -415,7 +419,7 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     }
 
     // ---- RawMode: chain rules of exp / normalize / sigmoid (scene/gaussian_model.py:28-45) ----
-    if (p.raw && vis_any) {
+    if (kRaw && vis_any) {
         gop *= opacity * (1.0f - opacity);
         if (!p.cov3D_precomp) {
             gs[0] *= rs0; gs[1] *= rs1; gs[2] *= rs2;
@@ -458,22 +462,18 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         } else {
             __syncwarp();
             const int nrows = min(32, p.P - warp_base);
-            if (nrows > 0 && p.dL_dsh_rest) {  // RawMode: dc rows -> dL_dsh [P,1,3], the rest -> dL_dsh_rest [P,M-1,3]
+            if (kRaw && nrows > 0) {  // RawMode: dc rows -> dL_dsh [P,1,3], the rest -> dL_dsh_rest [P,M-1,3]
                 const int rr = row - 3;
                 float* ddc = p.dL_dsh + 3 * (size_t)warp_base;
-                for (int j = lane; j < 3 * nrows; j += 32) {
-                    const int r = j / 3, k = j - 3 * r;
-                    if (!acc) ddc[j] = tile[r * kShStride + k];
-                    else if ((vmask >> r) & 1u) ddc[j] += tile[r * kShStride + k];
-                }
                 float* drest = p.dL_dsh_rest + (size_t)warp_base * rr;
                 if (!acc) {
-#pragma unroll 4
-                    for (int j = lane; j < nrows * rr; j += 32) {
-                        const int r = j / rr, k = j - r * rr;
-                        __stcs(drest + j, tile[r * kShStride + 3 + k]);
-                    }
+                    store_rows_f4(ddc, nrows, 3, 0, tile, kShStride, lane);
+                    if (rr > 0) store_rows_f4(drest, nrows, rr, 3, tile, kShStride, lane);
                 } else {
+                    for (int j = lane; j < 3 * nrows; j += 32) {
+                        const int r = j / 3, k = j - 3 * r;
+                        if ((vmask >> r) & 1u) ddc[j] += tile[r * kShStride + k];
+                    }
                     for (int j = lane; j < nrows * rr; j += 32) {
                         const int r = j / rr, k = j - r * rr;
                         if ((vmask >> r) & 1u) drest[j] += tile[r * kShStride + 3 + k];
@@ -531,8 +531,10 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
     static bool attr_set = false;  // idempotent; racing threads set the same value
     if (!attr_set) {
-        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)bwd_smem_bytes(true)));
+        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, false>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
+        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
         attr_set = true;
     }
     BwdParams p;
@@ -556,10 +558,13 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     }
     StageScope scope(kStagePreprocessBwd, s);
     const unsigned blocks = (unsigned)((P + kBwdThreads - 1) / kBwdThreads);
-    if (n_views == 1)
-        preprocess_backward_kernel<false><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
-    else
-        preprocess_backward_kernel<true><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
+    if (rm.raw) {
+        if (n_views == 1) preprocess_backward_kernel<false, true><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
+        else preprocess_backward_kernel<true, true><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
+    } else {
+        if (n_views == 1) preprocess_backward_kernel<false, false><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
+        else preprocess_backward_kernel<true, false><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
+    }
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;
 }

@@ -239,23 +239,69 @@ __device__ __forceinline__ float4 act_rotation(float4 q) {
     return make_float4(__fdiv_rn(q.x, n), __fdiv_rn(q.y, n), __fdiv_rn(q.z, n), __fdiv_rn(q.w, n));
 }
 
-// Warp-cooperative fetch of SH rows stored split as dc [P,1,3] + rest [P,M-1,3] into the shared tile
-// (row r of the warp at tile + r*stride: [dc | rest]); only rows in `want` and the first `need` floats.
-__device__ __forceinline__ void fetch_split_sh(const float* __restrict__ dc, const float* __restrict__ rest,
-                                               int warp_base, int M, int need, unsigned want, float* tile,
-                                               int stride, unsigned lane) {
-    if ((want >> lane) & 1u) {
-        const float* d = dc + 3 * (size_t)(warp_base + (int)lane);
-        float* t = tile + lane * stride;
-        t[0] = __ldg(d); t[1] = __ldg(d + 1); t[2] = __ldg(d + 2);
+// Warp-cooperative copy between a contiguous global block of `nrows` rows x `rr` floats (16-byte
+// aligned start) and columns [c0, c0 + rr) of the warp's shared tile (row r at tile + r*stride), moved as
+// 16-byte pieces that may straddle two rows.  Fetch: only rows in `want` and the first `nr` floats of a
+// row are loaded / written.  Used for the split SH layout of RawMode (dc: rr = 3; rest: rr = 3(M-1)).
+__device__ __forceinline__ void fetch_rows_f4(const float* __restrict__ base, int nrows, int rr, int nr, int c0,
+                                              unsigned want, float* tile, int stride, unsigned lane) {
+    const int total = nrows * rr, nvec = total >> 2;
+    for (int jb = 0; jb < nvec; jb += 128) {
+        float4 val[4];
+        int r0[4], k0[4];
+        bool ld[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int j = jb + (int)lane + 32 * u;
+            ld[u] = false;
+            r0[u] = k0[u] = 0;
+            if (j < nvec) {
+                r0[u] = (4 * j) / rr;
+                k0[u] = 4 * j - r0[u] * rr;
+                const bool first = ((want >> r0[u]) & 1u) && k0[u] < nr;
+                const bool second = k0[u] + 3 >= rr && r0[u] + 1 < 32 && ((want >> (r0[u] + 1)) & 1u);
+                ld[u] = first || second;
+                if (ld[u]) val[u] = __ldg(reinterpret_cast<const float4*>(base) + j);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (!ld[u]) continue;
+            const float e[4] = {val[u].x, val[u].y, val[u].z, val[u].w};
+            int r = r0[u], k = k0[u];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (k >= rr) { k -= rr; ++r; }
+                if (r < 32 && ((want >> r) & 1u) && k < nr) tile[r * stride + c0 + k] = e[i];
+                ++k;
+            }
+        }
     }
-    const int rr = 3 * (M - 1), nr = need - 3;  // floats per rest row, floats of it that are needed
-    if (nr <= 0) return;
-    const float* base = rest + (size_t)warp_base * rr;
+    for (int f = 4 * nvec + (int)lane; f < total; f += 32) {
+        const int r = f / rr, k = f - r * rr;
+        if (((want >> r) & 1u) && k < nr) tile[r * stride + c0 + k] = __ldg(base + f);
+    }
+}
+
+// The reverse: columns [c0, c0 + rr) of all `nrows` tile rows -> the contiguous global block (streaming).
+__device__ __forceinline__ void store_rows_f4(float* __restrict__ base, int nrows, int rr, int c0, const float* tile,
+                                              int stride, unsigned lane) {
+    const int total = nrows * rr, nvec = total >> 2;
 #pragma unroll 4
-    for (int j = lane; j < 32 * nr; j += 32) {
-        const int r = j / nr, k = j - r * nr;
-        if ((want >> r) & 1u) tile[r * stride + 3 + k] = __ldg(base + r * rr + k);
+    for (int j = lane; j < nvec; j += 32) {
+        int r = (4 * j) / rr, k = 4 * j - r * rr;
+        float e[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (k >= rr) { k -= rr; ++r; }
+            e[i] = tile[r * stride + c0 + k];
+            ++k;
+        }
+        __stcs(reinterpret_cast<float4*>(base) + j, make_float4(e[0], e[1], e[2], e[3]));
+    }
+    for (int f = 4 * nvec + (int)lane; f < total; f += 32) {
+        const int r = f / rr, k = f - r * rr;
+        base[f] = tile[r * stride + c0 + k];
     }
 }
 

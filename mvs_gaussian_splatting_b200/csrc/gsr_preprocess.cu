@@ -171,7 +171,7 @@ __device__ __forceinline__ void sh_to_rgb(int deg, float dx, float dy, float dz,
 
 // kMulti = true: means / scales / rotation / opacity and the SH rows of the CTA are read ONCE and the
 // views are looped over (SH rows are fetched when the first view that sees the Gaussian needs them).
-template <bool kMulti>
+template <bool kMulti, bool kRaw>
 __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel(const PreParams p) {
     __shared__ float s_mean[3 * kPreThreads];
     __shared__ float s_scale[3 * kPreThreads];
@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
                 } else {
                     float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
                     float sx = s_scale[3 * threadIdx.x], sy = s_scale[3 * threadIdx.x + 1], sz = s_scale[3 * threadIdx.x + 2];
-                    if (p.raw) {
+                    if (kRaw) {
                         q = act_rotation(q);
                         sx = act_scale(sx); sy = act_scale(sy); sz = act_scale(sz);
                     }
@@ -266,8 +266,12 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
         const unsigned want = vis & ~fetched;   // rows this view needs that are not in the tile yet
         fetched |= kMulti ? vis : 0u;
         const int nvis = __popc(want);
-        if (p.sh_rest) {
-            fetch_split_sh(p.shs, p.sh_rest, warp_base, p.M, need, want, tile, kShStride, lane);
+        if (kRaw) {  // split layout: dc [P,1,3] | rest [P,M-1,3]
+            const int nrows = min(32, p.P - warp_base);
+            fetch_rows_f4(p.shs + 3 * (size_t)warp_base, nrows, 3, 3, 0, want, tile, kShStride, lane);
+            if (need > 3)
+                fetch_rows_f4(p.sh_rest + (size_t)warp_base * (row - 3), nrows, row - 3, need - 3, 3, want, tile,
+                              kShStride, lane);
         } else if ((row & 3) == 0) {
             const int vpr = (need + 3) >> 2;  // float4 pieces per row (row start is 16B aligned)
             const int total = nvis * vpr;
@@ -318,7 +322,7 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
             V.gv.means2D[idx] = make_float2(px, py);
             V.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
                                                   __fmul_rn(ca, det_inv),
-                                                  p.raw ? act_opacity(__ldg(p.opacities + idx)) : __ldg(p.opacities + idx));
+                                                  kRaw ? act_opacity(__ldg(p.opacities + idx)) : __ldg(p.opacities + idx));
             V.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
         }
     }
@@ -387,8 +391,13 @@ int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* mea
     }
     const int blocks = (P + kPreThreads - 1) / kPreThreads;
     StageScope scope(kStagePreprocess, s);
-    if (n_views == 1) preprocess_kernel<false><<<blocks, kPreThreads, 0, s>>>(p);
-    else preprocess_kernel<true><<<blocks, kPreThreads, 0, s>>>(p);
+    if (rm.raw) {
+        if (n_views == 1) preprocess_kernel<false, true><<<blocks, kPreThreads, 0, s>>>(p);
+        else preprocess_kernel<true, true><<<blocks, kPreThreads, 0, s>>>(p);
+    } else {
+        if (n_views == 1) preprocess_kernel<false, false><<<blocks, kPreThreads, 0, s>>>(p);
+        else preprocess_kernel<true, false><<<blocks, kPreThreads, 0, s>>>(p);
+    }
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;
 }
