@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 4
+#define GSR_ABI_VERSION 5
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -179,6 +179,31 @@ GSR_API int gsr_backward_raw(int P, int D, int M, int width, int height, const f
 GSR_API int gsr_activate(int P, int M, const float* features_dc, const float* features_rest,
                          const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
                          float* shs, float* opacities, float* scales, float* rotations, void* stream);
+
+/* ---- The step after backward (no counterpart in `_C`: the reference runs
+ * torch.optim.Adam(l, lr=0.0, eps=1e-15) over six parameter groups, scene/gaussian_model.py:245-268,
+ * train.py:140, and keeps per-Gaussian densification statistics with indexed PyTorch ops,
+ * train.py:130-131, scene/gaussian_model.py:775-777).  gsr_adam_step applies ONE Adam step (torch's
+ * formula: no amsgrad, no weight decay) to every group in one launch; `step` is the 1-based step count
+ * used for the bias corrections; all pointers 16-byte aligned device pointers of n floats.
+ * gsr_densification_stats: for radii[i] > 0: max_radii2D[i] = max(., radii[i]),
+ * xyz_gradient_accum[i] += ||dL_dmeans2D[i,:2]||, denom[i] += 1. */
+#define GSR_MAX_ADAM_GROUPS 16
+typedef struct gsr_adam_group {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int64_t n;
+    double lr;   /* as Python holds it: lr / (1 - beta1^step) is formed in binary64, as torch does */
+} gsr_adam_group;
+
+GSR_API int gsr_adam_step(int n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
+                          int step, void* stream);
+
+GSR_API int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D,
+                                    float* max_radii2D, float* xyz_gradient_accum, float* denom,
+                                    void* stream);
 
 /* ---- Gaussian-sharded multi-view entries (no reference equivalent: the reference is single-GPU,
  * utils/general_utils.py:133).  With N ranks, rank r owns the parameter rows of slice r and renders

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -34,7 +34,9 @@ EXPORTS = (
     "gsr_preprocess_slots", "gsr_depth_order", "gsr_blend_backward", "gsr_preprocess_backward_slots",
     "gsr_preprocess_views", "gsr_preprocess_backward_views",
     "gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate",
+    "gsr_adam_step", "gsr_densification_stats",
 )
+MAX_ADAM_GROUPS = 16
 MAX_VIEWS = 16
 
 
@@ -43,6 +45,12 @@ class ViewSlot(ctypes.Structure):
     _fields_ = [("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p),
                 ("tanfovx", ctypes.c_float), ("tanfovy", ctypes.c_float), ("geom_ws", ctypes.c_void_p),
                 ("radii_slots", ctypes.c_void_p), ("dL_dmeans2D", ctypes.c_void_p)]
+
+
+class AdamGroup(ctypes.Structure):
+    """gsr_adam_group of include/gsrast_b200.h."""
+    _fields_ = [("param", ctypes.c_void_p), ("grad", ctypes.c_void_p), ("exp_avg", ctypes.c_void_p),
+                ("exp_avg_sq", ctypes.c_void_p), ("n", ctypes.c_int64), ("lr", ctypes.c_double)]
 
 
 class ForwardInfo(ctypes.Structure):
@@ -192,6 +200,11 @@ def lib() -> ctypes.CDLL:
         L.gsr_activate.argtypes = [_i, _i] + [_vp] * 10
         for name in ("gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate"):
             getattr(L, name).restype = _i
+        _d = ctypes.c_double
+        L.gsr_adam_step.argtypes = [_i, ctypes.POINTER(AdamGroup), _d, _d, _d, _i, _vp]
+        L.gsr_densification_stats.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _vp]
+        L.gsr_adam_step.restype = _i
+        L.gsr_densification_stats.restype = _i
         L.gsr_preprocess_views.restype = _i
         L.gsr_preprocess_backward_views.restype = _i
         for name in ("gsr_workspace_bytes", "gsr_workspace_layout", "gsr_forward_geometry",

@@ -567,6 +567,21 @@ int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int 
                                             accumulate != 0, static_cast<cudaStream_t>(stream), debug);
 }
 
+int gsr_adam_step(int n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps, int step,
+                  void* stream) {
+    if (!groups) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_adam(n_groups, groups, beta1, beta2, eps, step, static_cast<cudaStream_t>(stream));
+}
+
+int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, float* max_radii2D,
+                            float* xyz_gradient_accum, float* denom, void* stream) {
+    if (P < 0) return GSR_ERR_INVALID_ARGUMENT;
+    if (P == 0) return GSR_OK;
+    if (!radii || !dL_dmeans2D || !max_radii2D || !xyz_gradient_accum || !denom) return GSR_ERR_INVALID_ARGUMENT;
+    return launch_densification_stats(P, radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom,
+                                      static_cast<cudaStream_t>(stream));
+}
+
 int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
                            int64_t instance_capacity, void* image_ws, uint64_t* d_counters, void* stream) {
     int st = check_dims(P, width, height, instance_capacity);

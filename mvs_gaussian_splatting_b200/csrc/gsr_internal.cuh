@@ -198,6 +198,12 @@ int launch_activate(int P, int M, const float* features_dc, const float* feature
                     const float* scaling_raw, const float* rotation_raw, float* shs, float* opacities, float* scales,
                     float* rotations, cudaStream_t s);
 
+// fused Adam over all parameter groups + densification statistics (gsr_optim.cu).
+int launch_adam(int n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps, int step,
+                cudaStream_t s);
+int launch_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, float* max_radii2D,
+                               float* xyz_gradient_accum, float* denom, cudaStream_t s);
+
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);
 

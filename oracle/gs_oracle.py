@@ -315,3 +315,29 @@ def activate_backward(opacity_raw, scaling_raw, rotation_raw, g_shs, g_opacities
                 opacity_raw=np.asarray(g_opacities, dt).reshape(-1, 1) * op * (1 - op),
                 scaling_raw=np.asarray(g_scales, dt) * sc,
                 rotation_raw=(gq - qh * (qh * gq).sum(1, keepdims=True)) / n)
+
+
+# ---------------------------------------------------------------------------------------------
+# The step after backward: torch.optim.Adam's single-tensor update as the reference
+# configures it (scene/gaussian_model.py:262: lr per group, betas (0.9, 0.999), eps 1e-15, no amsgrad, no
+# weight decay) and the densification statistics of train.py:130-131 / scene/gaussian_model.py:775-777.
+# numpy restatement in binary32, pinned against tests/golden/adam.npz and densification.npz.
+# ---------------------------------------------------------------------------------------------
+def adam_step(p, g, m, v, lr, step, beta1=0.9, beta2=0.999, eps=1e-15):
+    """One step in place on float32 arrays (same operation order as the CUDA kernel)."""
+    f = np.float32
+    w1, w2 = f(1.0 - beta1), f(1.0 - beta2)
+    bc1, bc2 = 1.0 - beta1 ** step, 1.0 - beta2 ** step
+    step_size, bc2_sqrt = f(lr / bc1), f(np.sqrt(bc2))
+    m += w1 * (g - m)
+    v *= f(beta2)
+    v += (w2 * g) * g
+    denom = np.sqrt(v) / bc2_sqrt + f(eps)
+    p -= step_size * (m / denom)
+
+
+def densification_stats(radii, grad, max_radii2D, xyz_gradient_accum, denom):
+    vis = radii > 0
+    max_radii2D[vis] = np.maximum(max_radii2D[vis], radii[vis].astype(np.float32))
+    xyz_gradient_accum[vis, 0] += np.sqrt(grad[vis, 0] ** 2 + grad[vis, 1] ** 2, dtype=np.float32)
+    denom[vis] += 1

@@ -15,6 +15,11 @@ sub-steps plus the camera conventions:
                                          gradients                        -> activations.npz
                                          (scene.gaussian_model imports simple_knn and plyfile, which are
                                          absent here and unused by the getters: both are stubbed)
+  scene/gaussian_model.py:245-262 + arguments/__init__.py:83-95  the optimizer: torch.optim.Adam(l, lr=0.0,
+                                         eps=1e-15) over the six named groups with the reference's learning
+                                         rates, stepped on seeded gradients   -> adam.npz
+  train.py:130-131 + scene/gaussian_model.py:775-777  max_radii2D / xyz_gradient_accum / denom updates
+                                                                             -> densification.npz
 Those helpers hard-code device="cuda"; torch.zeros is patched to ignore the device so they run on
 the CPU unmodified.
 
@@ -161,7 +166,60 @@ def activation_fixture():
                         **{k: v.detach().numpy() for k, v in out.items()})
 
 
+def adam_fixture():
+    """The optimizer exactly as GaussianModel.training_setup builds it, with OptimizationParams' defaults."""
+    from argparse import ArgumentParser
+    from arguments import OptimizationParams
+    opt = OptimizationParams(ArgumentParser())
+    gen = torch.Generator().manual_seed(21)
+    P, spatial_lr_scale = 301, 4.2          # P*3, P*45 ... not multiples of 4: exercises the kernel's tail
+    shapes = dict(xyz=(P, 3), f_dc=(P, 1, 3), f_rest=(P, 15, 3), opacity=(P, 1), scaling=(P, 3), rotation=(P, 4))
+    lrs = dict(xyz=opt.position_lr_init * spatial_lr_scale, f_dc=opt.feature_lr, f_rest=opt.feature_lr / 20.0,
+               opacity=opt.opacity_lr, scaling=opt.scaling_lr, rotation=opt.rotation_lr)
+    params = {k: torch.nn.Parameter(torch.randn(*s, generator=gen)) for k, s in shapes.items()}
+    l = [{'params': [params[k]], 'lr': lrs[k], "name": k} for k in shapes]
+    optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15)          # scene/gaussian_model.py:262
+    out = {f"p0_{k}": v.detach().clone().numpy() for k, v in params.items()}
+    out["lrs"] = np.array([lrs[k] for k in shapes], np.float64)
+    steps = 5
+    for it in range(steps):
+        for k, v in params.items():
+            scale = 10.0 ** float(torch.randint(-6, 1, (1,), generator=gen))
+            g = torch.randn(*shapes[k], generator=gen) * scale
+            if it == 2:
+                g[::3] = 0.0                                     # rows of culled Gaussians have zero gradient
+            v.grad = g
+            out[f"g{it}_{k}"] = g.numpy().copy()
+        optimizer.step()
+        for k, v in params.items():
+            out[f"p{it + 1}_{k}"] = v.detach().clone().numpy()
+    for k, v in params.items():
+        st = optimizer.state[v]
+        out[f"m_{k}"], out[f"v_{k}"] = st["exp_avg"].numpy().copy(), st["exp_avg_sq"].numpy().copy()
+    out["steps"] = np.array(steps)
+    np.savez_compressed(os.path.join(HERE, "adam.npz"), **out)
+
+
+def densification_fixture():
+    gen = torch.Generator().manual_seed(31)
+    P = 1000
+    max_radii2D = torch.rand(P, generator=gen) * 30                       # scene/gaussian_model.py:238 (float)
+    xyz_gradient_accum, denom = torch.rand(P, 1, generator=gen), torch.randint(0, 5, (P, 1), generator=gen).float()
+    radii = torch.randint(-1, 60, (P,), generator=gen).clamp_min(0).int()
+    grad = torch.randn(P, 3, generator=gen)
+    out = dict(max_radii2D0=max_radii2D.clone(), accum0=xyz_gradient_accum.clone(), denom0=denom.clone(),
+               radii=radii, grad=grad)
+    visibility_filter = radii > 0                                          # gaussian_renderer/__init__.py:311
+    max_radii2D[visibility_filter] = torch.max(max_radii2D[visibility_filter], radii[visibility_filter])   # train.py:130
+    xyz_gradient_accum[visibility_filter] += torch.norm(grad[visibility_filter, :2], dim=-1, keepdim=True)  # gaussian_model.py:776
+    denom[visibility_filter] += 1                                          # gaussian_model.py:777
+    out.update(max_radii2D1=max_radii2D, accum1=xyz_gradient_accum, denom1=denom)
+    np.savez_compressed(os.path.join(HERE, "densification.npz"), **{k: v.numpy() for k, v in out.items()})
+
+
 if __name__ == "__main__":
+    adam_fixture()
+    densification_fixture()
     activation_fixture()
     sh_fixture()
     cov_fixture()
