@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the raw_entry / optimizer_step side measurements (profiler passes)")
     ap.add_argument("--forward-only", action="store_true",
                     help="render.py path (BASELINE.json configs[4]): forward only, frames/s; combine with "
                          "--points 6000000 --width 3840 --height 2160 [--sh-degree 0]")
@@ -414,8 +416,11 @@ def run_b200_arm(args):
     }
     if e2e_hp is not None:
         line["e2e_host_params"] = e2e_hp
-    if world == 1:
+    if world == 1 and not args.no_extras:
         line["raw_entry"] = run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer)
+        line["optimizer_step"] = run_optimizer_compare(torch, dev, t)
+        line["loss_step"] = run_loss_compare(torch, dev, W, H)
+        line["train_iteration"] = run_train_iteration_compare(torch, dev, t, rs, W, H, GaussianRasterizer)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
     if rank == 0:
@@ -575,6 +580,170 @@ def run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer):
         out[name] = e0.elapsed_time(e1) / 10
     out["note"] = ("fwd+bwd of one view from raw leaf parameters: PyTorch getters + autograd around the standard "
                    "entry vs GaussianRasterizer.forward_raw")
+    return out
+
+
+def run_train_iteration_compare(torch, dev, t, rs, W, H, GaussianRasterizer):
+    """One whole training iteration on this workload, as train.py:90-142 strings it together, both ways:
+    (reference formulation) PyTorch getters -> rasterizer (standard entry) -> torch L1 + D-SSIM -> autograd ->
+    indexed densification statistics -> torch.optim.Adam over six groups;
+    (fused) forward_raw -> l1_dssim_loss -> backward -> densification_stats -> FusedAdam.
+    The rasterizer kernels are the same in both; the difference is N1 + N2 + N3 of SURVEY 8f."""
+    import math
+    from mvs_gaussian_splatting_b200.loss import l1_dssim_loss
+    from mvs_gaussian_splatting_b200.optim import FusedAdam, densification_stats
+    F = torch.nn.functional
+    sh = t["shs"]
+    raw = dict(xyz=t["means3D"], f_dc=sh[:, :1].contiguous(), f_rest=sh[:, 1:].contiguous(),
+               opacity=torch.logit(t["opacities"].clamp(1e-6, 1 - 1e-6)), scaling=torch.log(t["scales"]),
+               rotation=t["rotations"] * 1.7)
+    lrs = dict(xyz=0.00016, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05, scaling=0.005, rotation=0.001)
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    gt = torch.rand(3, H, W, generator=gen).to(dev)
+    R = GaussianRasterizer(rs)
+    P = raw["xyz"].shape[0]
+    lam = 0.2
+    out = {}
+    for name, fused in (("torch_ms", False), ("fused_ms", True)):
+        ps = {k: v.detach().clone().requires_grad_(True) for k, v in raw.items()}
+        opt = (FusedAdam if fused else torch.optim.Adam)([dict(params=[ps[k]], lr=lrs[k], name=k) for k in ps],
+                                                         lr=0.0, eps=1e-15)
+        max_radii2D = torch.zeros(P, device=dev)
+        accum, denom = torch.zeros(P, 1, device=dev), torch.zeros(P, 1, device=dev)
+
+        def iteration():
+            m2 = torch.zeros_like(ps["xyz"], requires_grad=True)
+            if fused:
+                image, radii = R.forward_raw(ps["xyz"], m2, ps["f_dc"], ps["f_rest"], ps["opacity"], ps["scaling"],
+                                             ps["rotation"])
+                loss = l1_dssim_loss(image, gt, lam)
+            else:
+                image, radii = R(means3D=ps["xyz"], means2D=m2, shs=torch.cat((ps["f_dc"], ps["f_rest"]), dim=1),
+                                 opacities=torch.sigmoid(ps["opacity"]), scales=torch.exp(ps["scaling"]),
+                                 rotations=F.normalize(ps["rotation"]))
+                g = torch.tensor([math.exp(-(i - 5) ** 2 / (2 * 1.5 ** 2)) for i in range(11)])
+                g = (g / g.sum()).unsqueeze(1)
+                win = g.mm(g.t()).float().expand(3, 1, 11, 11).contiguous().to(dev)
+                conv = lambda a: F.conv2d(a, win, padding=5, groups=3)
+                mu1, mu2 = conv(image), conv(gt)
+                mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+                s1, s2, s12 = conv(image * image) - mu1_sq, conv(gt * gt) - mu2_sq, conv(image * gt) - mu12
+                m = ((2 * mu12 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1_sq + mu2_sq + 1e-4) * (s1 + s2 + 9e-4))
+                loss = (1.0 - lam) * torch.abs(image - gt).mean() + lam * (1.0 - m.mean())
+            loss.backward()
+            with torch.no_grad():
+                if fused:
+                    densification_stats(radii, m2.grad, max_radii2D, accum, denom)
+                else:
+                    vis = radii > 0
+                    max_radii2D[vis] = torch.max(max_radii2D[vis], radii[vis])
+                    accum[vis] += torch.norm(m2.grad[vis, :2], dim=-1, keepdim=True)
+                    denom[vis] += 1
+                opt.step()
+                opt.zero_grad(set_to_none=True)
+
+        for _ in range(3):
+            iteration()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            iteration()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) / 10
+        del opt, ps
+    out["note"] = ("one training iteration (render, L1 + D-SSIM, backward, densification statistics, Adam) from raw "
+                   "leaf parameters: PyTorch ops around the rasterizer as the reference's train.py has them vs the "
+                   "fused entries (forward_raw, l1_dssim_loss, densification_stats, FusedAdam)")
+    return out
+
+
+def run_loss_compare(torch, dev, W, H):
+    """the photometric loss between forward and backward, (1 - lambda) L1 + lambda (1 - SSIM)
+    with lambda = 0.2 on a [3,H,W] image, value + gradient w.r.t. the rendered image — the torch formulation
+    the reference uses (utils/loss_utils.py:17-63: window rebuilt and uploaded per call, five zero-padded
+    grouped 11x11 conv2d, elementwise map, autograd) against l1_dssim_loss (two launches).  Algorithmic
+    bytes of the fused pair: 44 B per pixel-channel."""
+    import math
+    from mvs_gaussian_splatting_b200.loss import l1_dssim_loss
+    F = torch.nn.functional
+    gen = torch.Generator(device="cpu").manual_seed(3)
+    gt = torch.rand(3, H, W, generator=gen).to(dev)
+    img = (gt + 0.1 * torch.randn(3, H, W, generator=gen).to(dev)).clamp(0, 1)
+    lam = 0.2
+
+    def torch_step():
+        x = img.detach().requires_grad_(True)
+        g = torch.tensor([math.exp(-(i - 5) ** 2 / (2 * 1.5 ** 2)) for i in range(11)])
+        g = (g / g.sum()).unsqueeze(1)
+        win = g.mm(g.t()).float().expand(3, 1, 11, 11).contiguous().to(dev)
+        conv = lambda a: F.conv2d(a, win, padding=5, groups=3)
+        mu1, mu2 = conv(x), conv(gt)
+        mu1_sq, mu2_sq, mu12 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+        s1, s2, s12 = conv(x * x) - mu1_sq, conv(gt * gt) - mu2_sq, conv(x * gt) - mu12
+        m = ((2 * mu12 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1_sq + mu2_sq + 1e-4) * (s1 + s2 + 9e-4))
+        loss = (1.0 - lam) * torch.abs(x - gt).mean() + lam * (1.0 - m.mean())
+        loss.backward()
+        return loss
+
+    def fused_step():
+        x = img.detach().requires_grad_(True)
+        loss = l1_dssim_loss(x, gt, lam)
+        loss.backward()
+        return loss
+
+    out = {}
+    for name, fn in (("torch_loss_ms", torch_step), ("fused_loss_ms", fused_step)):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) / 10
+    out["fused_gbps"] = 44.0 * 3 * H * W / (out["fused_loss_ms"] * 1e-3) / 1e9
+    out["note"] = ("loss value + gradient w.r.t. the rendered image at this resolution: torch ops as "
+                   "utils/loss_utils.py forms them vs l1_dssim_loss (gsr_loss_forward + gsr_loss_backward)")
+    return out
+
+
+def run_optimizer_compare(torch, dev, t):
+    """the optimizer step that follows backward, on the reference's six parameter groups
+    (scene/gaussian_model.py:245-262: Adam, lr per group, eps 1e-15) at this workload's sizes —
+    torch.optim.Adam as the reference constructs it against FusedAdam (one launch for all groups).  59 floats
+    per Gaussian x 4 arrays (param, grad, exp_avg, exp_avg_sq): 7 x 4 B x 59 = 1652 algorithmic bytes/Gaussian."""
+    from mvs_gaussian_splatting_b200.optim import FusedAdam
+    sh = t["shs"]
+    shapes = dict(xyz=t["means3D"], f_dc=sh[:, :1], f_rest=sh[:, 1:], opacity=t["opacities"], scaling=t["scales"],
+                  rotation=t["rotations"])
+    lrs = dict(xyz=0.00016, f_dc=0.0025, f_rest=0.0025 / 20.0, opacity=0.05, scaling=0.005, rotation=0.001)
+    out = {}
+    floats = 0
+    for name, cls in (("torch_adam_ms", torch.optim.Adam), ("fused_adam_ms", FusedAdam)):
+        ps = {k: v.detach().clone().contiguous().requires_grad_(True) for k, v in shapes.items()}
+        for p in ps.values():
+            p.grad = torch.randn_like(p) * 1e-3
+        floats = sum(p.numel() for p in ps.values())
+        opt = cls([dict(params=[ps[k]], lr=lrs[k], name=k) for k in ps], lr=0.0, eps=1e-15)
+        for _ in range(3):
+            opt.step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            opt.step()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) / 10
+        del opt, ps
+    out["fused_gbps"] = 7 * 4 * floats / (out["fused_adam_ms"] * 1e-3) / 1e9
+    out["note"] = ("Adam step over the reference's six parameter groups at this P: torch.optim.Adam (as "
+                   "gaussian_model.training_setup builds it) vs FusedAdam, one gsr_adam_step launch; "
+                   "fused_gbps = 28 B per float / time")
     return out
 
 

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 5
+#define GSR_ABI_VERSION 6
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -204,6 +204,23 @@ GSR_API int gsr_adam_step(int n_groups, const gsr_adam_group* groups, double bet
 GSR_API int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D,
                                     float* max_radii2D, float* xyz_gradient_accum, float* denom,
                                     void* stream);
+
+/* ---- The step between forward and backward (no counterpart in `_C`: the reference forms
+ * the photometric loss with PyTorch ops, utils/loss_utils.py:17-63 — l1_loss, and ssim as five zero-padded
+ * grouped 11x11 Gaussian-window conv2d calls plus ~15 elementwise ops — combined at train.py:99-101 as
+ * (1 - lambda) * l1 + lambda * (1 - ssim), then autograd).  image / gt: [C,H,W] contiguous float device
+ * pointers.  gsr_loss_forward writes out3 = { a0 + a_l1 * l1 + a_ssim * ssim, l1, ssim } (device floats;
+ * the training loss is a0 = lambda, a_l1 = 1 - lambda, a_ssim = -lambda) and, when save_for_backward != 0,
+ * the three per-pixel partial-derivative maps gsr_loss_backward needs into the workspace
+ * (gsr_loss_workspace_bytes; 256-byte aligned).  gsr_loss_backward writes
+ * dL_dimage = upstream * d(a_l1 * l1 + a_ssim * ssim)/d image for every pixel; `upstream` is a device
+ * scalar (autograd's grad_output) or NULL for 1.  Two launches in all; no host synchronisation. */
+GSR_API int gsr_loss_workspace_bytes(int C, int H, int W, int save_for_backward, size_t* bytes);
+GSR_API int gsr_loss_forward(int C, int H, int W, const float* image, const float* gt, double a0, double a_l1,
+                             double a_ssim, void* workspace, int save_for_backward, float* out3, void* stream);
+GSR_API int gsr_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1,
+                              double a_ssim, const void* workspace, const float* upstream, float* dL_dimage,
+                              void* stream);
 
 /* ---- Gaussian-sharded multi-view entries (no reference equivalent: the reference is single-GPU,
  * utils/general_utils.py:133).  With N ranks, rank r owns the parameter rows of slice r and renders

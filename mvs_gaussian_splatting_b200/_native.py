@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -35,6 +35,7 @@ EXPORTS = (
     "gsr_preprocess_views", "gsr_preprocess_backward_views",
     "gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate",
     "gsr_adam_step", "gsr_densification_stats",
+    "gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward",
 )
 MAX_ADAM_GROUPS = 16
 MAX_VIEWS = 16
@@ -204,6 +205,11 @@ def lib() -> ctypes.CDLL:
         L.gsr_adam_step.argtypes = [_i, ctypes.POINTER(AdamGroup), _d, _d, _d, _i, _vp]
         L.gsr_densification_stats.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _vp]
         L.gsr_adam_step.restype = _i
+        L.gsr_loss_workspace_bytes.argtypes = [_i, _i, _i, _i, ctypes.POINTER(ctypes.c_size_t)]
+        L.gsr_loss_forward.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _d, _vp, _i, _vp, _vp]
+        L.gsr_loss_backward.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _vp, _vp, _vp, _vp]
+        for name in ("gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward"):
+            getattr(L, name).restype = _i
         L.gsr_densification_stats.restype = _i
         L.gsr_preprocess_views.restype = _i
         L.gsr_preprocess_backward_views.restype = _i

@@ -582,6 +582,40 @@ int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2
                                       static_cast<cudaStream_t>(stream));
 }
 
+static int check_loss_dims(int C, int H, int W) {
+    if (C <= 0 || H <= 0 || W <= 0) return GSR_ERR_INVALID_ARGUMENT;
+    if ((long long)C * H * W >= (1ll << 31) || C > 65535 || (H + 31) / 32 > 65535) return GSR_ERR_UNSUPPORTED;
+    return GSR_OK;
+}
+
+int gsr_loss_workspace_bytes(int C, int H, int W, int save_for_backward, size_t* bytes) {
+    if (!bytes) return GSR_ERR_INVALID_ARGUMENT;
+    int st = check_loss_dims(C, H, W);
+    if (st != GSR_OK) return st;
+    *bytes = loss_workspace_bytes(C, H, W, save_for_backward != 0);
+    return GSR_OK;
+}
+
+int gsr_loss_forward(int C, int H, int W, const float* image, const float* gt, double a0, double a_l1, double a_ssim,
+                     void* workspace, int save_for_backward, float* out3, void* stream) {
+    int st = check_loss_dims(C, H, W);
+    if (st != GSR_OK) return st;
+    if (!image || !gt || !out3) return GSR_ERR_INVALID_ARGUMENT;
+    if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 255)) return GSR_ERR_WORKSPACE;
+    return launch_loss_forward(C, H, W, image, gt, a0, a_l1, a_ssim, workspace, save_for_backward != 0, out3,
+                               static_cast<cudaStream_t>(stream));
+}
+
+int gsr_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1, double a_ssim,
+                      const void* workspace, const float* upstream, float* dL_dimage, void* stream) {
+    int st = check_loss_dims(C, H, W);
+    if (st != GSR_OK) return st;
+    if (!image || !gt || !dL_dimage) return GSR_ERR_INVALID_ARGUMENT;
+    if (!workspace || (reinterpret_cast<uintptr_t>(workspace) & 255)) return GSR_ERR_WORKSPACE;
+    return launch_loss_backward(C, H, W, image, gt, a_l1, a_ssim, workspace, upstream, dL_dimage,
+                                static_cast<cudaStream_t>(stream));
+}
+
 int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
                            int64_t instance_capacity, void* image_ws, uint64_t* d_counters, void* stream) {
     int st = check_dims(P, width, height, instance_capacity);

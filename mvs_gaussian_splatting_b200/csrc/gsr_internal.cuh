@@ -204,6 +204,13 @@ int launch_adam(int n_groups, const gsr_adam_group* groups, double beta1, double
 int launch_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, float* max_radii2D,
                                float* xyz_gradient_accum, float* denom, cudaStream_t s);
 
+constexpr size_t kLossHeaderBytes = 256;  // two binary64 sums + the finished-CTA counter, maps follow
+size_t loss_workspace_bytes(int C, int H, int W, bool save_for_backward);
+int launch_loss_forward(int C, int H, int W, const float* image, const float* gt, double a0, double a_l1,
+                        double a_ssim, void* workspace, bool save_for_backward, float* out3, cudaStream_t s);
+int launch_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1, double a_ssim,
+                         const void* workspace, const float* upstream, float* dL_dimage, cudaStream_t s);
+
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);
 

@@ -12,6 +12,7 @@ The functions mirror the stages of the rasterizer the reference calls at
 from __future__ import annotations
 
 import ctypes
+import math
 import os
 import subprocess
 from concurrent.futures import ThreadPoolExecutor
@@ -341,3 +342,52 @@ def densification_stats(radii, grad, max_radii2D, xyz_gradient_accum, denom):
     max_radii2D[vis] = np.maximum(max_radii2D[vis], radii[vis].astype(np.float32))
     xyz_gradient_accum[vis, 0] += np.sqrt(grad[vis, 0] ** 2 + grad[vis, 1] ** 2, dtype=np.float32)
     denom[vis] += 1
+
+
+# ---- N3: photometric loss (utils/loss_utils.py:17-63, train.py:99-101) -------------------------------------------
+def ssim_window(window_size=11, sigma=1.5):
+    """utils/loss_utils.py:23-31: binary32 1-D Gaussian normalised by its binary32 sum, 2-D window = outer product."""
+    g = np.array([math.exp(-(x - window_size // 2) ** 2 / float(2 * sigma ** 2)) for x in range(window_size)], np.float32)
+    g = (g / g.sum(dtype=np.float32)).astype(np.float32)
+    return g, np.outer(g, g).astype(np.float32)
+
+
+def _conv_same(a, w2d):
+    """Zero-padded 'same' correlation of every channel of a [C,H,W] with the 2-D window (F.conv2d, groups=C);
+    accumulated in binary64."""
+    C, H, W = a.shape
+    k = w2d.shape[0] // 2
+    pad = np.zeros((C, H + 2 * k, W + 2 * k), np.float64)
+    pad[:, k:k + H, k:k + W] = a
+    out = np.zeros((C, H, W), np.float64)
+    for dy in range(2 * k + 1):
+        for dx in range(2 * k + 1):
+            out += float(w2d[dy, dx]) * pad[:, dy:dy + H, dx:dx + W]
+    return out
+
+
+def photometric_loss(image, gt, lambda_dssim=0.2):
+    """Returns dict(l1, ssim, loss, grad, grad_ssim): l1_loss (loss_utils.py:17-18), ssim with size_average
+    (:39-63), loss = (1-lambda) l1 + lambda (1-ssim) (train.py:100-101), and the analytic gradients of loss and
+    of ssim w.r.t. `image` (what autograd computes through the five grouped convolutions)."""
+    x, y = np.asarray(image, np.float64), np.asarray(gt, np.float64)
+    _, w2d = ssim_window()
+    N = x.size
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    mu1, mu2 = _conv_same(x, w2d), _conv_same(y, w2d)
+    e11, e22, e12 = _conv_same(x * x, w2d), _conv_same(y * y, w2d), _conv_same(x * y, w2d)
+    s1, s2, s12 = e11 - mu1 * mu1, e22 - mu2 * mu2, e12 - mu1 * mu2
+    A1, A2 = 2 * mu1 * mu2 + C1, 2 * s12 + C2
+    B1, B2 = mu1 * mu1 + mu2 * mu2 + C1, s1 + s2 + C2
+    S = A1 * A2 / (B1 * B2)
+    l1, ssim = np.abs(x - y).mean() if N else 0.0, S.mean() if N else 0.0
+    # partial derivatives of the map w.r.t. the three convolution outputs that depend on `image`
+    d_mu1 = 2 * mu2 * (A2 - A1) / (B1 * B2) - 2 * mu1 * S * (1 / B1 - 1 / B2)
+    d_e11 = -S / B2
+    d_e12 = 2 * A1 / (B1 * B2)
+    # the window is symmetric: the adjoint of the correlation is the same correlation
+    g_ssim = (_conv_same(d_mu1, w2d) + 2 * x * _conv_same(d_e11, w2d) + y * _conv_same(d_e12, w2d)) / max(N, 1)
+    g_l1 = np.sign(x - y) / max(N, 1)
+    lam = float(lambda_dssim)
+    return dict(l1=l1, ssim=ssim, loss=(1.0 - lam) * l1 + lam * (1.0 - ssim),
+                grad=(1.0 - lam) * g_l1 - lam * g_ssim, grad_ssim=g_ssim)

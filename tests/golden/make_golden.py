@@ -20,6 +20,9 @@ sub-steps plus the camera conventions:
                                          rates, stepped on seeded gradients   -> adam.npz
   train.py:130-131 + scene/gaussian_model.py:775-777  max_radii2D / xyz_gradient_accum / denom updates
                                                                              -> densification.npz
+  utils/loss_utils.py:17-63 + train.py:99-101  l1_loss, ssim and the training loss
+                                         (1 - lambda) L1 + lambda (1 - SSIM) with its autograd gradient
+                                         w.r.t. the rendered image             -> loss.npz
 Those helpers hard-code device="cuda"; torch.zeros is patched to ignore the device so they run on
 the CPU unmodified.
 
@@ -217,7 +220,40 @@ def densification_fixture():
     np.savez_compressed(os.path.join(HERE, "densification.npz"), **{k: v.numpy() for k, v in out.items()})
 
 
+def loss_fixture():
+    """The photometric loss exactly as train.py:99-101 forms it from utils/loss_utils.py (CPU torch), with
+    autograd's gradient w.r.t. the rendered image.  Sizes: ragged (not tile multiples), narrower than the
+    11-tap window, one pixel, and a rendered image equal to the ground truth in places (|x-y| = 0)."""
+    from argparse import ArgumentParser
+    from arguments import OptimizationParams
+    from utils.loss_utils import l1_loss, ssim
+    lam = OptimizationParams(ArgumentParser()).lambda_dssim
+    gen = torch.Generator().manual_seed(41)
+    out = dict(lambda_dssim=np.array(lam, np.float64))
+    for n, (H, W) in enumerate(((37, 53), (9, 7), (1, 1), (64, 96))):
+        gt = torch.rand(3, H, W, generator=gen)
+        if n == 3:   # smooth images: small local variance, the regime rendered images live in
+            yy, xx = torch.meshgrid(torch.linspace(0, 1, H), torch.linspace(0, 1, W), indexing="ij")
+            gt = torch.stack([0.5 + 0.4 * torch.sin(6 * xx + c) * torch.cos(4 * yy) for c in range(3)])
+        image = (gt + 0.1 * torch.randn(3, H, W, generator=gen)).clamp(0, 1)
+        image[:, ::4, ::5] = gt[:, ::4, ::5]
+        image.requires_grad_(True)
+        Ll1 = l1_loss(image, gt)
+        s = ssim(image, gt)
+        loss = (1.0 - lam) * Ll1 + lam * (1.0 - s)           # train.py:100-101
+        loss.backward()
+        g_loss = image.grad.clone()
+        image.grad = None
+        ssim(image, gt).backward()
+        out.update({f"image{n}": image.detach().numpy(), f"gt{n}": gt.numpy(), f"l1_{n}": Ll1.detach().numpy(),
+                    f"ssim{n}": s.detach().numpy(), f"loss{n}": loss.detach().numpy(), f"grad{n}": g_loss.numpy(),
+                    f"grad_ssim{n}": image.grad.numpy().copy()})
+    out["cases"] = np.array(4)
+    np.savez_compressed(os.path.join(HERE, "loss.npz"), **out)
+
+
 if __name__ == "__main__":
+    loss_fixture()
     adam_fixture()
     densification_fixture()
     activation_fixture()

@@ -7,7 +7,7 @@ TAG=${1:-r01}
 LPS=${2:-16}   # kernel launches of libgsrast_b200.so per fwd+bwd step
 OUT=gpurun_out
 mkdir -p $OUT
-BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
+BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
 
 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest_gpu.log 2>&1
 echo "pytest exit $?" | tee -a $OUT/${TAG}_pytest_gpu.log
