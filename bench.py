@@ -389,6 +389,13 @@ def run_b200_arm(args):
     for k, r in roofs.items():
         r["traffic"] = traffic.get(k)
     dominant = max(stage_ms, key=stage_ms.get)
+    per_rank = None
+    if world > 1:   # which rank sets the pace: each rank renders a different view (different R, different blend cost)
+        mine = dict(rank=rank, num_rendered=int(counts["R"]), stage_ms_sum=round(sum(stage_ms.values()), 4),
+                    blend_ms=round(stage_ms.get("blend_forward", 0.0) + stage_ms.get("blend_backward", 0.0), 4))
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+        per_rank = gathered
 
     # ---- e2e: the public autograd API with host-side per-step inputs ----
     e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer,
@@ -416,10 +423,13 @@ def run_b200_arm(args):
     }
     if e2e_hp is not None:
         line["e2e_host_params"] = e2e_hp
+    if per_rank is not None:
+        line["per_rank"] = per_rank
     if world == 1 and not args.no_extras:
         line["raw_entry"] = run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer)
         line["optimizer_step"] = run_optimizer_compare(torch, dev, t)
         line["loss_step"] = run_loss_compare(torch, dev, W, H)
+        line["ply_io"] = run_ply_io(torch, dev, t)
         line["train_iteration"] = run_train_iteration_compare(torch, dev, t, rs, W, H, GaussianRasterizer)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
@@ -656,6 +666,56 @@ def run_train_iteration_compare(torch, dev, t, rs, W, H, GaussianRasterizer):
     out["note"] = ("one training iteration (render, L1 + D-SSIM, backward, densification statistics, Adam) from raw "
                    "leaf parameters: PyTorch ops around the rasterizer as the reference's train.py has them vs the "
                    "fused entries (forward_raw, l1_dssim_loss, densification_stats, FusedAdam)")
+    return out
+
+
+def run_ply_io(torch, dev, t):
+    """the model of this workload written to and read from a Gaussian .ply (62 binary32 per row).
+    Wall-clock of save_ply / load_ply (file system included; page cache warm for the read) and the
+    device-side (de)interleave kernels alone (CUDA events; 484 algorithmic bytes per Gaussian)."""
+    import tempfile
+    import time
+    from mvs_gaussian_splatting_b200 import _native, ply
+    sh = t["shs"]
+    args = (t["means3D"], sh[:, :1].contiguous(), sh[:, 1:].contiguous(), t["opacities"], t["scales"], t["rotations"])
+    P = args[0].shape[0]
+    out = {"P": P, "file_MB": round(P * 62 * 4 / 1e6, 1)}
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "point_cloud.ply")
+        ply.save_ply(path, *args)                                           # warm-up (pinned allocation, page cache)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ply.save_ply(path, *args)
+        out["save_ms"] = 1e3 * (time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        got = ply.load_ply(path, dev, 3)
+        torch.cuda.synchronize()
+        out["load_ms"] = 1e3 * (time.perf_counter() - t0)
+        out["round_trip_exact"] = bool(all(torch.equal(a.reshape(b.shape), b) for a, b in
+                                           zip(args, (got["xyz"], got["features_dc"], got["features_rest"],
+                                                      got["opacity"], got["scaling"], got["rotation"]))))
+    cols, _ = ply.resolve_columns(ply.attribute_names(45), 3)
+    rows = torch.empty(P * 62, device=dev)
+    import ctypes
+    ptr = lambda x: ctypes.c_void_p(x.data_ptr())
+    stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    L = _native.lib()
+    outs = [torch.empty_like(a) for a in args]
+    for name, fn in (("pack_kernel_ms", lambda: L.gsr_ply_pack(P, ctypes.byref(cols), *[ptr(a) for a in args], ptr(rows), stream)),
+                     ("unpack_kernel_ms", lambda: L.gsr_ply_unpack(P, ctypes.byref(cols), ptr(rows), *[ptr(a) for a in outs], stream))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[name] = e0.elapsed_time(e1) / 10
+        out[name.replace("_ms", "_gbps")] = 484.0 * P / (out[name] * 1e-3) / 1e9
+    out["note"] = ("save_ply / load_ply of this model (one read or write of the whole body through pinned memory, one "
+                   "H2D/D2H copy, one (de)interleave launch); kernel lines are the launches alone")
     return out
 
 

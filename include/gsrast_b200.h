@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 6
+#define GSR_ABI_VERSION 7
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -221,6 +221,33 @@ GSR_API int gsr_loss_forward(int C, int H, int W, const float* image, const floa
 GSR_API int gsr_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1,
                               double a_ssim, const void* workspace, const float* upstream, float* dL_dimage,
                               void* stream);
+
+/* ---- The on-disk format either side of the render path (no counterpart in `_C`: the
+ * reference reads and writes Gaussian .ply files with per-property Python loops over `plyfile`,
+ * scene/gaussian_model.py:279-358).  `rows` is the file body on the device: row-major [P, n_props] binary32.
+ * gsr_ply_columns gives, for every element of a row of each parameter array, its column in the file row
+ * (the caller resolves property names; f_rest is stored transposed in the file: column of
+ * features_rest[p, k, c] = column of "f_rest_{c*(M-1)+k}").  n_rest = 3*(M-1) in {0, 9, 24, 45}.
+ * gsr_ply_unpack: rows -> xyz [P,3], f_dc [P,1,3], f_rest [P,M-1,3], opacity [P,1], scale [P,3], rot [P,4].
+ * gsr_ply_pack: the reverse; columns no array maps to (nx ny nz) are written as zeros, as save_ply does.
+ * Every column may be named at most once.  `rows` must be 16-byte aligned. */
+#define GSR_PLY_MAX_PROPS 96
+typedef struct gsr_ply_columns {
+    int32_t n_props;
+    int32_t n_rest;
+    int16_t xyz[3];
+    int16_t f_dc[3];
+    int16_t f_rest[45];
+    int16_t opacity;
+    int16_t scale[3];
+    int16_t rot[4];
+} gsr_ply_columns;
+
+GSR_API int gsr_ply_unpack(int64_t P, const gsr_ply_columns* cols, const float* rows, float* xyz, float* f_dc,
+                           float* f_rest, float* opacity, float* scale, float* rot, void* stream);
+GSR_API int gsr_ply_pack(int64_t P, const gsr_ply_columns* cols, const float* xyz, const float* f_dc,
+                         const float* f_rest, const float* opacity, const float* scale, const float* rot,
+                         float* rows, void* stream);
 
 /* ---- Gaussian-sharded multi-view entries (no reference equivalent: the reference is single-GPU,
  * utils/general_utils.py:133).  With N ranks, rank r owns the parameter rows of slice r and renders

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -36,9 +36,18 @@ EXPORTS = (
     "gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate",
     "gsr_adam_step", "gsr_densification_stats",
     "gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward",
+    "gsr_ply_unpack", "gsr_ply_pack",
 )
+PLY_MAX_PROPS = 96
 MAX_ADAM_GROUPS = 16
 MAX_VIEWS = 16
+
+
+class PlyColumns(ctypes.Structure):
+    """gsr_ply_columns (include/gsrast_b200.h)."""
+    _fields_ = [("n_props", ctypes.c_int32), ("n_rest", ctypes.c_int32), ("xyz", ctypes.c_int16 * 3),
+                ("f_dc", ctypes.c_int16 * 3), ("f_rest", ctypes.c_int16 * 45), ("opacity", ctypes.c_int16),
+                ("scale", ctypes.c_int16 * 3), ("rot", ctypes.c_int16 * 4)]
 
 
 class ViewSlot(ctypes.Structure):
@@ -209,6 +218,9 @@ def lib() -> ctypes.CDLL:
         L.gsr_loss_forward.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _d, _vp, _i, _vp, _vp]
         L.gsr_loss_backward.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _vp, _vp, _vp, _vp]
         for name in ("gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward"):
+            getattr(L, name).restype = _i
+        for name in ("gsr_ply_unpack", "gsr_ply_pack"):
+            getattr(L, name).argtypes = [ctypes.c_int64, ctypes.POINTER(PlyColumns)] + [_vp] * 8
             getattr(L, name).restype = _i
         L.gsr_densification_stats.restype = _i
         L.gsr_preprocess_views.restype = _i

@@ -616,6 +616,32 @@ int gsr_loss_backward(int C, int H, int W, const float* image, const float* gt, 
                                 static_cast<cudaStream_t>(stream));
 }
 
+static int check_ply(int64_t P, const gsr_ply_columns* c, const void* rows) {
+    if (P < 0 || !c) return GSR_ERR_INVALID_ARGUMENT;
+    if (c->n_props < 14 || c->n_props > GSR_PLY_MAX_PROPS) return GSR_ERR_UNSUPPORTED;
+    if (c->n_rest != 0 && c->n_rest != 9 && c->n_rest != 24 && c->n_rest != 45) return GSR_ERR_INVALID_ARGUMENT;
+    if (P > 0 && (!rows || (reinterpret_cast<uintptr_t>(rows) & 15))) return GSR_ERR_INVALID_ARGUMENT;
+    if (P >= (1ll << 30)) return GSR_ERR_UNSUPPORTED;
+    return GSR_OK;
+}
+
+int gsr_ply_unpack(int64_t P, const gsr_ply_columns* cols, const float* rows, float* xyz, float* f_dc, float* f_rest,
+                   float* opacity, float* scale, float* rot, void* stream) {
+    int st = check_ply(P, cols, rows);
+    if (st != GSR_OK || P == 0) return st;
+    return launch_ply(false, P, cols, const_cast<float*>(rows), xyz, f_dc, f_rest, opacity, scale, rot,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int gsr_ply_pack(int64_t P, const gsr_ply_columns* cols, const float* xyz, const float* f_dc, const float* f_rest,
+                 const float* opacity, const float* scale, const float* rot, float* rows, void* stream) {
+    int st = check_ply(P, cols, rows);
+    if (st != GSR_OK || P == 0) return st;
+    return launch_ply(true, P, cols, rows, const_cast<float*>(xyz), const_cast<float*>(f_dc),
+                      const_cast<float*>(f_rest), const_cast<float*>(opacity), const_cast<float*>(scale),
+                      const_cast<float*>(rot), static_cast<cudaStream_t>(stream));
+}
+
 int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* binning_ws,
                            int64_t instance_capacity, void* image_ws, uint64_t* d_counters, void* stream) {
     int st = check_dims(P, width, height, instance_capacity);

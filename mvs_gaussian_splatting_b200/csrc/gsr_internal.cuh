@@ -211,6 +211,9 @@ int launch_loss_forward(int C, int H, int W, const float* image, const float* gt
 int launch_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1, double a_ssim,
                          const void* workspace, const float* upstream, float* dL_dimage, cudaStream_t s);
 
+int launch_ply(bool pack, int64_t P, const gsr_ply_columns* c, float* rows, float* xyz, float* f_dc, float* f_rest,
+               float* opacity, float* scale, float* rot, cudaStream_t s);
+
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,
                         cudaStream_t s);
 

@@ -391,3 +391,44 @@ def photometric_loss(image, gt, lambda_dssim=0.2):
     lam = float(lambda_dssim)
     return dict(l1=l1, ssim=ssim, loss=(1.0 - lam) * l1 + lam * (1.0 - ssim),
                 grad=(1.0 - lam) * g_l1 - lam * g_ssim, grad_ssim=g_ssim)
+
+
+# ---- N4: Gaussian .ply layout (scene/gaussian_model.py:279-358) ----------------------------------------------------
+def ply_attribute_names(n_dc=3, n_rest=45):
+    """construct_list_of_attributes (:279-291)."""
+    return (["x", "y", "z", "nx", "ny", "nz"] + [f"f_dc_{i}" for i in range(n_dc)]
+            + [f"f_rest_{i}" for i in range(n_rest)] + ["opacity"] + [f"scale_{i}" for i in range(3)]
+            + [f"rot_{i}" for i in range(4)])
+
+
+def ply_rows_from_params(xyz, features_dc, features_rest, opacity, scaling, rotation):
+    """save_ply (:293-309): the [P, n_props] binary32 matrix; features are stored transposed
+    ([P,K,3] -> [P,3,K] flattened), normals as zeros."""
+    P = xyz.shape[0]
+    f_dc = np.transpose(features_dc, (0, 2, 1)).reshape(P, 3 * features_dc.shape[1])
+    f_rest = np.transpose(features_rest, (0, 2, 1)).reshape(P, 3 * features_rest.shape[1])
+    rows = np.concatenate((xyz, np.zeros_like(xyz), f_dc, f_rest, opacity, scaling, rotation), axis=1)
+    return ply_attribute_names(f_dc.shape[1], f_rest.shape[1]), rows.astype(np.float32)
+
+
+def ply_params_from_rows(names, rows, max_sh_degree=3):
+    """load_ply (:316-358): columns found by property name; f_rest_* / scale_* / rot* sorted by numeric suffix;
+    features reshaped (P, 3, K) and transposed back to (P, K, 3)."""
+    names = [str(n) for n in names]
+    col = {n: i for i, n in enumerate(names)}
+    P = rows.shape[0]
+    by_suffix = lambda prefix: sorted((n for n in names if n.startswith(prefix)), key=lambda n: int(n.split("_")[-1]))
+    xyz = np.stack([rows[:, col[k]] for k in ("x", "y", "z")], axis=1)
+    opacity = rows[:, col["opacity"]][:, None]
+    f_dc = np.stack([rows[:, col[f"f_dc_{c}"]] for c in range(3)], axis=1).reshape(P, 3, 1)
+    extra = by_suffix("f_rest_")
+    if len(extra) != 3 * (max_sh_degree + 1) ** 2 - 3:
+        raise AssertionError("f_rest_* count does not match max_sh_degree")
+    f_rest = np.stack([rows[:, col[n]] for n in extra], axis=1).reshape(P, 3, (max_sh_degree + 1) ** 2 - 1) \
+        if extra else np.zeros((P, 3, 0), rows.dtype)
+    scaling = np.stack([rows[:, col[n]] for n in by_suffix("scale_")], axis=1)
+    rotation = np.stack([rows[:, col[n]] for n in by_suffix("rot")], axis=1)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    return dict(xyz=f32(xyz), features_dc=f32(np.transpose(f_dc, (0, 2, 1))),
+                features_rest=f32(np.transpose(f_rest, (0, 2, 1))), opacity=f32(opacity), scaling=f32(scaling),
+                rotation=f32(rotation))

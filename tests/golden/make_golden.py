@@ -23,6 +23,13 @@ sub-steps plus the camera conventions:
   utils/loss_utils.py:17-63 + train.py:99-101  l1_loss, ssim and the training loss
                                          (1 - lambda) L1 + lambda (1 - SSIM) with its autograd gradient
                                          w.r.t. the rendered image             -> loss.npz
+  scene/gaussian_model.py:279-358    save_ply / load_ply: the structured array save_ply hands to plyfile
+                                         (property names in order + the row matrix) and the six tensors
+                                         load_ply builds from it.  plyfile itself is absent here: a stand-in
+                                         captures the array save_ply describes and serves it back to load_ply
+                                         by property name, so what is pinned is the reference's column order,
+                                         feature transposition and name sorting — not plyfile's container
+                                         syntax, which is the PLY standard           -> ply.npz
 Those helpers hard-code device="cuda"; torch.zeros is patched to ignore the device so they run on
 the CPU unmodified.
 
@@ -220,6 +227,70 @@ def densification_fixture():
     np.savez_compressed(os.path.join(HERE, "densification.npz"), **{k: v.numpy() for k, v in out.items()})
 
 
+def ply_fixture():
+    import types
+    for name in ("simple_knn", "simple_knn._C", "plyfile"):
+        sys.modules.setdefault(name, types.ModuleType(name))
+    sys.modules["simple_knn._C"].distCUDA2 = None
+    captured = {}
+
+    class PlyElement:
+        @staticmethod
+        def describe(elements, name):
+            captured["elements"], captured["name"] = elements.copy(), name
+            class El:
+                data = captured["elements"]
+                properties = [types.SimpleNamespace(name=n) for n in elements.dtype.names]
+
+                def __getitem__(self, k):
+                    return self.data[k]
+            return El()
+
+    class PlyData:
+        def __init__(self, elements):
+            self.elements = elements
+
+        def write(self, path):
+            captured["path"] = path
+
+        @staticmethod
+        def read(path):
+            return PlyData([PlyElement.describe(captured["elements"], "vertex")])
+
+    sys.modules["plyfile"].PlyData, sys.modules["plyfile"].PlyElement = PlyData, PlyElement
+    import scene.gaussian_model as gmod
+    gmod.PlyData, gmod.PlyElement = PlyData, PlyElement
+    gmod.mkdir_p = lambda d: None
+    _tensor = torch.tensor
+    gmod.torch.tensor = lambda *a, **k: _tensor(*a, **{kk: v for kk, v in k.items() if kk != "device"})
+    try:
+        gen = torch.Generator().manual_seed(51)
+        P = 77
+        gm = gmod.GaussianModel.__new__(gmod.GaussianModel)
+        torch.nn.Module.__init__(gm) if isinstance(gm, torch.nn.Module) else None
+        gm.max_sh_degree = 3
+        gm._xyz = torch.randn(P, 3, generator=gen)
+        gm._features_dc = torch.randn(P, 1, 3, generator=gen)
+        gm._features_rest = torch.randn(P, 15, 3, generator=gen)
+        gm._opacity = torch.randn(P, 1, generator=gen)
+        gm._scaling = torch.randn(P, 3, generator=gen)
+        gm._rotation = torch.randn(P, 4, generator=gen)
+        gm.save_ply("/tmp/unused/point_cloud.ply")
+        el = captured["elements"]
+        names = list(el.dtype.names)
+        rows = np.stack([el[n] for n in names], axis=1).astype(np.float32)
+        g2 = gmod.GaussianModel.__new__(gmod.GaussianModel)
+        g2.max_sh_degree = 3
+        g2.load_ply("/tmp/unused/point_cloud.ply")
+        out = dict(names=np.array(names), rows=rows)
+        for k in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+            out["saved" + k] = getattr(gm, k).detach().numpy()
+            out["loaded" + k] = getattr(g2, k).detach().numpy()
+        np.savez_compressed(os.path.join(HERE, "ply.npz"), **out)
+    finally:
+        gmod.torch.tensor = _tensor
+
+
 def loss_fixture():
     """The photometric loss exactly as train.py:99-101 forms it from utils/loss_utils.py (CPU torch), with
     autograd's gradient w.r.t. the rendered image.  Sizes: ragged (not tile multiples), narrower than the
@@ -253,6 +324,7 @@ def loss_fixture():
 
 
 if __name__ == "__main__":
+    ply_fixture()
     loss_fixture()
     adam_fixture()
     densification_fixture()
