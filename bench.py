@@ -459,6 +459,7 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     rendered through GaussianRasterizer (autograd), an L1 loss is formed, backward() runs, and the
     loss is read back to the host.  The Gaussian parameters are model state and stay in HBM, as in
     the reference's training loop."""
+    from mvs_gaussian_splatting_b200.loss import l1_loss
     H, W = args.height, args.width
     gt_host = torch.from_numpy((0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)).pin_memory()
     params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
@@ -495,16 +496,17 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         if sharded is not None:
             cams = [settings_from(sl["block"][38 * v:38 * v + 38]) for v in range(world)]
             color, radii = sr.forward(slices, cams)
-            diff = color - sl["gt"]
-            loss = diff.abs().mean()
-            sr.backward(torch.sign(diff) / diff.numel())      # dL/dpixel of the L1 loss
+            color.requires_grad_(True)
+            loss = l1_loss(color, sl["gt"])                   # library loss (loss.py): one launch each way
+            loss.backward()
+            sr.backward(color.grad)
         else:
             rs = settings_from(sl["block"])
             means2D = torch.zeros_like(params["means3D"], requires_grad=True)
             color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
                                                   opacities=params["opacities"], scales=params["scales"],
                                                   rotations=params["rotations"])
-            loss = (color - sl["gt"]).abs().mean()
+            loss = l1_loss(color, sl["gt"])
             loss.backward()
             if world > 1:
                 for p in params.values():
@@ -540,7 +542,7 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         dt = float(tt.item())
     return {"value": world * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
             "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4,
-            "api": "GaussianRasterizer(settings)(...) + L1 loss + backward(), camera + ground-truth image from "
+            "api": "GaussianRasterizer(settings)(...) + l1_loss (mvs_gaussian_splatting_b200.loss) + backward(), camera + ground-truth image from "
                    "pinned host memory (prefetched one step ahead on a copy stream), loss copied back to pinned "
                    "memory every step; Gaussian parameters resident in HBM (model state)"
                    + ("; N > 1: ShardedViewRasterizer.forward/backward on each rank's parameter slice" if sharded else "")}

@@ -214,7 +214,9 @@ GSR_API int gsr_densification_stats(int P, const int32_t* radii, const float* dL
  * the three per-pixel partial-derivative maps gsr_loss_backward needs into the workspace
  * (gsr_loss_workspace_bytes; 256-byte aligned).  gsr_loss_backward writes
  * dL_dimage = upstream * d(a_l1 * l1 + a_ssim * ssim)/d image for every pixel; `upstream` is a device
- * scalar (autograd's grad_output) or NULL for 1.  Two launches in all; no host synchronisation. */
+ * scalar (autograd's grad_output) or NULL for 1.  Two launches in all; no host synchronisation.
+ * With a_ssim == 0 (l1_loss alone) both calls take a streaming L1-only path: no maps are written or read
+ * (save_for_backward may be 0) and out3[2] is 0. */
 GSR_API int gsr_loss_workspace_bytes(int C, int H, int W, int save_for_backward, size_t* bytes);
 GSR_API int gsr_loss_forward(int C, int H, int W, const float* image, const float* gt, double a0, double a_l1,
                              double a_ssim, void* workspace, int save_for_backward, float* out3, void* stream);

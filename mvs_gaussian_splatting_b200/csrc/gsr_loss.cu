@@ -20,7 +20,9 @@
 // three stored maps the same separable way and adds the L1 term's sign(x - y).
 //
 // Algorithmic bytes per pixel-channel: forward 8 in + 12 out, backward 20 in + 4 out = 44 B; HBM-bound.
+#include <algorithm>
 #include <cmath>
+#include <cstdint>
 
 #include "gsr_internal.cuh"
 
@@ -37,6 +39,7 @@ constexpr int kRowsPerThread = kTile * kTile / kLossThreads;  // 4
 
 struct LossArgs {
     int C, H, W;
+    int vec4;        // l1-only kernels: all pointers 16-byte aligned
     const float* x;  // rendered image [C,H,W]
     const float* y;  // ground truth   [C,H,W]
     float* maps;     // [3][C][H][W]: d map / d mu_x, d map / d E[x^2], d map / d E[xy]
@@ -57,6 +60,69 @@ __device__ __forceinline__ void stage_tile(float (*dst)[kIn], const float* __res
         const int gy = y0 + r - kHalo, gx = x0 + c - kHalo;
         dst[r][c] = (gy >= 0 && gy < H && gx >= 0 && gx < W) ? __ldg(plane + (size_t)gy * W + gx) : 0.f;
     }
+}
+
+// CTA sums (fixed order inside the CTA), two binary64 atomics per CTA; the last CTA to arrive writes the scalars.
+__device__ __forceinline__ void finish_sums(const LossArgs& a, float l1_sum, float ssim_sum,
+                                            float (*s_part)[kLossThreads / 32], double N) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        l1_sum += __shfl_xor_sync(0xffffffffu, l1_sum, o);
+        ssim_sum += __shfl_xor_sync(0xffffffffu, ssim_sum, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        s_part[0][threadIdx.x >> 5] = l1_sum;
+        s_part[1][threadIdx.x >> 5] = ssim_sum;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double l1 = 0.0, ss = 0.0;
+        for (int k = 0; k < kLossThreads / 32; ++k) {
+            l1 += (double)s_part[0][k];
+            ss += (double)s_part[1][k];
+        }
+        atomicAdd(a.sums + 0, l1);
+        atomicAdd(a.sums + 1, ss);
+        __threadfence();
+        unsigned* done = reinterpret_cast<unsigned*>(a.sums + 2);
+        const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+        if (atomicAdd(done, 1u) + 1u == total) {
+            __threadfence();
+            const double l1m = *reinterpret_cast<volatile double*>(a.sums + 0) / N;
+            const double ssm = *reinterpret_cast<volatile double*>(a.sums + 1) / N;
+            a.out3[0] = (float)(a.a0 + a.a_l1 * l1m + a.a_ssim * ssm);
+            a.out3[1] = (float)l1m;
+            a.out3[2] = (float)ssm;
+        }
+    }
+}
+
+// a_ssim == 0 (l1_loss alone): no moments, no maps — one streaming pass each way.
+__global__ void __launch_bounds__(kLossThreads) l1_forward_kernel(const LossArgs a) {
+    __shared__ float s_part[2][kLossThreads / 32];
+    const long long n = (long long)a.C * a.H * a.W, n4 = a.vec4 ? n >> 2 : 0;
+    const long long stride = (long long)gridDim.x * kLossThreads;
+    float sum = 0.f;
+    for (long long i = (long long)blockIdx.x * kLossThreads + threadIdx.x; i < n4; i += stride) {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(a.x) + i), y = __ldg(reinterpret_cast<const float4*>(a.y) + i);
+        sum += (fabsf(x.x - y.x) + fabsf(x.y - y.y)) + (fabsf(x.z - y.z) + fabsf(x.w - y.w));
+    }
+    if (blockIdx.x == 0)
+        for (long long i = 4 * n4 + threadIdx.x; i < n; i += kLossThreads) sum += fabsf(a.x[i] - a.y[i]);
+    finish_sums(a, sum, 0.f, s_part, (double)n);
+}
+
+__global__ void __launch_bounds__(kLossThreads) l1_backward_kernel(const LossArgs a) {
+    const long long n = (long long)a.C * a.H * a.W, n4 = a.vec4 ? n >> 2 : 0;
+    const long long stride = (long long)gridDim.x * kLossThreads;
+    const float k = (a.upstream ? __ldg(a.upstream) : 1.f) * a.coef_l1;
+    auto sgn = [k](float d) { return d > 0.f ? k : (d < 0.f ? -k : 0.f); };
+    for (long long i = (long long)blockIdx.x * kLossThreads + threadIdx.x; i < n4; i += stride) {
+        const float4 x = __ldg(reinterpret_cast<const float4*>(a.x) + i), y = __ldg(reinterpret_cast<const float4*>(a.y) + i);
+        reinterpret_cast<float4*>(a.dL_dx)[i] = make_float4(sgn(x.x - y.x), sgn(x.y - y.y), sgn(x.z - y.z), sgn(x.w - y.w));
+    }
+    if (blockIdx.x == 0)
+        for (long long i = 4 * n4 + threadIdx.x; i < n; i += kLossThreads) a.dL_dx[i] = sgn(a.x[i] - a.y[i]);
 }
 
 __global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(const LossArgs a) {
@@ -130,38 +196,7 @@ __global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(const LossAr
             a.maps[2 * n + at] = 2.f * A1 * inv_B;
         }
     }
-    // CTA sums (fixed order inside the CTA), then two binary64 atomics per CTA
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        l1_sum += __shfl_xor_sync(0xffffffffu, l1_sum, o);
-        ssim_sum += __shfl_xor_sync(0xffffffffu, ssim_sum, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        s_part[0][threadIdx.x >> 5] = l1_sum;
-        s_part[1][threadIdx.x >> 5] = ssim_sum;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double l1 = 0.0, ss = 0.0;
-        for (int k = 0; k < kLossThreads / 32; ++k) {
-            l1 += (double)s_part[0][k];
-            ss += (double)s_part[1][k];
-        }
-        atomicAdd(a.sums + 0, l1);
-        atomicAdd(a.sums + 1, ss);
-        __threadfence();
-        unsigned* done = reinterpret_cast<unsigned*>(a.sums + 2);
-        const unsigned total = gridDim.x * gridDim.y * gridDim.z;
-        if (atomicAdd(done, 1u) + 1u == total) {
-            __threadfence();
-            const double N = (double)a.C * (double)plane;
-            const double l1m = *reinterpret_cast<volatile double*>(a.sums + 0) / N;
-            const double ssm = *reinterpret_cast<volatile double*>(a.sums + 1) / N;
-            a.out3[0] = (float)(a.a0 + a.a_l1 * l1m + a.a_ssim * ssm);
-            a.out3[1] = (float)l1m;
-            a.out3[2] = (float)ssm;
-        }
-    }
+    finish_sums(a, l1_sum, ssim_sum, s_part, (double)a.C * (double)plane);
 }
 
 __global__ void __launch_bounds__(kLossThreads) loss_backward_kernel(const LossArgs a) {
@@ -227,6 +262,13 @@ void fill_window(float* w) {
     for (int x = 0; x < kWin; ++x) w[x] = g[x] / sum;
 }
 
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+unsigned l1_grid(int C, int H, int W) {
+    const long long n4 = ((long long)C * H * W) >> 2;
+    return (unsigned)std::max(1ll, std::min((n4 + kLossThreads - 1) / kLossThreads, 148ll * 8));
+}
+
 dim3 loss_grid(int C, int H, int W) { return dim3((W + kTile - 1) / kTile, (H + kTile - 1) / kTile, C); }
 
 }  // namespace
@@ -246,7 +288,13 @@ int launch_loss_forward(int C, int H, int W, const float* image, const float* gt
     a.a0 = a0; a.a_l1 = a_l1; a.a_ssim = a_ssim;
     fill_window(a.w);
     if (cudaMemsetAsync(workspace, 0, kLossHeaderBytes, s) != cudaSuccess) return GSR_ERR_CUDA;
-    loss_forward_kernel<<<loss_grid(C, H, W), kLossThreads, 0, s>>>(a);
+    if (a_ssim == 0.0) {
+        a.maps = nullptr;
+        a.vec4 = aligned16(image) && aligned16(gt);
+        l1_forward_kernel<<<l1_grid(C, H, W), kLossThreads, 0, s>>>(a);
+    } else {
+        loss_forward_kernel<<<loss_grid(C, H, W), kLossThreads, 0, s>>>(a);
+    }
     GSR_AFTER_LAUNCH(s, 0);
     return GSR_OK;
 }
@@ -263,7 +311,12 @@ int launch_loss_backward(int C, int H, int W, const float* image, const float* g
     a.upstream = upstream;
     a.dL_dx = dL_dimage;
     fill_window(a.w);
-    loss_backward_kernel<<<loss_grid(C, H, W), kLossThreads, 0, s>>>(a);
+    if (a_ssim == 0.0) {
+        a.vec4 = aligned16(image) && aligned16(gt) && aligned16(dL_dimage);
+        l1_backward_kernel<<<l1_grid(C, H, W), kLossThreads, 0, s>>>(a);   // never touches the maps
+    } else {
+        loss_backward_kernel<<<loss_grid(C, H, W), kLossThreads, 0, s>>>(a);
+    }
     GSR_AFTER_LAUNCH(s, 0);
     return GSR_OK;
 }

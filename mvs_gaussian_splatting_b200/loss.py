@@ -52,15 +52,16 @@ class _PhotometricLoss(torch.autograd.Function):
         x = image.detach().to(torch.float32).contiguous()
         y = gt.detach().to(torch.float32).contiguous()
         need_grad = bool(ctx.needs_input_grad[0])
+        save = int(need_grad and float(a_ssim) != 0.0)   # the L1-only path keeps no per-pixel maps
         L = _native.lib()
         nbytes = ctypes.c_size_t()
-        _native.check(L.gsr_loss_workspace_bytes(C, H, W, int(need_grad), ctypes.byref(nbytes)),
+        _native.check(L.gsr_loss_workspace_bytes(C, H, W, save, ctypes.byref(nbytes)),
                       "gsr_loss_workspace_bytes")
         ws = torch.empty(nbytes.value, dtype=torch.uint8, device=x.device)
         out3 = torch.empty(3, dtype=torch.float32, device=x.device)
         with torch.cuda.device(x.device):
             _native.check(L.gsr_loss_forward(C, H, W, _ptr(x), _ptr(y), float(a0), float(a_l1), float(a_ssim),
-                                             _ptr(ws), int(need_grad), _ptr(out3), _stream(x.device)),
+                                             _ptr(ws), save, _ptr(out3), _stream(x.device)),
                           "gsr_loss_forward")
         ctx.save_for_backward(x, y, ws)
         ctx.dims, ctx.coef, ctx.in_dtype = (C, H, W), (float(a_l1), float(a_ssim)), image.dtype

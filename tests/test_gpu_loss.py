@@ -114,3 +114,31 @@ def test_full_hd_against_the_torch_formulation(cuda):
     rel = ((a.grad.double() - b.grad).abs().sum() / b.grad.abs().sum()).item()
     assert rel <= TOL, rel
     assert (a.grad.double() - b.grad).abs().max().item() <= TOL * b.grad.abs().max().item()
+
+
+def test_l1_only_path(cuda, native):
+    """a_ssim == 0 takes the streaming L1 kernels: same value and gradient as torch, odd sizes and an unaligned view."""
+    from mvs_gaussian_splatting_b200 import loss as L
+    gen = torch.Generator(device="cpu").manual_seed(4)
+    for shape in ((3, 1080, 1920), (3, 37, 53), (1, 1, 1), (2, 5, 7)):
+        y = torch.rand(*shape, generator=gen).to(cuda)
+        x = (y + 0.1 * torch.randn(*shape, generator=gen).to(cuda)).clamp(0, 1)
+        x[..., ::3] = y[..., ::3]
+        a = x.clone().requires_grad_(True)
+        n0 = native.lib().gsr_launch_count()
+        la = L.l1_loss(a, y)
+        (2.0 * la).backward()
+        assert native.lib().gsr_launch_count() - n0 == 2
+        b = x.clone().double().requires_grad_(True)
+        lb = (b - y.double()).abs().mean()
+        (2.0 * lb).backward()
+        assert abs(la.item() - lb.item()) <= 2e-6 * abs(lb.item()) + 1e-9
+        np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.float().cpu().numpy(), rtol=1e-6, atol=0)
+    # a view whose storage is not 16-byte aligned takes the scalar loop
+    base = torch.rand(3 * 9 * 11 + 1, generator=gen).to(cuda)
+    xv, yv = base[1:].view(3, 9, 11), torch.rand(3, 9, 11, generator=gen).to(cuda)
+    assert xv.data_ptr() % 16 != 0
+    a = xv.requires_grad_(True)
+    L.l1_loss(a, yv).backward()
+    want = torch.sign(xv.detach() - yv) / xv.numel()
+    np.testing.assert_allclose(a.grad.cpu().numpy(), want.cpu().numpy(), rtol=1e-6)
