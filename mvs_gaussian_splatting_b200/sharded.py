@@ -136,13 +136,22 @@ class ShardedViewRasterizer:
         self.geom_bytes, _, self.image_bytes = _native.workspace_bytes(P, width, height, 0)
         if exchange == "peer":
             import torch.distributed._symmetric_memory as symm_mem
+            # TWO workspaces, used on alternate steps: the rows a peer stores into my workspace for step k+1 must
+            # not land while any rank still reads step k's.  With one buffer that takes a barrier at the top of
+            # every step; with two, the buffer written in step k+1 was last read in step k-1, and every rank has
+            # passed step k's barriers — which follow its step k-1 reads in stream order — before anyone stores.
             self.radii_off = (self.geom_bytes + 255) // 256 * 256
-            nbytes = self.radii_off + 4 * max(P, 1)
-            self.symm = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+            self.half = (self.radii_off + 4 * max(P, 1) + 255) // 256 * 256
+            self.symm = symm_mem.empty(2 * self.half, dtype=torch.uint8, device=dev)
             self.hdl = symm_mem.rendezvous(self.symm, group if group is not None else dist.group.WORLD)
             self.peer_base = [int(x) for x in self.hdl.buffer_ptrs]
-            self.geom_ws = self.symm[:self.geom_bytes]
-            self.radii_ws = self.symm[self.radii_off:self.radii_off + 4 * P].view(torch.int32)
+            self._bufs = []
+            for b in (0, self.half):
+                ws = self.symm[b:b + self.geom_bytes]
+                self._bufs.append((ws, self.symm[b + self.radii_off:b + self.radii_off + 4 * P].view(torch.int32),
+                                   _ws_arrays(ws, self.L_full, P)))
+            self.parity = 1
+            self.geom_ws, self.radii_ws, self.full = self._bufs[self.parity]
         else:
             self.stride = self.plan.slot_stride(self.rank)
             self.P_send = self.world * self.stride
@@ -152,7 +161,7 @@ class ShardedViewRasterizer:
             self.send = _ws_arrays(self.send_ws, _native.workspace_layout(self.P_send, width, height, 0), self.P_send)
             self.geom_ws = torch.empty(self.geom_bytes, dtype=torch.uint8, device=dev)
             self.radii_ws = torch.empty(P, dtype=torch.int32, device=dev)
-        self.full = _ws_arrays(self.geom_ws, self.L_full, P)
+            self.full = _ws_arrays(self.geom_ws, self.L_full, P)
         # parameter gradients of the slice (summed over views) and per-view dL/dmeans2D
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         Ps = max(self.Ps, 1)
@@ -184,7 +193,7 @@ class ShardedViewRasterizer:
     def _target(self, v: int):
         """(geom_ws pointer, rows in it, first row, radii pointer) a slot call for view v addresses."""
         if self.exchange == "peer":
-            base = self.peer_base[v]
+            base = self.peer_base[v] + self.parity * self.half
             return (ctypes.c_void_p(base), self.P, self.start,
                     ctypes.c_void_p(base + self.radii_off + 4 * self.start))
         return (_ptr(self.send_ws), self.P_send, v * self.stride,
@@ -216,8 +225,10 @@ class ShardedViewRasterizer:
             ctx.geom_ws = self.geom_ws
             ctx.image_ws = torch.empty(self.image_bytes, dtype=torch.uint8, device=dev)
             color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
-            if peer:
-                self.hdl.barrier(channel=0)   # every rank is done reading the previous step's workspaces
+            if peer:   # no barrier here: this step's rows go to the workspace last read two steps ago (see __init__)
+                self.parity ^= 1
+                self.geom_ws, self.radii_ws, self.full = self._bufs[self.parity]
+                ctx.geom_ws = self.geom_ws
             order = self._view_order()
             step = _native.MAX_VIEWS if peer else 1   # staged (nccl) slots sit at different rows: one view per call
             for c0 in range(0, N, step):
