@@ -167,8 +167,14 @@ __global__ void __launch_bounds__(kBlk) scan_sorted_tiles_kernel(int P, const ui
 }
 
 // =========================== stable LSD radix sort, one kernel per pass ====================
-constexpr int kSortItems = 16;                  // per thread
-constexpr int kSortChunk = kBlk * kSortItems;   // 4096 items per ticket
+#ifndef GSR_SORT_ITEMS
+#define GSR_SORT_ITEMS 24   // A/B on B200 (config 3): 8/12/16/20/24/32 items -> 24 at 2 CTAs/SM is fastest and spill-free
+#endif
+#ifndef GSR_SORT_MINBLOCKS
+#define GSR_SORT_MINBLOCKS 2
+#endif
+constexpr int kSortItems = GSR_SORT_ITEMS;      // per thread
+constexpr int kSortChunk = kBlk * kSortItems;   // 6144 items per ticket
 constexpr int kSortWarps = kBlk / 32;
 constexpr int kSortWarpSpan = 32 * kSortItems;  // consecutive items owned by one warp
 constexpr int kMaxBins = 256;
@@ -217,12 +223,11 @@ __global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ 
 // One pass.  kIdentityVal: the payload of item i is i itself (first pass of the depth sort), so no
 // payload array is read.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.
 template <typename K, bool kIdentityVal, int kBits>
-__global__ void __launch_bounds__(kBlk, 3) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+__global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                           K* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                           const uint32_t* __restrict__ n_ptr, uint32_t n_host, uint32_t cap,
                                                           int shift, const uint32_t* __restrict__ hist,
                                                           uint32_t* status, uint32_t* ticket) {
-    constexpr int bits = kBits;
     extern __shared__ __align__(16) unsigned char s_raw[];
     K* s_keys = reinterpret_cast<K*>(s_raw);                                          // [kSortChunk]
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw + sizeof(K) * kSortChunk);   // [kSortChunk]
@@ -481,6 +486,8 @@ void launch_tile_pass(int bits, unsigned grid, size_t smem, cudaStream_t s, cons
 cudaError_t set_tile_pass_attributes() {
     cudaError_t e = cudaSuccess;
     const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, true, 8>, attr, (int)radix_pass_smem<uint32_t>(8));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, false, 8>, attr, (int)radix_pass_smem<uint32_t>(8));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 4>, attr, (int)radix_pass_smem<uint64_t>(4));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 5>, attr, (int)radix_pass_smem<uint64_t>(5));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 6>, attr, (int)radix_pass_smem<uint64_t>(6));

@@ -23,8 +23,9 @@ Two transports.  exchange="peer" (default): every rank's geometry workspace live
 memory (torch.distributed._symmetric_memory: peer-mapped over NVLink); the preprocess kernel of rank
 r writes view v's rows STRAIGHT INTO rank v's workspace (remote stores, no staging, no copy kernel)
 and preprocess_backward reads view v's accumulators straight from rank v's workspace (remote loads),
-so each exchange is fused into the kernel that produces / consumes the data; three device-side
-barriers per step order the phases.  exchange="nccl": staged rows + one batched group of NCCL
+so each exchange is fused into the kernel that produces / consumes the data; two device-side
+barriers per step order the phases (the workspace is double-buffered across steps, which removes the
+third: "peers are done reading the previous step").  exchange="nccl": staged rows + one batched group of NCCL
 point-to-point operations per exchange (measured 0.43 + 0.27 ms at 2 GPUs against 0.17 ms of peer
 copies, hence not the default).
 
