@@ -1,9 +1,11 @@
 // gsr_blend.cu — per-16x16-tile alpha compositing, forward and backward, for sm_100a
 // (the reference's two `renderCUDA` kernels).
 //
-// One CTA per tile, 256 threads, one pixel per thread; warp w owns an 8x4 pixel block so that the
-// lanes of a warp are spatially compact.  Splats are staged through shared memory in batches of
-// 256 list entries.  B200-first differences from the reference algorithm, none of which changes
+// One CTA per tile.  Forward: 256 threads, one pixel per thread, warp w owns an 8x4 pixel block so that the
+// lanes of a warp are spatially compact; splats are staged through shared memory in batches of 256 list
+// entries.  Backward (blend_backward2_kernel, the default): 128 threads, TWO pixels per lane, warp w owns an
+// 8x8 block, batches of 128 — the per-(warp, splat) reduction is paid once per 64 pixels (0.750 -> 0.639 ms);
+// the one-pixel backward (blend_backward_kernel) is kept selectable with GSR_BLEND_BWD=1 for A/B runs.  B200-first differences from the reference algorithm, none of which changes
 // a result:
 //   * two-level exact culling.  Staging applies a CONSERVATIVE ellipse-vs-rectangle test (maximum of
 //     the conic's exponent over the rectangle against -log2(255*opacity)) for the TILE and compacts
@@ -23,6 +25,8 @@
 //     butterfly — then flushed as 128-bit vector reductions (RED.E.ADD.F32x4) to L2: three per
 //     (8x4 block, splat) — versus 9 scalar global atomics per contributing (pixel, splat) pair in
 //     the reference.  No CTA-wide barrier inside the walk.
+#include <cstdlib>
+
 #include "gsr_internal.cuh"
 
 namespace gsr {
@@ -96,6 +100,7 @@ __device__ __forceinline__ TileCtx tile_ctx(int gx, int W, int H) {
 }
 
 // Ordered CTA-wide compaction slot for `keep`; returns slot (valid if keep) and the total.
+template <int kWarps = kBlendWarps>
 __device__ __forceinline__ int compact_slot(bool keep, int* s_wcount, int& total) {
     const unsigned bal = __ballot_sync(0xffffffffu, keep);
     const int w = threadIdx.x >> 5;
@@ -104,7 +109,7 @@ __device__ __forceinline__ int compact_slot(bool keep, int* s_wcount, int& total
     int off = 0;
     total = 0;
 #pragma unroll
-    for (int i = 0; i < kBlendWarps; ++i) {
+    for (int i = 0; i < kWarps; ++i) {
         const int c = s_wcount[i];
         off += (i < w) ? c : 0;
         total += c;
@@ -403,11 +408,191 @@ __global__ void __launch_bounds__(kBlendThreads, 4) blend_backward_kernel(
     if (nh) flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
 }
 
+// Two pixels per lane: 128 threads per tile, warp w owns an 8x8 pixel block, lane l the pixels
+// (l & 7, l >> 3) and (l & 7, (l >> 3) + 4) of it.  Same decisions and the same per-pair arithmetic as
+// blend_backward_kernel; what changes is that the per-(warp, splat) costs — the walk, the three shared
+// loads of the staged entry, and above all the transposed shared-memory reduction (9 stores + the row
+// sums, the pipe that bounds the one-pixel kernel) — are paid once per 64 pixels instead of once per 32:
+// each lane adds its two pixels' nine terms in registers before parking them.
+constexpr int kB2Threads = 128;
+constexpr int kB2Warps = 4;
+
+#ifndef GSR_B2_MINBLOCKS
+#define GSR_B2_MINBLOCKS 5   // A/B on B200: 4 / 5 / 6 / 7 / 8 CTAs per SM -> 0.718 / 0.639 / 0.654 / 0.670 / 0.677 ms
+#endif
+__global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_kernel(
+    int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+    const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
+    const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
+    const float* __restrict__ dL_dpix, float* __restrict__ grad_accum) {
+    __shared__ float4 s_e[3 * kB2Threads];
+    __shared__ __align__(16) float s_red[kB2Warps][kRedSplats * 9][32];
+    __shared__ __align__(16) float s_tot[kB2Warps][kRedSplats][12];
+    __shared__ uint32_t s_gid[kB2Warps][kRedSplats + 1];
+    __shared__ int s_wcount[kB2Warps];
+    __shared__ uint32_t s_wmax[kB2Warps];
+
+    const int tile = blockIdx.x;
+    const int ty = tile / gx, tx = tile - ty * gx;
+    const unsigned lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    const int bx = tx * kTile + (warp & 1) * 8, by = ty * kTile + (warp >> 1) * 8;
+    const int px = bx + (int)(lane & 7), py0 = by + (int)(lane >> 3);
+    Rect tile_rect, warp_rect;
+    tile_rect.x0 = (float)(tx * kTile);
+    tile_rect.y0 = (float)(ty * kTile);
+    tile_rect.x1 = (float)min(tx * kTile + kTile - 1, W - 1);
+    tile_rect.y1 = (float)min(ty * kTile + kTile - 1, H - 1);
+    warp_rect.x0 = (float)bx;
+    warp_rect.y0 = (float)by;
+    warp_rect.x1 = (float)min(bx + 7, W - 1);
+    warp_rect.y1 = (float)min(by + 7, H - 1);
+    const uint2 range = ranges[tile];
+    const float fx = (float)px;
+    if (lane < kRedSplats * 3) s_tot[warp][lane / 3][9 + lane % 3] = 0.0f;
+    float* const my_red = &s_red[warp][0][lane];
+    int nh = 0;
+
+    float fy[2], Tfin[2], g0[2], g1[2], g2[2], bgdot[2];
+    uint32_t last[2];
+    const size_t plane = (size_t)W * H;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int py = py0 + 4 * k;
+        fy[k] = (float)py;
+        Tfin[k] = 0.f; g0[k] = 0.f; g1[k] = 0.f; g2[k] = 0.f; last[k] = 0;
+        if (px < W && py < H) {
+            const size_t pix = (size_t)py * W + px;
+            Tfin[k] = final_T[pix];
+            last[k] = n_contrib[pix];
+            g0[k] = __ldg(dL_dpix + pix);
+            g1[k] = __ldg(dL_dpix + plane + pix);
+            g2[k] = __ldg(dL_dpix + 2 * plane + pix);
+        }
+        bgdot[k] = __ldg(bg) * g0[k] + __ldg(bg + 1) * g1[k] + __ldg(bg + 2) * g2[k];
+    }
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(last[0], last[1]));
+    if (lane == 0) s_wmax[warp] = wmax;
+    __syncthreads();
+    uint32_t m = 0;
+#pragma unroll
+    for (int i = 0; i < kB2Warps; ++i) m = max(m, s_wmax[i]);
+
+    float T[2] = {Tfin[0], Tfin[1]}, last_alpha[2] = {0.f, 0.f};
+    float lc0[2] = {0.f, 0.f}, lc1[2] = {0.f, 0.f}, lc2[2] = {0.f, 0.f};
+    float bh0[2] = {0.f, 0.f}, bh1[2] = {0.f, 0.f}, bh2[2] = {0.f, 0.f};
+
+    for (int hi = (int)m; hi > 0; hi -= kB2Threads) {
+        __syncthreads();
+        const int p = hi - 1 - (int)threadIdx.x;
+        bool keep = false;
+        uint32_t gid = 0;
+        float2 mm = make_float2(0.f, 0.f);
+        float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
+        if (p >= 0) {
+            gid = __ldg(point_list + range.x + p);
+            mm = __ldg(means2D + gid);
+            const float4 co = __ldg(conic_opacity + gid);
+            op = co.w;
+            keep = stage_test(mm, co, tile_rect, a2, b2, c2, tau2);
+        }
+        int total;
+        const int slot = compact_slot<kB2Warps>(keep, s_wcount, total);
+        if (keep) {
+            const float4 col = __ldg(rgb + gid);
+            s_e[3 * slot] = make_float4(mm.x, mm.y, a2, b2);
+            s_e[3 * slot + 1] = make_float4(c2, op, tau2, __int_as_float(p + 1));
+            s_e[3 * slot + 2] = make_float4(col.x, col.y, col.z, __uint_as_float(gid));
+        }
+        __syncthreads();
+        if (wmax == 0) continue;
+
+        for (int cb = 0; cb < total; cb += 32) {
+            const int jt = cb + (int)lane;
+            bool hit = false;
+            if (jt < total) {
+                const float4 ta = s_e[3 * jt];
+                const float4 tb = s_e[3 * jt + 1];
+                hit = ((uint32_t)__float_as_int(tb.w) <= wmax) &&
+                      splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, warp_rect);
+            }
+            unsigned mask = __ballot_sync(0xffffffffu, hit);
+            while (mask) {
+                const int j = cb + __ffs(mask) - 1;
+                mask &= mask - 1;
+                const float4 g = s_e[3 * j];
+                const float4 cc = s_e[3 * j + 1];
+                const float dx = g.x - fx;
+                const float lin = g.z * dx;  // a2 * dx
+                float dy[2], G[2], alpha[2], pw[2];
+                bool ok[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    dy[k] = g.y - fy[k];
+                    pw[k] = fmaf(cc.x * dy[k], dy[k], fmaf(g.w, dy[k], lin) * dx);
+                    G[k] = ex2_approx(pw[k]);
+                    alpha[k] = fminf(0.99f, cc.y * G[k]);
+                    ok[k] = ((uint32_t)__float_as_int(cc.w) <= last[k]) && !(pw[k] > 0.0f) && !(alpha[k] < kAlphaMin);
+                }
+                if (!__any_sync(0xffffffffu, ok[0] || ok[1])) continue;
+                const float4 col = s_e[3 * j + 2];
+                float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, t4 = 0.f, t5 = 0.f, t6 = 0.f, t7 = 0.f, t8 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    if (ok[k]) {
+                        const float ra = rcp_approx(1.0f - alpha[k]);
+                        T[k] *= ra;
+                        const float wgt = alpha[k] * T[k];
+                        bh0[k] = last_alpha[k] * lc0[k] + (1.0f - last_alpha[k]) * bh0[k];
+                        bh1[k] = last_alpha[k] * lc1[k] + (1.0f - last_alpha[k]) * bh1[k];
+                        bh2[k] = last_alpha[k] * lc2[k] + (1.0f - last_alpha[k]) * bh2[k];
+                        lc0[k] = col.x; lc1[k] = col.y; lc2[k] = col.z;
+                        float dL_dalpha = (col.x - bh0[k]) * g0[k] + (col.y - bh1[k]) * g1[k] + (col.z - bh2[k]) * g2[k];
+                        dL_dalpha *= T[k];
+                        last_alpha[k] = alpha[k];
+                        dL_dalpha -= Tfin[k] * ra * bgdot[k];
+                        const float gdl = G[k] * dL_dalpha;
+                        const float h = cc.y * gdl;
+                        const float hx = h * dx, hy = h * dy[k];
+                        t0 += hx;
+                        t1 += hy;
+                        t2 = fmaf(hx, dx, t2);
+                        t3 = fmaf(hx, dy[k], t3);
+                        t4 = fmaf(hy, dy[k], t4);
+                        t5 += gdl;
+                        t6 = fmaf(wgt, g0[k], t6);
+                        t7 = fmaf(wgt, g1[k], t7);
+                        t8 = fmaf(wgt, g2[k], t8);
+                    }
+                }
+                float* dst = my_red + nh * (9 * 32);
+                dst[0 * 32] = t0;
+                dst[1 * 32] = t1;
+                dst[2 * 32] = t2;
+                dst[3 * 32] = t3;
+                dst[4 * 32] = t4;
+                dst[5 * 32] = t5;
+                dst[6 * 32] = t6;
+                dst[7 * 32] = t7;
+                dst[8 * 32] = t8;
+                if (lane == 0) s_gid[warp][nh] = __float_as_uint(col.w);
+                if (++nh == kRedSplats) {
+                    flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
+                    nh = 0;
+                }
+            }
+        }
+    }
+    if (nh) flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
+}
+
 }  // namespace
 
 int launch_blend_forward(const Grid& g, const float* bg, GeomView gv, BinView bv, ImageView iv,
                          float* out_color, cudaStream_t s, int debug) {
     StageScope scope(kStageBlendFwd, s);
+    // (a two-pixels-per-lane forward was measured too: 0.319 ms against 0.312 ms — the forward has no reduction to
+    // amortise and the coarser 8x8 block test lets more pairs through — so the forward keeps one pixel per lane)
     blend_forward_kernel<false><<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list,
                                                                   gv.means2D, gv.conic_opacity, gv.rgb, bg, out_color,
                                                                   iv.final_T, iv.n_contrib, nullptr);
@@ -429,9 +614,15 @@ int launch_blend_backward(int P, const Grid& g, const float* bg, GeomView gv, Bi
                           const float* dL_dpix, cudaStream_t s, int debug) {
     StageScope scope(kStageBlendBwd, s);
     GSR_CUDA(cudaMemsetAsync(gv.grad_accum, 0, sizeof(float) * 12 * (size_t)P, s));
-    blend_backward_kernel<<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
-                                                            gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
-                                                            dL_dpix, gv.grad_accum);
+    static const int variant = [] { const char* e = getenv("GSR_BLEND_BWD"); return e ? atoi(e) : 2; }();
+    if (variant == 2)
+        blend_backward2_kernel<<<g.tiles, kB2Threads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
+                                                              gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
+                                                              dL_dpix, gv.grad_accum);
+    else
+        blend_backward_kernel<<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
+                                                                gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
+                                                                dL_dpix, gv.grad_accum);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;
 }
