@@ -66,7 +66,11 @@ def grad_report(a, b64, o32, rel=REL_TOL):
       (1) the tensor-level relative error  sum|a-b| / sum|b|  <= rel, and
       (2) element-wise |a-b| <= rel*max(|b|, mean|b|) for all but a fraction of elements no larger
           than twice the fraction on which the fp32 oracle itself exceeds it (+1e-3), with the worst
-          element no worse than 5x the fp32 oracle's own worst element (+rel).
+          element no worse than 5x the fp32 oracle's own worst element (+10 rel).  The additive slack is
+          there because the fp32 oracle's worst element is itself a draw: its backward runs on all host
+          threads, so its summation order — and with it that figure — changes from run to run (measured on
+          the opaque-wall stress case, tools/flaky_probe.py: 1.4e-4 ... 1.5e-3 for the oracle against a
+          steady 1.0e-3 for the CUDA path, old and new blend-backward kernels alike).
     Returns (ok, dict of the measured figures)."""
     a, b, o = (np.asarray(x, np.float64) for x in (a, b64, o32))
     nz = np.abs(b[b != 0])
@@ -79,7 +83,7 @@ def grad_report(a, b64, o32, rel=REL_TOL):
                frac_fp32_oracle=float((eo > rel).mean()) if eo.size else 0.0,
                worst=float(ea.max()) if ea.size else 0.0, worst_fp32_oracle=float(eo.max()) if eo.size else 0.0)
     ok = (rep["rel_l1"] <= rel and rep["frac"] <= 2 * rep["frac_fp32_oracle"] + 1e-3
-          and rep["worst"] <= 5 * rep["worst_fp32_oracle"] + rel)
+          and rep["worst"] <= 5 * rep["worst_fp32_oracle"] + 10 * rel)
     return ok, rep
 
 
