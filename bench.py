@@ -525,17 +525,26 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
                 p.grad = None                               # train.py:142 zero_grad(set_to_none=True)
         return val
 
-    for _ in range(3):
+    for _ in range(5):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    n = max(5, min(args.steps, 20))
+    n = max(30, args.steps)   # wall-clock: enough steps that one host hiccup does not move the figure
+    prof = None
+    if os.environ.get("GSR_E2E_PROFILE"):   # where the host time of an e2e step goes (stderr; perturbs the figure)
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
     t0 = time.perf_counter()
     for _ in range(n):
         step()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    if prof is not None:
+        import pstats
+        prof.disable()
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(14)
     if world > 1:
         tt = torch.tensor([dt], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)

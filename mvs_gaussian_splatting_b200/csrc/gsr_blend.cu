@@ -4,7 +4,7 @@
 // One CTA per tile.  Forward: 256 threads, one pixel per thread, warp w owns an 8x4 pixel block so that the
 // lanes of a warp are spatially compact; splats are staged through shared memory in batches of 256 list
 // entries.  Backward (blend_backward2_kernel, the default): 128 threads, TWO pixels per lane, warp w owns an
-// 8x8 block, batches of 128 — the per-(warp, splat) reduction is paid once per 64 pixels (0.750 -> 0.639 ms);
+// 8x8 block, batches of 128 — the per-(warp, splat) reduction is paid once per 64 pixels (0.750 -> 0.604 ms);
 // the one-pixel backward (blend_backward_kernel) is kept selectable with GSR_BLEND_BWD=1 for A/B runs.  B200-first differences from the reference algorithm, none of which changes
 // a result:
 //   * two-level exact culling.  Staging applies a CONSERVATIVE ellipse-vs-rectangle test (maximum of
@@ -418,7 +418,7 @@ constexpr int kB2Threads = 128;
 constexpr int kB2Warps = 4;
 
 #ifndef GSR_B2_MINBLOCKS
-#define GSR_B2_MINBLOCKS 5   // A/B on B200: 4 / 5 / 6 / 7 / 8 CTAs per SM -> 0.718 / 0.639 / 0.654 / 0.670 / 0.677 ms
+#define GSR_B2_MINBLOCKS 6   // 80 registers, no spills once the per-pixel state is packed: 0.604 ms (5 CTAs/SM: 0.643 ms)
 #endif
 __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_kernel(
     int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
@@ -453,24 +453,28 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
     float* const my_red = &s_red[warp][0][lane];
     int nh = 0;
 
-    float fy[2], Tfin[2], g0[2], g1[2], g2[2], bgdot[2];
+    // per-pixel state, packed for registers: row py0 + 4k is recomputed, final_T only survives as the product
+    // final_T * (bg . dL/dpixel), and the running "colour behind" bh is advanced right after a splat is used
+    // (alpha * colour + (1 - alpha) * bh — the expression the reference evaluates at the start of the NEXT
+    // contributing splat from the saved alpha and colour) so neither has to be kept.
+    float Tb[2], T[2], g0[2], g1[2], g2[2];
     uint32_t last[2];
     const size_t plane = (size_t)W * H;
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
         const int py = py0 + 4 * k;
-        fy[k] = (float)py;
-        Tfin[k] = 0.f; g0[k] = 0.f; g1[k] = 0.f; g2[k] = 0.f; last[k] = 0;
+        T[k] = 0.f; g0[k] = 0.f; g1[k] = 0.f; g2[k] = 0.f; last[k] = 0;
         if (px < W && py < H) {
             const size_t pix = (size_t)py * W + px;
-            Tfin[k] = final_T[pix];
+            T[k] = final_T[pix];
             last[k] = n_contrib[pix];
             g0[k] = __ldg(dL_dpix + pix);
             g1[k] = __ldg(dL_dpix + plane + pix);
             g2[k] = __ldg(dL_dpix + 2 * plane + pix);
         }
-        bgdot[k] = __ldg(bg) * g0[k] + __ldg(bg + 1) * g1[k] + __ldg(bg + 2) * g2[k];
+        Tb[k] = T[k] * (__ldg(bg) * g0[k] + __ldg(bg + 1) * g1[k] + __ldg(bg + 2) * g2[k]);
     }
+    const float fy0 = (float)py0;
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(last[0], last[1]));
     if (lane == 0) s_wmax[warp] = wmax;
     __syncthreads();
@@ -478,8 +482,6 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
 #pragma unroll
     for (int i = 0; i < kB2Warps; ++i) m = max(m, s_wmax[i]);
 
-    float T[2] = {Tfin[0], Tfin[1]}, last_alpha[2] = {0.f, 0.f};
-    float lc0[2] = {0.f, 0.f}, lc1[2] = {0.f, 0.f}, lc2[2] = {0.f, 0.f};
     float bh0[2] = {0.f, 0.f}, bh1[2] = {0.f, 0.f}, bh2[2] = {0.f, 0.f};
 
     for (int hi = (int)m; hi > 0; hi -= kB2Threads) {
@@ -528,7 +530,7 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
                 bool ok[2];
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
-                    dy[k] = g.y - fy[k];
+                    dy[k] = g.y - (fy0 + (float)(4 * k));
                     pw[k] = fmaf(cc.x * dy[k], dy[k], fmaf(g.w, dy[k], lin) * dx);
                     G[k] = ex2_approx(pw[k]);
                     alpha[k] = fminf(0.99f, cc.y * G[k]);
@@ -543,14 +545,12 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
                         const float ra = rcp_approx(1.0f - alpha[k]);
                         T[k] *= ra;
                         const float wgt = alpha[k] * T[k];
-                        bh0[k] = last_alpha[k] * lc0[k] + (1.0f - last_alpha[k]) * bh0[k];
-                        bh1[k] = last_alpha[k] * lc1[k] + (1.0f - last_alpha[k]) * bh1[k];
-                        bh2[k] = last_alpha[k] * lc2[k] + (1.0f - last_alpha[k]) * bh2[k];
-                        lc0[k] = col.x; lc1[k] = col.y; lc2[k] = col.z;
                         float dL_dalpha = (col.x - bh0[k]) * g0[k] + (col.y - bh1[k]) * g1[k] + (col.z - bh2[k]) * g2[k];
                         dL_dalpha *= T[k];
-                        last_alpha[k] = alpha[k];
-                        dL_dalpha -= Tfin[k] * ra * bgdot[k];
+                        dL_dalpha -= Tb[k] * ra;
+                        bh0[k] = alpha[k] * col.x + (1.0f - alpha[k]) * bh0[k];
+                        bh1[k] = alpha[k] * col.y + (1.0f - alpha[k]) * bh1[k];
+                        bh2[k] = alpha[k] * col.z + (1.0f - alpha[k]) * bh2[k];
                         const float gdl = G[k] * dL_dalpha;
                         const float h = cc.y * gdl;
                         const float hx = h * dx, hy = h * dy[k];
