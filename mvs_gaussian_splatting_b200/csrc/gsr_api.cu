@@ -21,6 +21,17 @@ int cuda_fail(cudaError_t e) {
     return GSR_ERR_CUDA;
 }
 
+bool first_use_on_current_device(unsigned long long* mask) {
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;  // unknown: set the attributes again
+    std::lock_guard<std::mutex> lock(mu);
+    const unsigned long long bit = 1ull << dev;
+    if (*mask & bit) return false;
+    *mask |= bit;
+    return true;
+}
+
 // ---- per-stage timing: event pairs appended while enabled, summed by gsr_stage_timing_read ----
 static std::atomic<bool> g_timing{false};
 static std::mutex g_timing_mu;
@@ -399,6 +410,7 @@ int gsr_activate(int P, int M, const float* features_dc, const float* features_r
 // ---- Gaussian-sharded multi-view entries ---------------------------------------------------
 static int check_slots(int P_ws, int slot_offset, int Ps) {
     if (P_ws < 0 || Ps < 0 || slot_offset < 0 || (int64_t)slot_offset + Ps > P_ws) return GSR_ERR_INVALID_ARGUMENT;
+    if (Ps == 0) return GSR_OK;  // an empty trailing slice may start at an unaligned P: nothing is addressed
     if (slot_offset & 3) return GSR_ERR_INVALID_ARGUMENT;  // keeps the 16-byte row alignment of every array
     return GSR_OK;
 }

@@ -529,13 +529,12 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
                                      float* dL_dmeans3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscales,
                                      float* dL_drots, int accumulate, cudaStream_t s, int debug, const RawMode& rm) {
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
-    static bool attr_set = false;  // idempotent; racing threads set the same value
-    if (!attr_set) {
+    static unsigned long long attr_devices = 0;
+    if (first_use_on_current_device(&attr_devices)) {
         GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, false>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
         GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
-        attr_set = true;
     }
     BwdParams p;
     p.raw = rm.raw; p.sh_rest = rm.sh_rest; p.dL_dsh_rest = rm.dL_dsh_rest;

@@ -510,11 +510,8 @@ size_t tile_sort_ctl_entries(size_t cap) { return kCtlHeader + (size_t)kMaxPasse
 // Per-Gaussian stage after preprocess: depth-order sort of all P (key, index) pairs, then the prefix
 // sum of tiles_touched in that order (writes info->num_rendered).
 int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
-    static bool attr_set = false;  // idempotent; racing threads set the same value
-    if (!attr_set) {
-        GSR_CUDA(set_tile_pass_attributes());
-        attr_set = true;
-    }
+    static unsigned long long attr_devices = 0;
+    if (first_use_on_current_device(&attr_devices)) GSR_CUDA(set_tile_pass_attributes());
     const size_t nchunk = chunks_of((size_t)P);
     uint32_t* ctl = gv.sort_ctl;
     uint32_t* hist = ctl;

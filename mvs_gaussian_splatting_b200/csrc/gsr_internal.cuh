@@ -56,6 +56,11 @@ struct StageScope {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// True the first time it is called for `mask` on the CURRENT device (per-device bit set): function
+// attributes such as the dynamic shared-memory opt-in apply only to the device that is current when they
+// are set, and one process may render on several devices.  Racing threads set the same values twice at worst.
+bool first_use_on_current_device(unsigned long long* mask);
+
 struct Grid {
     int W, H, gx, gy, tiles;
 };

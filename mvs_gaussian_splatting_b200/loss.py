@@ -27,6 +27,19 @@ def _stream(device):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+def _as_target(image: torch.Tensor, gt) -> torch.Tensor:
+    """`gt` as the reference's torch expressions accept it: a tensor of the image's shape, a tensor that
+    broadcasts against it, or a Python scalar (train.py:105 calls `l1_loss(opacity[mask], 1)`); expanded
+    to the image's shape on its device."""
+    if not isinstance(gt, torch.Tensor):
+        gt = torch.as_tensor(gt, dtype=torch.float32, device=image.device)
+    elif gt.device != image.device:
+        raise ValueError("image and gt must be on the same device")
+    if gt.shape != image.shape:
+        gt = gt.to(torch.float32).expand(image.shape)   # raises if not broadcastable
+    return gt
+
+
 def _planes(image: torch.Tensor, gt: torch.Tensor):
     if image.device.type != "cuda":
         raise RuntimeError("the fused photometric loss has no CPU path: tensors must be on a CUDA device")
@@ -92,7 +105,14 @@ def l1_dssim_loss(image: torch.Tensor, gt: torch.Tensor, lambda_dssim: float = 0
 
 
 def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
-    """utils/loss_utils.py:17-18."""
+    """utils/loss_utils.py:17-18: mean |network_output - gt|.  `gt` may be a scalar or any tensor that
+    broadcasts against `network_output` (train.py:105); inputs with fewer than two dimensions are treated
+    as one row."""
+    gt = _as_target(network_output, gt)
+    if network_output.numel() == 0:
+        return torch.abs(network_output - gt).mean()   # nan, as torch gives for an empty selection
+    if network_output.dim() < 3:   # not an image (e.g. the [K,1] opacity rows of train.py:105): one long row
+        network_output, gt = network_output.reshape(1, -1), gt.reshape(1, -1)
     return photometric_terms(network_output, gt, 0.0, 1.0, 0.0)[0]
 
 

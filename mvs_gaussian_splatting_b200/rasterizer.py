@@ -191,7 +191,8 @@ def _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev
 
 def rasterize_forward(means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                       raster_settings: GaussianRasterizationSettings, capacity: Optional[int] = None):
-    """Forward through the C ABI.  Returns (color[3,H,W], radii[P] int32, RasterContext).
+    """Forward through the C ABI.  Returns (color[3,H,W], radii[P] int32, RasterContext, inputs) —
+    `inputs` is the tuple of dense tensors `rasterize_backward` takes as `ctx_inputs`.
 
     `capacity`: instance capacity of the binning workspace.  None = use the per-device hint from
     earlier calls and verify it against the device's count WITHOUT stalling the GPU (the count is
@@ -340,16 +341,17 @@ class _RasterizeGaussiansRaw(torch.autograd.Function):
                 raster_settings):
         color, radii, rctx, inputs = rasterize_forward_raw(means3D, features_dc, features_rest, opacity_raw,
                                                            scaling_raw, rotation_raw, raster_settings)
-        ctx.raster_settings, ctx.rctx, ctx.inputs = raster_settings, rctx, inputs
+        ctx.raster_settings, ctx.rctx = raster_settings, rctx
+        ctx.save_for_backward(*inputs)   # in-place edits before backward are detected; freed with the graph
         ctx.has_rest = features_rest is not None and features_rest.numel() > 0
         ctx.mark_non_differentiable(radii)
         return color, radii
 
     @staticmethod
     def backward(ctx, grad_out_color, _grad_radii):
+        # the workspaces live as long as the graph does, so backward(retain_graph=True) can run again
         d_means3D, d_means2D, d_dc, d_rest, d_op, d_sc, d_rot = rasterize_backward_raw(
-            ctx.rctx, ctx.inputs, ctx.raster_settings, grad_out_color)
-        ctx.rctx = ctx.inputs = None
+            ctx.rctx, ctx.saved_tensors, ctx.raster_settings, grad_out_color)
         return d_means3D, d_means2D, d_dc, (d_rest if ctx.has_rest else None), d_op, d_sc, d_rot, None
 
 
@@ -478,7 +480,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             color, radii, rctx, inputs = rasterize_forward(*args)
         ctx.raster_settings = rs
         ctx.rctx = rctx
-        ctx.inputs = inputs
+        ctx.save_for_backward(*inputs)   # in-place edits before backward are detected; freed with the graph
         ctx.mark_non_differentiable(radii)
         return color, radii
 
@@ -487,17 +489,18 @@ class _RasterizeGaussians(torch.autograd.Function):
         if ctx.empty:
             return (None,) * 9
         rs = ctx.raster_settings
+        inputs = ctx.saved_tensors   # raises autograd's own error after the graph was freed
+        # The workspaces (ctx.rctx) live exactly as long as the graph: a second backward under
+        # retain_graph=True recomputes from them, as the reference's saved byte tensors allow.
         if rs.debug:
             try:
-                grads = rasterize_backward(ctx.rctx, ctx.inputs, rs, grad_out_color)
+                grads = rasterize_backward(ctx.rctx, inputs, rs, grad_out_color)
             except Exception:
-                torch.save(_cpu_deep_copy_tuple(ctx.inputs + (grad_out_color,)), "snapshot_bw.dump")
+                torch.save(_cpu_deep_copy_tuple(tuple(inputs) + (grad_out_color,)), "snapshot_bw.dump")
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise
         else:
-            grads = rasterize_backward(ctx.rctx, ctx.inputs, rs, grad_out_color)
-        ctx.rctx = None  # release the workspaces
-        ctx.inputs = None
+            grads = rasterize_backward(ctx.rctx, inputs, rs, grad_out_color)
         return grads + (None,)
 
 

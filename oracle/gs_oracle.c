@@ -33,15 +33,84 @@
  *   i.e. the most likely numerics of a stock build of the third-party module on sm_100.
  *   Division, sqrt, ceil and float->int truncation are the IEEE / CUDA-saturating ones.
  *
- * The same source builds twice: binary32 (suffix _f32, the parity oracle) and binary64
- * (suffix _f64, -DORC_F64, used for finite-difference / autograd gradient checks).
+ * The same source builds three times: binary32 (suffix _f32, the parity oracle), binary64
+ * (suffix _f64, -DORC_F64, used for finite-difference / autograd gradient checks) and, compiled as
+ * C++ with -DORC_RE (suffix _re), binary64 values that carry a running rounding-error bound of the
+ * binary32 evaluation — the conditioning-aware scale of the gradient tests.
  */
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
 
-#ifdef ORC_F64
+#ifdef ORC_RE
+/* ---- third build (g++ -x c++ -DORC_RE): RUNNING ERROR ANALYSIS of the same source -----------------
+ * `real` carries (v, e): the binary64 value and a first-order bound, in units of the binary32 unit
+ * roundoff u = 2^-24, on the absolute error ANY binary32 evaluation of the same expression tree
+ * accumulates (Higham, Accuracy and Stability of Numerical Algorithms, §3.3): every operation
+ * propagates its operands' bounds through its partial derivatives and adds |result| for its own
+ * rounding.  Inputs are exact (e = 0).  Gradient tests use e as the conditioning-aware scale of each
+ * element: |cuda - oracle_f64| <= max(1e-4 |oracle|, K u e) for EVERY element (tests/helpers.py).
+ * Discrete decisions (skip / stop / clamp selection) follow v. */
+#ifndef __cplusplus
+#error "the ORC_RE build compiles this file as C++ (operator overloading); see oracle/Makefile"
+#endif
+struct real {
+    double v, e;
+    real() = default;
+    real(double x) : v(x), e((double)(float)x == x ? 0.0 : (x < 0 ? -x : x)) {}  /* constants round once */
+    real(double x, double err) : v(x), e(err) {}
+    explicit operator double() const { return v; }
+};
+static inline double re_abs(double x) { return x < 0 ? -x : x; }
+static inline real operator-(real a) { return real(-a.v, a.e); }
+static inline real operator+(real a, real b) { double v = a.v + b.v; return real(v, a.e + b.e + re_abs(v)); }
+static inline real operator-(real a, real b) { double v = a.v - b.v; return real(v, a.e + b.e + re_abs(v)); }
+static inline real operator*(real a, real b) {
+    double v = a.v * b.v;
+    return real(v, re_abs(a.v) * b.e + re_abs(b.v) * a.e + re_abs(v));
+}
+static inline real operator/(real a, real b) {
+    double v = a.v / b.v;
+    return real(v, a.e / re_abs(b.v) + re_abs(v) * b.e / re_abs(b.v) + re_abs(v));
+}
+static inline real& operator+=(real& a, real b) { a = a + b; return a; }
+static inline real& operator*=(real& a, real b) { a = a * b; return a; }
+static inline bool operator<(real a, real b) { return a.v < b.v; }
+static inline bool operator>(real a, real b) { return a.v > b.v; }
+static inline bool operator<=(real a, real b) { return a.v <= b.v; }
+static inline bool operator>=(real a, real b) { return a.v >= b.v; }
+static inline bool operator==(real a, real b) { return a.v == b.v; }
+static inline bool operator!=(real a, real b) { return a.v != b.v; }
+static inline real re_fma(real a, real b, real c) {   /* one rounding */
+    double v = fma(a.v, b.v, c.v);
+    return real(v, re_abs(a.v) * b.e + re_abs(b.v) * a.e + c.e + re_abs(v));
+}
+static inline real re_sqrt(real a) {
+    double v = sqrt(a.v);
+    return real(v, (v > 0 ? a.e / (2.0 * v) : 0.0) + v);
+}
+static inline real re_exp(real a) {   /* library / MUFU exponentials are good to ~2 ulp */
+    double v = exp(a.v);
+    return real(v, v * a.e + 2.0 * v);
+}
+static inline real re_ceil(real a) { return real(ceil(a.v), 0.0); }   /* only feeds the integer radius */
+#define K(x) real(x)
+#define FMA(a, b, c) re_fma((a), (b), (c))
+#define SQRT(x) re_sqrt(x)
+#define EXP(x) re_exp(x)
+#define CEIL(x) re_ceil(x)
+#define FMIN(a, b) ((b) < (a) ? (b) : (a))
+#define FMAX(a, b) ((b) > (a) ? (b) : (a))
+#define FABS(x) real(re_abs((x).v), (x).e)
+#define FN(n) n##_re
+#define TOD(x) ((x).v)
+/* a decision `x < thr` whose operand sits within RE_UNSURE_K u e of the threshold may fall either way in
+ * binary32 (measured: binary32 results stay within 0.35 u e of the binary64 ones, tests/test_oracle_golden.py) */
+#define RE_UNSURE_K 2.0
+#define UNSURE(x, thr) (re_abs((x).v - (thr)) <= RE_UNSURE_K * 5.9604644775390625e-08 * (x).e)
+extern "C" {
+#elif defined(ORC_F64)
 typedef double real;
 #define K(x) x
 #define FMA(a, b, c) fma((a), (b), (c))
@@ -52,6 +121,8 @@ typedef double real;
 #define FMAX(a, b) fmax((a), (b))
 #define FABS(x) fabs(x)
 #define FN(n) n##_f64
+#define TOD(x) ((double)(x))
+#define UNSURE(x, thr) 0
 #else
 typedef float real;
 #define K(x) x##f
@@ -63,6 +134,8 @@ typedef float real;
 #define FMAX(a, b) fmaxf((a), (b))
 #define FABS(x) fabsf(x)
 #define FN(n) n##_f32
+#define TOD(x) ((double)(x))
+#define UNSURE(x, thr) 0
 #endif
 
 #define TILE 16
@@ -81,13 +154,13 @@ static inline int f2i(real v) {
     if (v != v) return 0;
     if (v >= (real)2147483648.0) return INT32_MAX;
     if (v <= (real)-2147483648.0) return INT32_MIN;
-    return (int)v;
+    return (int)TOD(v);
 }
 static inline int imin(int a, int b) { return a < b ? a : b; }
 static inline int imax(int a, int b) { return a > b ? a : b; }
 
 static inline uint32_t depth_bits(real d) {
-    float f = (float)d;
+    float f = (float)TOD(d);
     uint32_t u;
     memcpy(&u, &f, 4);
     return u;
@@ -392,7 +465,9 @@ void FN(orc_bin)(int P, const int* radii, const int* rects, const real* depths, 
  *   C += rgb * alpha * T ; T *= (1-alpha)
  * n_contrib = 1-based list position of the last blended entry; out = C + T*bg (planar CHW).
  * fragile[pix] = 1 when some decision above sat within `margin` (relative) of its threshold,
- * i.e. a different-but-valid exp() rounding may legally flip it. */
+ * i.e. a different-but-valid exp() rounding may legally flip it; the running-error build (ORC_RE)
+ * also flags decisions whose operand is within 2 u e of the threshold (ill-conditioned pairs of
+ * needle splats, whose exponent carries far more than 1e-4 relative error in binary32). */
 void FN(orc_blend_fwd)(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
                        const real* means2D, const real* colors, const real* conic_opacity,
                        const real* bg, real* out_color, real* final_T, uint32_t* n_contrib,
@@ -417,14 +492,14 @@ void FN(orc_blend_fwd)(int W, int H, const uint32_t* ranges, const uint32_t* poi
                     real q = FMA(co[0] * dx, dx, (co[2] * dy) * dy);
                     real cross = (co[1] * dx) * dy;
                     real power = FMA(q, -K(0.5), -cross);
-                    if (FABS(power) < margin * (FABS(q) + FABS(cross))) frag = 1;
+                    if (FABS(power) < margin * (FABS(q) + FABS(cross)) || UNSURE(power, 0.0)) frag = 1;
                     if (power > K(0.0)) continue;
                     real av = co[3] * EXP(power);
                     real alpha = FMIN(K(0.99), av);
-                    if (FABS(alpha - K(1.0) / K(255.0)) <= margin * (K(1.0) / K(255.0))) frag = 1;
+                    if (FABS(alpha - K(1.0) / K(255.0)) <= margin * (K(1.0) / K(255.0)) || UNSURE(alpha, 1.0 / 255.0)) frag = 1;
                     if (alpha < K(1.0) / K(255.0)) continue;
                     real test_T = T * (K(1.0) - alpha);
-                    if (FABS(test_T - K(0.0001)) <= K(8.0) * margin * K(0.0001)) frag = 1;
+                    if (FABS(test_T - K(0.0001)) <= K(8.0) * margin * K(0.0001) || UNSURE(test_T, 0.0001)) frag = 1;
                     if (test_T < K(0.0001)) break;
                     for (int ch = 0; ch < 3; ++ch)
                         C[ch] = FMA(colors[3 * g + ch] * alpha, T, C[ch]);
@@ -703,3 +778,7 @@ void FN(orc_preprocess_bwd)(int P, int D, int M, const real* means3D, const int*
         }
     }
 }
+
+#ifdef ORC_RE
+}  /* extern "C" */
+#endif

@@ -40,7 +40,28 @@ def lib():
         _lib = ctypes.CDLL(_LIB_PATH)
         _lib.orc_count_instances_f32.restype = ctypes.c_int64
         _lib.orc_count_instances_f64.restype = ctypes.c_int64
+        _lib.orc_count_instances_re.restype = ctypes.c_int64
     return _lib
+
+
+# Third build of the oracle (gs_oracle.c compiled as C++ with -DORC_RE): every `real` is a pair
+# (v = binary64 value, e = first-order bound, in units of u = 2^-24, on the absolute error a binary32
+# evaluation of the same expression accumulates).  Pass dtype=RE to any stage function / rasterize().
+RE = np.dtype([("v", np.float64), ("e", np.float64)])
+U32 = 2.0 ** -24   # binary32 unit roundoff
+
+
+class _ReScalar(ctypes.Structure):
+    _fields_ = [("v", ctypes.c_double), ("e", ctypes.c_double)]
+
+
+def _re_scalar(x):
+    x = float(x)
+    return _ReScalar(x, 0.0 if float(np.float32(x)) == x else abs(x))   # the rule of real(double) in gs_oracle.c
+
+
+def _is_re(dt):
+    return np.dtype(dt) == RE
 
 
 def _p(a):
@@ -48,14 +69,26 @@ def _p(a):
 
 
 def _c(a, dt):
-    return None if a is None else np.ascontiguousarray(a, dtype=dt)
+    if a is None:
+        return None
+    if _is_re(dt):
+        a = np.asarray(a)
+        if a.dtype == RE:
+            return np.ascontiguousarray(a)
+        out = np.zeros(a.shape, RE)      # inputs are exact binary32 values: e = 0
+        out["v"] = a
+        return out
+    return np.ascontiguousarray(a, dtype=dt)
 
 
 def _fn(name, dt):
-    return getattr(lib(), f"{name}_{'f64' if dt == np.float64 else 'f32'}")
+    suffix = "re" if _is_re(dt) else ("f64" if dt == np.float64 else "f32")
+    return getattr(lib(), f"{name}_{suffix}")
 
 
 def _real(dt):
+    if _is_re(dt):
+        return _re_scalar
     return ctypes.c_double if dt == np.float64 else ctypes.c_float
 
 
@@ -215,7 +248,11 @@ def blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype=np.float32, thread
     acc = bufs[0]
     for g in bufs[1:]:
         for k in acc:
-            acc[k] += g[k]
+            if _is_re(dt):   # one more addition: bounds add, plus its own rounding
+                acc[k]["v"] += g[k]["v"]
+                acc[k]["e"] += g[k]["e"] + np.abs(acc[k]["v"])
+            else:
+                acc[k] += g[k]
     return acc
 
 
@@ -255,32 +292,62 @@ def preprocess_backward(means3D, scales, rotations, shs, viewmatrix, projmatrix,
 def rasterize(means3D, opacities, viewmatrix, projmatrix, campos, bg, W, H, tanfovx, tanfovy,
               sh_degree=0, shs=None, colors_precomp=None, scales=None, rotations=None,
               cov3D_precomp=None, scale_modifier=1.0, dL_dpix=None, dtype=np.float32,
-              margin=1e-4, threads=1):
+              margin=1e-4, threads=1, lists_from=None):
     """Whole path. With dL_dpix, also runs the reverse pass and returns the gradients the
-    reference's autograd function hands back (same order/meaning as SURVEY.md §8a a5)."""
+    reference's autograd function hands back (same order/meaning as SURVEY.md §8a a5).
+
+    lists_from: result of a binary32 run of the same scene.  The binary64 / running-error evaluations
+    then take every INTEGER decision of the geometry stage from it (visible set, radii, tile rects, the
+    depth-sorted per-tile lists), so that they differentiate the function the binary32 path evaluates
+    instead of a neighbouring one (a radius that rounds up in one precision and not in the other changes
+    which tiles a splat reaches)."""
     pre = preprocess(means3D, scales, rotations, opacities, shs, viewmatrix, projmatrix, campos,
                      W, H, tanfovx, tanfovy, sh_degree, scale_modifier, cov3D_precomp,
                      colors_precomp, dtype, threads)
-    binned = bin_instances(pre, W, H, dtype)
+    if lists_from is not None:
+        p32 = lists_from["pre"]
+        flipped = np.flatnonzero((p32["radii"] > 0) != (pre["radii"] > 0))
+        if flipped.size:
+            raise RuntimeError(f"visible sets differ between precisions for Gaussians {flipped[:8]} — "
+                               "a cull decision sits on its threshold; pick another seed")
+        for k in ("radii", "rects", "tiles_touched"):
+            pre[k] = p32[k]
+        binned = lists_from["binned"]
+    else:
+        binned = bin_instances(pre, W, H, dtype)
     fwd = blend_forward(pre, binned, bg, W, H, dtype, margin, threads)
     res = dict(pre=pre, binned=binned, fwd=fwd, color=fwd["color"], radii=pre["radii"])
+    res["call"] = dict(means3D=means3D, scales=scales, rotations=rotations, shs=shs, viewmatrix=viewmatrix,
+                       projmatrix=projmatrix, campos=campos, bg=bg, W=W, H=H, tanfovx=tanfovx, tanfovy=tanfovy,
+                       sh_degree=sh_degree, scale_modifier=scale_modifier, cov3D_precomp=cov3D_precomp,
+                       colors_precomp=colors_precomp, dtype=dtype, threads=threads)
     if dL_dpix is not None:
-        gb = blend_backward(pre, binned, fwd, bg, dL_dpix, W, H, dtype, threads)
-        gp = preprocess_backward(means3D, scales, rotations, shs, viewmatrix, projmatrix, campos,
-                                 W, H, tanfovx, tanfovy, sh_degree, pre, gb, scale_modifier,
-                                 cov3D_precomp, colors_precomp, dtype, threads)
-        P = pre["radii"].shape[0]
-        g2 = np.zeros((P, 3), dtype)
-        g2[:, :2] = gb["dL_dmean2D"]
-        res["grads"] = dict(
-            means3D=gp["dL_dmeans3D"], means2D=g2, shs=gp["dL_dsh"],
-            colors_precomp=gb["dL_dcolor"] if colors_precomp is not None else None,
-            opacities=gb["dL_dopacity"].reshape(P, 1), scales=gp["dL_dscales"],
-            rotations=gp["dL_drots"],
-            cov3D_precomp=gp["dL_dcov3D"] if cov3D_precomp is not None else None,
-        )
-        res["gblend"] = gb
-        res["gpre"] = gp
+        backward(res, dL_dpix)
+    return res
+
+
+def backward(res, dL_dpix):
+    """Reverse pass of a finished `rasterize` result (its forward state is reused, not recomputed);
+    adds res["grads"] (+ the stage outputs "gblend", "gpre") and returns res."""
+    c = res["call"]
+    pre, binned, fwd, dtype, threads = res["pre"], res["binned"], res["fwd"], c["dtype"], c["threads"]
+    W, H = c["W"], c["H"]
+    gb = blend_backward(pre, binned, fwd, c["bg"], dL_dpix, W, H, dtype, threads)
+    gp = preprocess_backward(c["means3D"], c["scales"], c["rotations"], c["shs"], c["viewmatrix"], c["projmatrix"],
+                             c["campos"], W, H, c["tanfovx"], c["tanfovy"], c["sh_degree"], pre, gb,
+                             c["scale_modifier"], c["cov3D_precomp"], c["colors_precomp"], dtype, threads)
+    P = pre["radii"].shape[0]
+    g2 = np.zeros((P, 3), dtype)
+    g2[:, :2] = gb["dL_dmean2D"]
+    res["grads"] = dict(
+        means3D=gp["dL_dmeans3D"], means2D=g2, shs=gp["dL_dsh"],
+        colors_precomp=gb["dL_dcolor"] if c["colors_precomp"] is not None else None,
+        opacities=gb["dL_dopacity"].reshape(P, 1), scales=gp["dL_dscales"],
+        rotations=gp["dL_drots"],
+        cov3D_precomp=gp["dL_dcov3D"] if c["cov3D_precomp"] is not None else None,
+    )
+    res["gblend"] = gb
+    res["gpre"] = gp
     return res
 
 

@@ -13,7 +13,7 @@ def make_case(P, W, H, seed=0, sh_coeffs=16, **kw):
 
 
 def run_oracle(O, cam, g, bg, sh_degree, dL_dpix=None, dtype=np.float32, threads=8, colors_precomp=None,
-               cov3D_precomp=None, scale_modifier=1.0, margin=1e-4):
+               cov3D_precomp=None, scale_modifier=1.0, margin=1e-4, lists_from=None):
     use_sr = cov3D_precomp is None
     return O.rasterize(g["means3D"], g["opacities"], cam.world_view_transform, cam.full_proj_transform,
                        cam.camera_center, np.asarray(bg, np.float32), cam.width, cam.height, cam.tanfovx,
@@ -21,7 +21,7 @@ def run_oracle(O, cam, g, bg, sh_degree, dL_dpix=None, dtype=np.float32, threads
                        colors_precomp=colors_precomp, scales=g["scales"] if use_sr else None,
                        rotations=g["rotations"] if use_sr else None, cov3D_precomp=cov3D_precomp,
                        scale_modifier=scale_modifier, dL_dpix=dL_dpix, dtype=dtype, threads=threads,
-                       margin=margin)
+                       margin=margin, lists_from=lists_from)
 
 
 def settings_for(cam, bg, sh_degree, device, scale_modifier=1.0, debug=False):
