@@ -55,38 +55,79 @@ def close(a, b, scale=None, rel=REL_TOL):
     return worst <= rel, worst
 
 
-def grad_report(a, b64, o32, rel=REL_TOL):
-    """Gradient comparison against the binary64 oracle, aware of binary32 conditioning.
+GRAD_K = 1.0   # multiples of the running rounding-error bound u*e accepted per element (see grad_check)
 
-    Per-Gaussian gradients are signed sums over hundreds of pixels and then pass through
-    det^-2-type cancellations (needle-shaped splats), so the binary32 restatement of the
-    reference algorithm (`o32`) itself deviates from exact arithmetic (`b64`) by up to ~1e-2 on a
-    fraction ~5e-3 of the ELEMENTS (measured; see DESIGN.md "Tolerances").  The 1e-4 bar is
-    therefore asserted on
-      (1) the tensor-level relative error  sum|a-b| / sum|b|  <= rel, and
-      (2) element-wise |a-b| <= rel*max(|b|, mean|b|) for all but a fraction of elements no larger
-          than twice the fraction on which the fp32 oracle itself exceeds it (+1e-3), with the worst
-          element no worse than 5x the fp32 oracle's own worst element (+10 rel).  The additive slack is
-          there because the fp32 oracle's worst element is itself a draw: its backward runs on all host
-          threads, so its summation order — and with it that figure — changes from run to run (measured on
-          the opaque-wall stress case, tools/flaky_probe.py: 1.4e-4 ... 1.5e-3 for the oracle against a
-          steady 1.0e-3 for the CUDA path, old and new blend-backward kernels alike).  For the same reason
-          a worst element below 5 % of the tensor's mean magnitude is accepted whatever the oracle drew:
-          how MANY elements may be that far off is what rule (2)'s fraction bounds.
-    Returns (ok, dict of the measured figures)."""
-    a, b, o = (np.asarray(x, np.float64) for x in (a, b64, o32))
-    nz = np.abs(b[b != 0])
-    scale = float(nz.mean()) if nz.size else 1.0
-    den = np.maximum(np.abs(b), scale)
-    ea, eo = np.abs(a - b) / den, np.abs(o - b) / den
-    tot = float(np.abs(b).sum()) or 1.0
-    rep = dict(rel_l1=float(np.abs(a - b).sum()) / tot, rel_l1_fp32_oracle=float(np.abs(o - b).sum()) / tot,
-               frac=float((ea > rel).mean()) if ea.size else 0.0,
-               frac_fp32_oracle=float((eo > rel).mean()) if eo.size else 0.0,
-               worst=float(ea.max()) if ea.size else 0.0, worst_fp32_oracle=float(eo.max()) if eo.size else 0.0)
-    ok = (rep["rel_l1"] <= rel and rep["frac"] <= 2 * rep["frac_fp32_oracle"] + 1e-3
-          and rep["worst"] <= max(5 * rep["worst_fp32_oracle"] + 10 * rel, 0.05))
+
+def gradient_reference(O, cam, g, bg, sh_degree, dL, threads=8, zero_fragile=True, **kw):
+    """The references a gradient test compares with, sharing ONE set of integer decisions:
+      ref32 — the binary32 oracle (forward + backward): radii / lists / image are compared with it;
+      refre — the running-error build (binary64 values `v` + per-element bound `e` on what a binary32
+              evaluation of the same expressions accumulates, in units of u = 2^-24), evaluated on the
+              binary32 run's visible set, radii, rects and sorted lists.
+    dL is zeroed on pixels either run flags `fragile` (a skip / stop decision within its own rounding
+    error of the threshold: the binary32 reference itself may fall either way there).  Returns
+    (dL, ref32, refre, fragile)."""
+    ref32 = run_oracle(O, cam, g, bg, sh_degree, threads=threads, **kw)
+    refre = run_oracle(O, cam, g, bg, sh_degree, dtype=O.RE, threads=threads, lists_from=ref32, **kw)
+    fragile = ref32["fwd"]["fragile"] | refre["fwd"]["fragile"]
+    dL = np.array(dL, np.float32, copy=True)
+    if zero_fragile:
+        dL[:, fragile] = 0.0
+    O.backward(ref32, dL)
+    O.backward(refre, dL)
+    return dL, ref32, refre, fragile
+
+
+def grad_check(a, re, rel=REL_TOL, k=GRAD_K):
+    """Conditioning-aware ELEMENTWISE gradient bound, every element, no outlier budget.
+
+    `re` is a gradient tensor of the running-error oracle: re["v"] the binary64 value, re["e"] a
+    first-order bound (units of u = 2^-24) on the absolute error that ANY binary32 evaluation of the
+    reference's expressions accumulates for that element — it grows with the magnitude of the terms that
+    are summed and cancelled on the way (hundreds of signed per-pixel terms, det = ac - b^2 of needle
+    splats, 1 - alpha, the T chain), which is what makes some elements ill-conditioned in binary32.
+    Rule:   |a - v| <= max(rel * |v|, k * u * e)   for EVERY element,
+    i.e. 1e-4 relative (north_star), or within k times the rounding-error bound of the reference algorithm
+    itself where that is larger.  Measured: the binary32 oracle stays below 0.35 u e on every
+    element; typical elements sit at 0.002 u e.  Also asserted: tensor-level sum|a-v| / sum|v| <= rel and the
+    99.9th percentile of |a-v| / (u e) <= k / 2.
+    Returns (ok, dict of measured figures)."""
+    a = np.asarray(a, np.float64)
+    v, e = np.asarray(re["v"], np.float64), np.asarray(re["e"], np.float64)
+    assert a.shape == v.shape, (a.shape, v.shape)
+    err = np.abs(a - v)
+    ue = (2.0 ** -24) * e
+    bound = np.maximum(rel * np.abs(v), k * ue)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ratio = np.where(ue > 0, err / ue, np.where(err > 0, np.inf, 0.0))
+    tot = float(np.abs(v).sum()) or 1.0
+    bad = err > bound
+    rep = dict(rel_l1=float(err.sum()) / tot, worst_over_ue=float(ratio.max()) if ratio.size else 0.0,
+               p999_over_ue=float(np.quantile(ratio, 0.999)) if ratio.size else 0.0,
+               median_over_ue=float(np.median(ratio)) if ratio.size else 0.0,
+               n_outside=int(bad.sum()), n=int(a.size),
+               frac_rel_gt_tol=float((err > rel * np.abs(v)).mean()) if a.size else 0.0)
+    if bad.any():
+        i = np.unravel_index(int(np.argmax(np.where(bad, err / np.maximum(bound, 1e-300), 0.0))), a.shape)
+        rep["worst_element"] = dict(index=tuple(int(x) for x in i), got=float(a[i]), want=float(v[i]), ue=float(ue[i]))
+    ok = (not bad.any()) and rep["rel_l1"] <= rel and rep["p999_over_ue"] <= 0.5 * k
     return ok, rep
+
+
+def dump_grad_report(title, report):
+    """Appends the measured per-tensor figures of grad_check to $GRAD_REPORT (default gpurun_out/grad_report.txt)."""
+    import os
+    path = os.environ.get("GRAD_REPORT", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                      "gpurun_out", "grad_report.txt"))
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        with open(path, "a") as f:
+            for k, r in report.items():
+                f.write(f"{title} {k}: worst |a-v|/(u e) {r['worst_over_ue']:.3f}  p99.9 {r['p999_over_ue']:.3f}  median "
+                        f"{r['median_over_ue']:.4f}  rel_l1 {r['rel_l1']:.2e}  outside {r['n_outside']}/{r['n']}  "
+                        f"(elements beyond plain 1e-4 relative: {r['frac_rel_gt_tol']:.2e})\n")
+    except OSError:
+        pass
 
 
 def depth_order_emission(pre, binned):

@@ -5,9 +5,13 @@ Bar (BASELINE.json north_star): bit-exact radii, tile counts, (tile|depth) key l
 point lists and tile ranges; image and gradient tensors within 1e-4 relative (fp32).
 
 Pixels the oracle flags `fragile` (a skip/stop decision sits within 1e-4 relative of its
-threshold, so a different but valid exp() rounding may legally flip it) are excluded from the
-image comparison and carry zero upstream gradient in the backward comparison; their share is
-asserted to be small.
+threshold — or, in the running-error build, within its own binary32 rounding error of it — so a
+different but valid exp() rounding may legally flip it) are excluded from the image comparison and
+carry zero upstream gradient in the backward comparison; their share is asserted to be small, and
+tests/test_gpu_fragile.py looks at the gradients THROUGH them.
+
+Gradients: every element within max(1e-4 relative, running rounding-error bound of the reference
+algorithm in binary32) of the binary64 value — helpers.grad_check.
 """
 import numpy as np
 import pytest
@@ -109,12 +113,9 @@ def check_backward(cuda, oracle, P, W, H, D, M, seed, threads=8):
     from mvs_gaussian_splatting_b200 import GaussianRasterizer
     cam, g = Hh.make_case(P, W, H, seed=seed, sh_coeffs=M)
     bg = [0.3, 0.2, 0.7]
-    fragile = Hh.run_oracle(oracle, cam, g, bg, D, threads=threads)["fwd"]["fragile"]
     rng = np.random.default_rng(100 + seed)
-    dL = rng.normal(size=(3, H, W)).astype(np.float32)
-    dL[:, fragile] = 0.0
-    ref = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, threads=threads)
-    ref64 = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, dtype=np.float64, threads=threads)
+    dL, ref, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D, rng.normal(size=(3, H, W)), threads=threads)
+    assert fragile.mean() < 0.06
 
     rs = Hh.settings_for(cam, bg, D, cuda)
     t = Hh.to_dev(g, cuda, requires_grad=True)
@@ -126,14 +127,18 @@ def check_backward(cuda, oracle, P, W, H, D, M, seed, threads=8):
     got = dict(means3D=t["means3D"].grad, means2D=means2D.grad, shs=t["shs"].grad, opacities=t["opacities"].grad,
                scales=t["scales"].grad, rotations=t["rotations"].grad)
     np.testing.assert_array_equal(radii.cpu().numpy(), ref["radii"])
+    report = {}
     for k, v in got.items():
         assert v is not None, k
         a = v.cpu().numpy()
         want = ref["grads"][k]
         assert a.shape == want.shape, k
         assert np.isfinite(a).all(), k
-        ok, rep = Hh.grad_report(a, ref64["grads"][k], want)
+        ok, rep = Hh.grad_check(a, refre["grads"][k])
+        report[k] = rep
         assert ok, f"{k}: {rep}"
+    if P >= 100000:   # the figures DESIGN.md quotes (pytest -s, or the GRAD_REPORT file)
+        Hh.dump_grad_report(f"P={P} {W}x{H} SH{D}", report)
     # rows of culled Gaussians are exact zeros (the reference leaves its zero-initialised tensors)
     culled = ref["radii"] == 0
     for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations"):

@@ -36,20 +36,17 @@ def _run_gpu(cuda, cam, g, bg, D, dL, colors=None, cov=None, scale_modifier=1.0)
 def _check(cuda, oracle, cam, g, bg, D, seed, colors=None, cov=None, scale_modifier=1.0):
     W, H = cam.width, cam.height
     kw = dict(colors_precomp=colors, cov3D_precomp=cov, scale_modifier=scale_modifier)
-    fwd = Hh.run_oracle(oracle, cam, g, bg, D, **kw)
-    dL = np.random.default_rng(seed).normal(size=(3, H, W)).astype(np.float32)
-    dL[:, fwd["fwd"]["fragile"]] = 0.0
-    ref = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, **kw)
-    ref64 = Hh.run_oracle(oracle, cam, g, bg, D, dL_dpix=dL, dtype=np.float64, **kw)
+    dL, ref, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D,
+                                                    np.random.default_rng(seed).normal(size=(3, H, W)), **kw)
     img, radii, grads = _run_gpu(cuda, cam, g, bg, D, dL, colors, cov, scale_modifier)
     np.testing.assert_array_equal(radii, ref["radii"])
-    ok = ~fwd["fwd"]["fragile"]
+    ok = ~fragile
     good, worst = Hh.close(img[:, ok], ref["color"][:, ok], scale=1.0)
     assert good, f"image worst rel err {worst:.3e}"
     for k, a in grads.items():
         want = ref["grads"][k]
         assert want is not None and a.shape == want.shape, k
-        good, rep = Hh.grad_report(a, ref64["grads"][k], want)
+        good, rep = Hh.grad_check(a, refre["grads"][k])
         assert good, f"{k}: {rep}"
     return ref
 

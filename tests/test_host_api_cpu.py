@@ -76,17 +76,3 @@ def test_gradient_arena_layout():
         assert v.untyped_storage().data_ptr() == a.flat.untyped_storage().data_ptr()
     a.shs.fill_(2.0)
     assert float(a.flat.sum()) == 2.0 * 3 * M * P
-
-
-def test_grad_report_accepts_fp32_noise_and_rejects_real_errors():
-    rng = np.random.default_rng(0)
-    b = rng.normal(size=(1000, 3))
-    o32 = b.astype(np.float32)
-    ok, rep = Hh.grad_report(o32 * (1 + 2e-6), b, o32)
-    assert ok, rep
-    bad = o32.copy()
-    bad[:50] *= 1.01
-    ok, rep = Hh.grad_report(bad, b, o32)
-    assert not ok
-    ok, rep = Hh.grad_report(o32 * 1.001, b, o32)
-    assert not ok

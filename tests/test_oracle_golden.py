@@ -213,3 +213,51 @@ def test_backward_matches_finite_differences_f64(oracle):
             assert abs(fd - an) <= 2e-4 * max(1.0, abs(an), abs(fd)), (name, idx, fd, an)
             checked += 1
     assert checked == 60
+
+
+# ---------------------------------------------------------------------------------------------------
+# running-error build (oracle/gs_oracle.c compiled with -DORC_RE): the conditioning-aware scale of the
+# elementwise gradient rule (helpers.grad_check)
+# ---------------------------------------------------------------------------------------------------
+def test_running_error_build_values_equal_f64_and_bound_the_fp32_oracle(oracle):
+    P, W, H, D = 3000, 200, 120, 3
+    cam, g = Hh.make_case(P, W, H, seed=21)
+    bg = [0.3, 0.2, 0.7]
+    dL0 = np.random.default_rng(5).normal(size=(3, H, W))
+    dL, ref32, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D, dL0, threads=4)
+    assert fragile.mean() < 0.06 and not dL[:, fragile].any()
+    # same integer decisions in both runs (lists_from), same values as the plain binary64 build on them
+    ref64 = Hh.run_oracle(oracle, cam, g, bg, D, dtype=np.float64, threads=4, lists_from=ref32)
+    oracle.backward(ref64, dL)
+    np.testing.assert_array_equal(refre["fwd"]["n_contrib"], ref32["fwd"]["n_contrib"])
+    culled = ref32["radii"] == 0
+    for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations"):
+        v, e = refre["grads"][k]["v"], refre["grads"][k]["e"]
+        np.testing.assert_allclose(v, ref64["grads"][k], rtol=1e-9, atol=1e-300, err_msg=k)
+        assert (e >= 0).all() and np.isfinite(e).all(), k
+        assert not v[culled].any() and not e[culled].any(), k          # exact zeros carry no error
+        assert (e[v != 0] >= np.abs(v[v != 0])).all(), k            # at least its own final rounding
+        # the binary32 restatement of the same algorithm sits well inside the bound, on every element
+        ok, rep = Hh.grad_check(ref32["grads"][k], refre["grads"][k])
+        assert ok and rep["worst_over_ue"] < 0.6, (k, rep)
+        # a 1 % error on every element is far outside it
+        ok, rep = Hh.grad_check(ref32["grads"][k] * 1.01, refre["grads"][k])
+        assert not ok, k
+        # ... and so is one on 50 elements only (no outlier budget)
+        bad = ref32["grads"][k].copy().reshape(-1)
+        idx = np.argsort(-np.abs(bad))[:50]
+        bad[idx] *= 1.05
+        ok, rep = Hh.grad_check(bad.reshape(ref32["grads"][k].shape), refre["grads"][k])
+        assert not ok and rep["n_outside"] >= 1, (k, rep)
+
+
+def test_running_error_scalar_rules(oracle):
+    """The arithmetic of the (v, e) pairs on a case small enough to follow by hand: cov3D of an axis-aligned
+    Gaussian with unit quaternion is diag(s^2) — products of exact inputs, so e is one rounding of the result
+    for the diagonal and exactly zero... for entries that are sums of exact zeros only their own rounding."""
+    sc = np.array([[0.5, 2.0, 3.0]], np.float32)
+    q = np.array([[1.0, 0.0, 0.0, 0.0]], np.float32)
+    out = oracle.cov3d(sc, q, 1.0, dtype=oracle.RE)
+    np.testing.assert_array_equal(out["v"][0], [0.25, 0.0, 0.0, 4.0, 0.0, 9.0])
+    assert (out["e"][0][[1, 2, 4]] == 0).all()                    # sums of exact zeros
+    assert (out["e"][0][[0, 3, 5]] > 0).all() and (out["e"][0][[0, 3, 5]] < 16 * out["v"][0][[0, 3, 5]]).all()
