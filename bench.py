@@ -3,11 +3,13 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
     python bench.py --impl reference --steps K --warmup W    # the CPU arm (oracle port, host cores)
 
-Workload (BASELINE.json configs[2], the one the metric is quoted on): 3 M synthetic Gaussians,
-SH degree 3, 1920x1080, one view per step per GPU, forward + backward with a fixed seeded
-dL/dpixel.  A "step" is one fwd+bwd of one view on every rank; with N > 1 each rank renders its
-own camera of the batch (weak scaling, one camera subset per GPU) and the 59-float-per-Gaussian
-parameter gradients are summed with ONE NCCL all-reduce inside the timed region.
+Workloads.  N = 1 (the headline): BASELINE.json configs[2], the one the metric is quoted on — 3 M synthetic
+Gaussians, SH degree 3, 1920x1080, one view per step, forward + backward with a fixed seeded dL/dpixel.
+N > 1: BASELINE.json configs[3] — 6 M Gaussians, an 8-VIEW batch per step split over the N GPUs (rank r
+renders views r, r+N, ...; cameras on SURVEY 8d's radius-4 ring), Gaussian-sharded: each rank owns 1/N of
+the parameters and of their gradients; the exchange is fused into the per-Gaussian kernels over NVLink peer
+memory.  The same batch on ONE GPU is measured inside the N = 1 line (key `multi_view_batch`), which is the
+single-GPU point of that scaling curve.  `--points / --views` select other sizes.
 Prints ONE JSON line on rank 0 (contract: see DESIGN.md "Measurement").
 """
 from __future__ import annotations
@@ -44,7 +46,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--points", type=int, default=3_000_000)
+    ap.add_argument("--points", type=int, default=None,
+                    help="Gaussians (default: 3 000 000 at one GPU = configs[2]; 6 000 000 at N > 1 = configs[3])")
+    ap.add_argument("--views", type=int, default=None,
+                    help="views per step, a multiple of the GPU count (default: 1 at one GPU; 8 at N > 1)")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--sh-degree", type=int, default=3)
@@ -62,14 +67,44 @@ def parse_args():
     return ap.parse_args()
 
 
-def bench_camera(k: int, W: int, H: int) -> S.Camera:
-    """Camera k of the batch: k = 0 is the front camera the scene was generated for; the others sit
-    on a 0.5-unit ring around it and look at the scene centre (similar work per rank)."""
-    if k == 0:
-        return S.front_camera(W, H)
-    a = 2 * math.pi * (k - 1) / 7.0
-    R, t = S.look_at([0.5 * math.cos(a), 0.5 * math.sin(a), 0.0], [0.0, 0.0, 10.5])
-    return S.make_camera(R, t, math.radians(60.0), W, H)
+def workload_sizes(args, world: int):
+    """(P, V): defaults follow BASELINE.json — configs[2] on one GPU, configs[3] (6 M, 8-view batch) on N > 1."""
+    P = args.points if args.points is not None else (3_000_000 if world == 1 else 6_000_000)
+    V = args.views if args.views is not None else (1 if world == 1 else 8)
+    if V < 1 or V % world:
+        raise SystemExit(f"bench.py: --views {V} must be a positive multiple of --gpus {world}")
+    return P, V
+
+
+def workload_text(P, D, W, H, V) -> str:
+    """The ONE description of the workload both arms print (the driver compares the strings)."""
+    return (f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, " +
+            ("1 view per step (front camera)" if V == 1 else f"{V}-view batch per step (cameras on a radius-4 ring)"))
+
+
+def baseline_config(P, V, W, H) -> str:
+    if (P, V, W, H) == (3_000_000, 1, 1920, 1080):
+        return "BASELINE.json configs[2]"
+    if (P, V, W, H) == (6_000_000, 8, 1920, 1080):
+        return "BASELINE.json configs[3]"
+    return "custom (--points/--views/--width/--height)"
+
+
+def measured_simt_peaks():
+    """FP32 / MUFU peaks measured on this pool's B200 with tools/fp32_peak.cu (profiles/r02a_fp32_peak.json);
+    MEASURED_PEAKS.json carries HBM and tensor-core figures only."""
+    p = os.path.join(ROOT, "profiles", "r02a_fp32_peak.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return dict(ffma_tflops=float(d["ffma_reg_tflops"]["best"]), ffma_3src_tflops=float(d["ffma_3src_tflops"]["best"]),
+                    mufu_tops=float(d["mufu_ex2_tops"]["best"]), source="measured: tools/fp32_peak.cu on B200 "
+                    "(profiles/r02a_fp32_peak.json; FFMA with two distinct source registers; with three distinct "
+                    "sources the register file sustains " + f"{float(d['ffma_3src_tflops']['best']):.1f} TFLOP/s)")
+    except (OSError, KeyError, ValueError):
+        nominal = N_SM * FP32_LANES_PER_SM * 2 * 1965e6 / 1e12
+        return dict(ffma_tflops=nominal, ffma_3src_tflops=None, mufu_tops=None,
+                    source="nominal 148 SM x 128 lanes x 2 x 1.965 GHz (no measured SIMT figure found)")
 
 
 def load_peaks():
@@ -172,6 +207,35 @@ class CpuArm:
         return dict(t_view_s=t_full, t_wall_s=t3 - t0, rows_frac=frac, t_fixed_s=(t1 - t0) + (t3 - t2),
                     t_blend_s=t2 - t1)
 
+    def forward_only(self, budget_s=12.0):
+        """Forward-only frame on the host cores (configs[4]): preprocess + binning in full, the blend on every
+        s-th tile row when the budget requires it (time scaled by rows)."""
+        O, g, cam, th = self.O, self.g, self.cam, self.threads
+        W, H = cam.width, cam.height
+        bg = np.zeros(3, np.float32)
+        t0 = time.perf_counter()
+        pre = O.preprocess(g["means3D"], g["scales"], g["rotations"], g["opacities"], g["shs"], cam.world_view_transform,
+                           cam.full_proj_transform, cam.camera_center, W, H, cam.tanfovx, cam.tanfovy, self.D, threads=th)
+        binned = O.bin_instances(pre, W, H)
+        t1 = time.perf_counter()
+        # calibrate the blend on 1/16 of the tile rows, then size the sample for the budget
+        tr = self.rows(16)
+        O.blend_forward(pre, binned, bg, W, H, threads=th, tile_ranges=tr)
+        t_cal = (time.perf_counter() - t1) * self.gy / len(tr)
+        stride = 1
+        while stride < self.gy and t_cal * len(self.rows(stride)) / self.gy > budget_s:
+            stride += 1
+        tr = None if stride == 1 else self.rows(stride)
+        t2 = time.perf_counter()
+        O.blend_forward(pre, binned, bg, W, H, threads=th, tile_ranges=tr)
+        t3 = time.perf_counter()
+        frac = 1.0 if stride == 1 else len(tr) / self.gy
+        t_frame = (t1 - t0) + (t3 - t2) / frac
+        return {"value": 1.0 / t_frame, "unit": "frames/s", "ms_per_frame": 1e3 * t_frame, "cores": th,
+                "kind": "port" if stride == 1 else "port-extrapolated",
+                "sample": "preprocess + binning of all Gaussians; blend forward on " +
+                          ("all tile rows" if stride == 1 else f"every {stride}th tile row ({len(tr)}/{self.gy}), time scaled by rows")}
+
     def describe(self, stride):
         if stride == 1:
             return "full view: all Gaussians, all tiles"
@@ -183,9 +247,11 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # under torchrun only rank 0 runs the CPU arm
-    W, H, P, D = args.width, args.height, args.points, args.sh_degree
-    cam = bench_camera(0, W, H)
-    g = S.make_gaussians(P, cam, seed=0)
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    W, H, D = args.width, args.height, args.sh_degree
+    P, V = workload_sizes(args, max(world, args.gpus))
+    cam = S.batch_cameras(V, W, H)[0]            # one view of the batch: views/s = 1 / seconds per view
+    g = S.make_gaussians(P, S.front_camera(W, H), seed=0)
     dL = np.random.Generator(np.random.PCG64(1234)).normal(size=(3, H, W)).astype(np.float32)
     th = host_threads()
     arm = CpuArm(g, cam, D, dL, th)
@@ -201,12 +267,16 @@ def run_reference_arm(args):
     ts = [arm.step(stride)["t_view_s"] for _ in range(args.steps)]
     t = float(np.mean(ts)) if ts else cal["t_view_s"]
     value = 1.0 / t
+    kind = "port" if stride == 1 else "port-extrapolated"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, 1 view", "arm": "CPU oracle port, host cores"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": th, "kind": "port", "sample": arm.describe(stride)},
+        "config": {"workload": workload_text(P, D, W, H, V), "baseline_config": baseline_config(P, V, W, H),
+                   "arm": "CPU oracle port (oracle/gs_oracle.c), all host cores; the reference's own CUDA rasterizer is "
+                          "an un-vendored submodule and is not installed on the box (tools/probe_reference_cuda.py); "
+                          "one view of the batch is timed, views/s = 1 / seconds per view"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": th, "kind": kind, "sample": arm.describe(stride)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -242,7 +312,8 @@ def stage_rooflines(stage_ms, counts, peaks, clocks):
         "blend_forward": FLOP_PER_EVAL * E + FLOP_PER_BLEND_FWD * C,
         "blend_backward": FLOP_PER_EVAL * En + FLOP_PER_BLEND_BWD * C,
     }
-    fp32_peak = N_SM * FP32_LANES_PER_SM * 2 * peaks["sm_max_mhz"] * 1e6 / 1e12  # TFLOP/s, FMA = 2
+    simt = measured_simt_peaks()
+    fp32_peak = simt["ffma_tflops"]   # TFLOP/s, FMA = 2 flops
     out = {}
     for name, ms in stage_ms.items():
         if ms <= 0:
@@ -256,9 +327,25 @@ def stage_rooflines(stage_ms, counts, peaks, clocks):
             a = flops[name] / (ms * 1e-3) / 1e12
             out[name] = {"bound": "fp32_simt_issue", "achieved": a, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": a / fp32_peak, "traffic": None, "ms": ms, "algorithmic_flops": flops[name],
-                         "peak_source": "nominal 148 SM x 128 lanes x 2 x clocks.max.sm (no tensor-core work on "
-                                        "this path; MEASURED_PEAKS.json has no FP32 SIMT figure)"}
+                         "peak_source": simt["source"],
+                         "note": "achieved counts the REFERENCE algorithm's flops per launch (18 per evaluated pair + "
+                                 "8 / 73 per blended pair); culling never issues most of them, so this is a useful-work "
+                                 "rate — pipe utilisation is the ncu issue-slot figure in `issue_slot_pct`",
+                         "issue_slot_pct": ncu_issue.get(name)}
     return out
+
+
+def load_ncu_issue():
+    """Issue-slot utilisation (smsp__issue_active, % of peak) of the two blend kernels from the committed
+    ncu --set full capture (profiles/*_ncu_full_summary.md); {} when none is recorded."""
+    p = os.path.join(ROOT, "profiles", "issue_slots.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
+
+
+ncu_issue = load_ncu_issue() if os.path.isdir(os.path.join(ROOT, "profiles")) else {}
 
 
 def load_traffic():
@@ -268,6 +355,18 @@ def load_traffic():
         with open(p) as f:
             return json.load(f)
     return {}
+
+
+def _event_stats(events, world, dist, torch, dev):
+    """Per-step device times from K+1 events: (mean, median, p90) in ms, each the MAX over ranks."""
+    per = np.array([events[i].elapsed_time(events[i + 1]) for i in range(len(events) - 1)], np.float64)
+    vals = [float(events[0].elapsed_time(events[-1])) / max(len(per), 1), float(np.median(per)),
+            float(np.quantile(per, 0.9))]
+    if world > 1:
+        tt = torch.tensor(vals, device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        vals = [float(x) for x in tt.tolist()]
+    return vals
 
 
 def run_b200_arm(args):
@@ -289,51 +388,54 @@ def run_b200_arm(args):
         dist.init_process_group("nccl", device_id=dev)
     _native.lib()  # fail loudly when libgsrast_b200.so is missing
 
-    W, H, P, D = args.width, args.height, args.points, args.sh_degree
+    W, H, D = args.width, args.height, args.sh_degree
+    P, V = workload_sizes(args, world)
     M = 16
-    g = S.make_gaussians(P, bench_camera(0, W, H), sh_coeffs=M, seed=0)   # same scene on every rank
-    cam = bench_camera(rank, W, H)                                        # this rank's camera of the batch
+    warmup = max(args.warmup, 3 if world == 1 else 20)   # the double-buffered peer exchange needs a longer run-in
+    g = S.make_gaussians(P, S.front_camera(W, H), sh_coeffs=M, seed=0)   # same scene on every rank
+    cam_list = S.batch_cameras(V, W, H)
     host = {k: torch.from_numpy(v).pin_memory() for k, v in g.items()}
     t = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-    kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], D)
-    cam_host = torch.from_numpy(np.concatenate([kw["viewmatrix"].ravel(), kw["projmatrix"].ravel(),
-                                                kw["campos"].ravel(), kw["bg"].ravel()]).astype(np.float32)).pin_memory()
+    multi = V > 1 or world > 1            # a batch of views: the Gaussian-sharded step (world 1: "local" transport)
+    if multi and not args.multi.startswith("sharded") and V != world:
+        raise SystemExit("bench.py: --multi allreduce renders one view per rank (use --views equal to --gpus)")
 
-    def settings_from(block):
-        k2 = dict(kw)
+    def cam_block(c):
+        kw = S.settings_kwargs(c, [0.0, 0.0, 0.0], D)
+        return np.concatenate([kw["viewmatrix"].ravel(), kw["projmatrix"].ravel(), kw["campos"].ravel(),
+                               kw["bg"].ravel()]).astype(np.float32)
+
+    kw0 = S.settings_kwargs(cam_list[0], [0.0, 0.0, 0.0], D)
+
+    def settings_from(block, v=0):
+        k2 = S.settings_kwargs(cam_list[v], [0.0, 0.0, 0.0], D) if v else dict(kw0)
         k2.update(viewmatrix=block[0:16].view(4, 4), projmatrix=block[16:32].view(4, 4), campos=block[32:35],
                   bg=block[35:38])
         return GaussianRasterizationSettings(**k2)
 
-    rs = settings_from(cam_host.to(dev))
+    cam_host = torch.from_numpy(np.concatenate([cam_block(c) for c in cam_list])).pin_memory()   # 38 floats per view
+    cam_dev = cam_host.to(dev)
+    cams_all = [settings_from(cam_dev[38 * v:38 * v + 38], v) for v in range(V)]
+    rs = cams_all[rank % V]
     rng = np.random.Generator(np.random.PCG64(1234))
     dL_np = rng.normal(size=(3, H, W)).astype(np.float32)
     dL = torch.from_numpy(dL_np).to(dev)
-    arena = GradientArena(P, M, dev)
-    sharded = world > 1 and args.multi.startswith("sharded")
-    sr = cams_all = slices = None
+    sharded = multi and args.multi.startswith("sharded")
+    arena = None if sharded else GradientArena(P, M, dev)
+    sr = slices = dL_local = None
     if sharded:
         from mvs_gaussian_splatting_b200.sharded import ShardedViewRasterizer
-        sr = ShardedViewRasterizer(P, M, W, H, dev, exchange="nccl" if args.multi == "sharded-nccl" else "peer")
+        sr = ShardedViewRasterizer(P, M, W, H, dev, exchange="nccl" if args.multi == "sharded-nccl" else "peer",
+                                   n_views=V)
         rows = sr.plan.rows(rank)
         slices = {k: t[k][rows].contiguous() for k in ("means3D", "shs", "opacities", "scales", "rotations")}
-        cams_all = []
-        for v in range(world):
-            kv = S.settings_kwargs(bench_camera(v, W, H), [0.0, 0.0, 0.0], D)
-            for k in ("bg", "viewmatrix", "projmatrix", "campos"):
-                kv[k] = torch.from_numpy(np.ascontiguousarray(kv[k])).to(dev)
-            cams_all.append(GaussianRasterizationSettings(**kv))
-        blocks = []
-        for v in range(world):
-            kv = S.settings_kwargs(bench_camera(v, W, H), [0.0, 0.0, 0.0], D)
-            blocks += [kv["viewmatrix"].ravel(), kv["projmatrix"].ravel(), kv["campos"].ravel(), kv["bg"].ravel()]
-        cam_host_all = torch.from_numpy(np.concatenate(blocks).astype(np.float32)).pin_memory()
+        dL_local = dL.unsqueeze(0).expand(sr.L, 3, H, W).contiguous()
 
     def step():
         if sharded:
             sr.forward(slices, cams_all)
-            sr.backward(dL)
-            return sr._state[0]
+            sr.backward(dL_local)
+            return sr._state[0][0]
         color, radii, ctx, inp = rasterize_forward(t["means3D"], t["shs"], None, t["opacities"], t["scales"],
                                                    t["rotations"], None, rs)
         rasterize_backward(ctx, inp, rs, dL, arena=arena)
@@ -347,97 +449,234 @@ def run_b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         ctx = step()
     barrier()
+    # ---- headline: K steps, stage timing OFF, one event per step boundary on the launching stream ----
     sampler = ClockSampler(local)
     sampler.start()
+    events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    n0 = _native.launch_count()
+    events[0].record()
+    for i in range(args.steps):
+        ctx = step()
+        events[i + 1].record()
+    barrier()
+    launches = _native.launch_count() - n0
+    clocks = sampler.result()
+    ms_step, ms_median, ms_p90 = _event_stats(events, world, dist, torch, dev)
+    value = V * 1e3 / ms_step
+    # ---- second pass: the same K steps with the library's per-stage event pairs switched on ----
     _native.stage_timing_enable(True)
     _native.stage_timing_read()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n0 = _native.launch_count()
     e0.record()
     for _ in range(args.steps):
         ctx = step()
     e1.record()
     barrier()
-    launches = _native.launch_count() - n0
-    ms_total = e0.elapsed_time(e1)
+    ms_stage_pass = e0.elapsed_time(e1) / args.steps
     _native.stage_timing_enable(False)
     stages = _native.stage_timing_read()
-    clocks = sampler.result()
-    if world > 1:
-        tt = torch.tensor([ms_total], device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_total = float(tt.item())
-    ms_step = ms_total / args.steps
-    value = world * 1e3 / ms_step
 
     # ---- counts for the algorithmic cost model (outside the timed region) ----
-    st = last_forward_stats(dev)
-    ev, bl, ev_ours, warp_iters = blend_pair_counts(ctx)
     gx, gy = (W + 15) // 16, (H + 15) // 16
-    if sharded:
-        st["num_visible"] = int((ctx.radii > 0).sum().item())
-    counts = dict(P=P, P_visible=st["num_visible"], R=st["num_rendered"], tiles=gx * gy, pairs_evaluated=ev,
+    L_views = sr.L if sharded else 1
+    if sharded:   # sums over this rank's views of the step
+        cts = sr._state[0]
+        pc = [blend_pair_counts(c) for c in cts]
+        ev, bl, ev_ours, warp_iters = (sum(x[i] for x in pc) for i in range(4))
+        nvis = sum(int((c.radii > 0).sum().item()) for c in cts)
+        nren = sum(int(c.num_rendered) for c in cts)
+        ncontrib = sum(int(c.array("n_contrib").long().sum().item()) for c in cts)
+        per_view_R = [int(c.num_rendered) for c in cts]
+    else:
+        st = last_forward_stats(dev)
+        ev, bl, ev_ours, warp_iters = blend_pair_counts(ctx)
+        nvis, nren = st["num_visible"], st["num_rendered"]
+        ncontrib = int(ctx.array("n_contrib").long().sum().item())
+        per_view_R = [int(nren)]
+    # per RANK and step: this rank preprocesses its slice under all V views and renders L views of all P Gaussians
+    counts = dict(P=P * L_views, P_visible=nvis, R=nren, tiles=gx * gy * L_views, pairs_evaluated=ev,
                   pairs_blended=bl, pairs_evaluated_after_culling=ev_ours, warp_splat_iterations=warp_iters,
-                  sum_n_contrib=int(ctx.array("n_contrib").long().sum().item()))
+                  sum_n_contrib=ncontrib, views_rendered_by_this_rank=L_views, instances_per_view=per_view_R)
     stage_ms = {k: v[0] / max(args.steps, 1) for k, v in stages.items() if v[1]}   # per step (a stage may launch N times)
     peaks = load_peaks()
     roofs = stage_rooflines(stage_ms, counts, peaks, clocks)
-    traffic = load_traffic()
+    traffic = load_traffic() if (P, V, W, H) == (3_000_000, 1, 1920, 1080) else {}
     for k, r in roofs.items():
         r["traffic"] = traffic.get(k)
     dominant = max(stage_ms, key=stage_ms.get)
     per_rank = None
-    if world > 1:   # which rank sets the pace: each rank renders a different view (different R, different blend cost)
-        mine = dict(rank=rank, num_rendered=int(counts["R"]), stage_ms_sum=round(sum(stage_ms.values()), 4),
+    if world > 1:   # which rank sets the pace: the ranks render different views (different R, different blend cost)
+        mine = dict(rank=rank, views=(sr.local_views() if sharded else [rank]), num_rendered=per_view_R,
+                    stage_ms_sum=round(sum(stage_ms.values()), 4),
                     blend_ms=round(stage_ms.get("blend_forward", 0.0) + stage_ms.get("blend_backward", 0.0), 4))
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
         per_rank = gathered
 
-    # ---- e2e: the public autograd API with host-side per-step inputs ----
-    e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer,
-                  sharded=(sr, slices, rank, cam_host_all) if sharded else None)
+    # ---- e2e: the public API with host-side per-step inputs ----
+    e2e = run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer, V,
+                  sharded=(sr, slices, rank) if sharded else None)
     e2e_hp = run_e2e_host_params(args, torch, world, dev, host, rs, dL, rasterize_forward, rasterize_backward,
-                                 arena) if world == 1 else None
+                                 arena) if (world == 1 and not sharded) else None
 
+    exchange = None
+    if sharded:
+        remote = (world - 1) / world
+        exchange = {"transport": sr.exchange, "forward_bytes_per_gaussian_view": 52, "backward_bytes_per_gaussian_view": 48,
+                    "nvlink_bytes_per_rank_step": int((52 + 48) * (P / world) * V * remote),
+                    "note": "rows written straight into / accumulators read straight from the rendering rank's workspace by the "
+                            "per-Gaussian kernels (peer memory); each rank owns 1/N of the parameters and gradients"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "warmup": warmup, "ms_per_step": ms_step, "ms_per_step_median": ms_median, "ms_per_step_p90": ms_p90,
+        "ms_per_view": ms_step / V, "higher_is_better": True,
+        "scaling": "weak" if (args.views is None and world == 1) or V == world else "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{P} Gaussians SH{D} {W}x{H} fwd+bwd, 1 view per GPU per step"
-                               + (f", Gaussian-sharded ({sr.exchange} exchange): all-to-all of 52 B (fwd) + 48 B (bwd) per Gaussian and view, "
-                                  "gradients of each rank's parameter slice summed over the views" if sharded else
-                                  ", + NCCL all-reduce of 59 f32/Gaussian gradients" if world > 1 else ""),
-                   "baseline_config": "BASELINE.json configs[2]", "l2": "inputs (708 MB) larger than L2, no flush",
-                   "parallelism": f"views x{world}", "counts": counts},
+        "config": {"workload": workload_text(P, D, W, H, V), "baseline_config": baseline_config(P, V, W, H),
+                   "l2": f"inputs ({236 * P / 1e6:.0f} MB) larger than L2, no flush",
+                   "parallelism": (f"{V} views over {world} GPU(s), Gaussian-sharded" if sharded else
+                                   f"views x{world}" + (" + NCCL all-reduce of 59 f32/Gaussian gradients" if world > 1 else "")),
+                   "exchange": exchange, "counts": counts,
+                   "timing": "value: K steps with per-stage timing OFF; stages: a second pass of K steps with the "
+                             "library's event pairs on (stage_pass_ms_per_step)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofs.get(dominant),
         "dominant_stage": dominant,
         "stages": roofs,
         "stage_ms_sum": sum(stage_ms.values()),
+        "stage_pass_ms_per_step": ms_stage_pass,
         "e2e": e2e,
     }
     if e2e_hp is not None:
         line["e2e_host_params"] = e2e_hp
     if per_rank is not None:
         line["per_rank"] = per_rank
-    if world == 1 and not args.no_extras:
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        try:
+            import probe_reference_cuda
+            line["reference_cuda"] = probe_reference_cuda.summary()
+        except Exception as e:   # the probe must never break the bench line
+            line["reference_cuda"] = f"probe failed: {e}"
+    if world == 1 and not multi and not args.no_extras:
+        line["multi_view_batch"] = run_multi_view_batch(torch, dev, D, W, H, min(args.steps, 5))
+        line["forward_only"] = run_forward_only_extra(torch, dev, min(args.steps, 10), not args.no_cpu_baseline)
         line["raw_entry"] = run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer)
         line["optimizer_step"] = run_optimizer_compare(torch, dev, t)
         line["loss_step"] = run_loss_compare(torch, dev, W, H)
         line["ply_io"] = run_ply_io(torch, dev, t)
         line["train_iteration"] = run_train_iteration_compare(torch, dev, t, rs, W, H, GaussianRasterizer)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(g, bench_camera(0, W, H), D, dL_np)
+        line["cpu_baseline"] = cpu_baseline(g, cam_list[0], D, dL_np)
+        line["cpu_baseline_2d"] = cpu_baseline_2d()
     if rank == 0:
         _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_multi_view_batch(torch, dev, D, W, H, steps, P=6_000_000, V=8):
+    """BASELINE.json configs[3] on ONE GPU — the single-GPU point of the multi-GPU scaling curve: the same
+    Gaussian-sharded step with world 1 ("local" transport): the multi-view per-Gaussian kernels read the 6 M
+    parameters once for the 8 views, every view is binned / blended in turn, gradients are summed over the
+    batch inside preprocess_backward.  Device-timed, K steps after 3 warm-up steps."""
+    from mvs_gaussian_splatting_b200 import GaussianRasterizationSettings
+    from mvs_gaussian_splatting_b200.sharded import ShardedViewRasterizer
+    M = 16
+    g = S.make_gaussians(P, S.front_camera(W, H), sh_coeffs=M, seed=0)
+    t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
+    cams = []
+    for c in S.batch_cameras(V, W, H):
+        kw = S.settings_kwargs(c, [0.0, 0.0, 0.0], D)
+        for k in ("bg", "viewmatrix", "projmatrix", "campos"):
+            kw[k] = torch.from_numpy(np.ascontiguousarray(kw[k])).to(dev)
+        cams.append(GaussianRasterizationSettings(**kw))
+    sr = ShardedViewRasterizer(P, M, W, H, dev, n_views=V)
+    gen = torch.Generator(device="cpu").manual_seed(1234)
+    dL = torch.randn(3, H, W, generator=gen).to(dev).unsqueeze(0).expand(V, 3, H, W).contiguous()
+    for _ in range(3):
+        sr.forward(t, cams)
+        sr.backward(dL)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        sr.forward(t, cams)
+        sr.backward(dL)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    out = {"value": V * 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "ms_per_view": ms / V, "steps": steps, "n_gpus": 1,
+           "workload": workload_text(P, D, W, H, V), "baseline_config": baseline_config(P, V, W, H),
+           "instances_per_view": [int(c.num_rendered) for c in sr._state[0]],
+           "note": "the N = 1 point of the configs[3] scaling curve: bench.py --gpus N (N > 1) runs this same batch "
+                   "split over N GPUs; efficiency(N) = value(N) / (N x this value)"}
+    del sr, t
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_forward_only_extra(torch, dev, steps, with_cpu):
+    """BASELINE.json configs[4] inside the default line (so the driver records it): forward-only render of 6 M
+    Gaussians at 3840x2160, SH degree 3 and the SH-degree-0 variant, frames/s device-timed; plus the CPU oracle's
+    forward-only time on the host cores (bounded sample of tile rows)."""
+    from mvs_gaussian_splatting_b200 import GaussianRasterizationSettings, last_forward_stats, rasterize_forward
+    P, W, H = 6_000_000, 3840, 2160
+    cam = S.front_camera(W, H)
+    g = S.make_gaussians(P, cam, sh_coeffs=16, seed=0)
+    out = {"workload": f"{P} Gaussians {W}x{H} forward only (render.py path)", "baseline_config": "BASELINE.json configs[4]"}
+    t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
+    for name, Dv in (("sh3", 3), ("sh0", 0)):
+        kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], Dv)
+        for k in ("bg", "viewmatrix", "projmatrix", "campos"):
+            kw[k] = torch.from_numpy(np.ascontiguousarray(kw[k])).to(dev)
+        rs = GaussianRasterizationSettings(**kw)
+        shs = t["shs"] if Dv else t["shs"][:, :1].contiguous()     # quantize.py's variant passes [P,1,3]
+        frame = lambda: rasterize_forward(t["means3D"], shs, None, t["opacities"], t["scales"], t["rotations"], None, rs)
+        for _ in range(3):
+            frame()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            frame()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        st = last_forward_stats(dev)
+        out[name] = {"value": 1e3 / ms, "unit": "frames/s", "ms_per_frame": ms, "steps": steps,
+                     "P_visible": st["num_visible"], "R": st["num_rendered"], "sh_coeffs": int(shs.shape[1])}
+    del t
+    torch.cuda.empty_cache()
+    if with_cpu:
+        th = host_threads()
+        arm = CpuArm(g, cam, 3, None, th)
+        out["cpu_baseline"] = arm.forward_only(budget_s=12.0)
+    return out
+
+
+def cpu_baseline_2d():
+    """north_star's CPU baseline: the reference's pure-PyTorch dense 2-D splat compositing
+    (2D-Gaussian-Splatting-main/2d_gaussian_splatting.py:44-123, restated in oracle/dense_splat_2d.py) timed on the
+    host cores in this same run: its own configuration (config.yml: 1000 Gaussians, 256x256, kernel 101) and a
+    scaled slice at 1920x1080.  A different function from the 3-D rasterizer (additive, unsorted): a throughput
+    baseline in ns per splat*pixel, nothing more."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import dense_splat_2d
+    th = host_threads()
+    a = dense_splat_2d.time_dense_splat_2d(1000, 256, 256, reps=1, threads=th)
+    b = dense_splat_2d.time_dense_splat_2d(16, 1080, 1920, reps=1, threads=th)
+    # what a dense pass over configs[2]'s visible splats would cost at that rate (it is O(N x pixels))
+    est = b["fwd_bwd_ns_per_splat_pixel"] * 1e-9 * 2_285_341 * 1920 * 1080
+    return {"kind": "reference-restated", "cores": th, "config1": a, "slice_1080p": b,
+            "extrapolated_fwd_bwd_s_per_view_config2": est,
+            "note": "dense compositing touches every pixel for every splat; the extrapolation multiplies the measured "
+                    "1080p rate by configs[2]'s 2.29 M visible splats (labelled extrapolated, SURVEY 8d)"}
 
 
 def cpu_baseline(g, cam, D, dL_np, budget_s=30.0):
@@ -449,24 +688,28 @@ def cpu_baseline(g, cam, D, dL_np, budget_s=30.0):
         stride += 1
     ts = [arm.step(stride)["t_view_s"] for _ in range(2)]
     t = float(np.mean(ts))
-    return {"value": 1.0 / t, "unit": UNIT, "cores": th, "kind": "port", "sample": arm.describe(stride),
-            "ms_per_view": 1e3 * t}
+    return {"value": 1.0 / t, "unit": UNIT, "cores": th, "kind": "port" if stride == 1 else "port-extrapolated",
+            "sample": arm.describe(stride), "ms_per_view": 1e3 * t}
 
 
-def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer, sharded=None):
+def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, GaussianRasterizer, V, sharded=None):
     """The call a user of the reference makes (gaussian_renderer/__init__.py:257-265 + train.py:95-113):
-    per step the camera block and the ground-truth image come from PINNED HOST memory, the image is
-    rendered through GaussianRasterizer (autograd), an L1 loss is formed, backward() runs, and the
-    loss is read back to the host.  The Gaussian parameters are model state and stay in HBM, as in
-    the reference's training loop."""
+    per step the camera blocks of the batch and the ground-truth images of the views this rank renders come from
+    PINNED HOST memory, the images are rendered through the public API (GaussianRasterizer under autograd at one
+    view per step; ShardedViewRasterizer for a batch), an L1 loss is formed per view, backward runs, and the loss
+    is read back to the host.  The Gaussian parameters are model state and stay in HBM, as in the reference's
+    training loop."""
     from mvs_gaussian_splatting_b200.loss import l1_loss
     H, W = args.height, args.width
-    gt_host = torch.from_numpy((0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)).pin_memory()
-    params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    params = sr = slices = None
+    L = 1
     if sharded is not None:
-        # Gaussian-sharded step: the host block carries the cameras of ALL N views of the step (38 floats each)
-        sr, slices, my_rank, cam_host = sharded
-        params = None
+        sr, slices, my_rank = sharded
+        L = sr.L
+    else:
+        params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
+    gt1 = (0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)
+    gt_host = torch.from_numpy(np.ascontiguousarray(np.broadcast_to(gt1, (L, 3, H, W)))).pin_memory()
 
     # Per-step host inputs are prefetched one step ahead on a copy stream (double-buffered), as a data
     # loader does; the loss is copied to pinned memory asynchronously and read one step late, so the
@@ -474,10 +717,12 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     copy_stream = torch.cuda.Stream(device=dev)
     main = torch.cuda.current_stream(dev)
     slots = [dict(block=torch.empty_like(cam_host, device=dev), gt=torch.empty_like(gt_host, device=dev),
-                  ready=torch.cuda.Event(), free=torch.cuda.Event(), loss=torch.zeros(1).pin_memory(),
+                  ready=torch.cuda.Event(), free=torch.cuda.Event(), loss=torch.zeros(L).pin_memory(),
                   loss_ready=torch.cuda.Event()) for _ in range(2)]
     for sl in slots:
         sl["free"].record(main)
+        # the settings NamedTuples are views of the slot's device block: built once per slot, refreshed by the copy
+        sl["cams"] = [settings_from(sl["block"][38 * v:38 * v + 38], v) for v in range(V)]
     state = {"k": 0, "pending": None}
 
     def prefetch(sl):
@@ -493,25 +738,25 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         sl = slots[state["k"] & 1]
         prefetch(slots[(state["k"] + 1) & 1])           # next step's inputs travel while this step computes
         main.wait_event(sl["ready"])
-        if sharded is not None:
-            cams = [settings_from(sl["block"][38 * v:38 * v + 38]) for v in range(world)]
-            color, radii = sr.forward(slices, cams)
-            color.requires_grad_(True)
-            loss = l1_loss(color, sl["gt"])                   # library loss (loss.py): one launch each way
-            loss.backward()
-            sr.backward(color.grad)
+        if sr is not None:
+            colors, radii = sr.forward(slices, sl["cams"])
+            colors.requires_grad_(True)
+            losses = [l1_loss(colors[l], sl["gt"][l]) for l in range(L)]   # library loss (loss.py): one launch each way
+            loss = torch.stack(losses)
+            loss.sum().backward()
+            sr.backward(colors.grad)
         else:
-            rs = settings_from(sl["block"])
+            rs = sl["cams"][int(os.environ.get("RANK", "0")) % V]
             means2D = torch.zeros_like(params["means3D"], requires_grad=True)
             color, radii = GaussianRasterizer(rs)(means3D=params["means3D"], means2D=means2D, shs=params["shs"],
                                                   opacities=params["opacities"], scales=params["scales"],
                                                   rotations=params["rotations"])
-            loss = l1_loss(color, sl["gt"])
+            loss = l1_loss(color, sl["gt"][0])
             loss.backward()
             if world > 1:
                 for p in params.values():
                     dist.all_reduce(p.grad)
-        sl["loss"].copy_(loss.detach().reshape(1), non_blocking=True)   # D2H read of the step's result
+        sl["loss"].copy_(loss.detach().reshape(L), non_blocking=True)   # D2H read of the step's result
         sl["loss_ready"].record(main)
         sl["free"].record(main)
         val = None
@@ -525,15 +770,15 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
                 p.grad = None                               # train.py:142 zero_grad(set_to_none=True)
         return val
 
-    for _ in range(5):
+    for _ in range(5 if world == 1 else 20):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     n = max(30, args.steps)   # wall-clock: enough steps that one host hiccup does not move the figure
     prof = None
-    if os.environ.get("GSR_E2E_PROFILE"):   # where the host time of an e2e step goes (stderr; perturbs the figure)
-        import cProfile
+    if os.environ.get("GSR_E2E_PROFILE") and int(os.environ.get("RANK", "0")) == 0:
+        import cProfile                                   # where the host time of an e2e step goes (stderr; perturbs the figure)
         prof = cProfile.Profile()
         prof.enable()
     t0 = time.perf_counter()
@@ -544,17 +789,19 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     if prof is not None:
         import pstats
         prof.disable()
-        pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(14)
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(16)
     if world > 1:
         tt = torch.tensor([dt], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-    return {"value": world * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
-            "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4,
-            "api": "GaussianRasterizer(settings)(...) + l1_loss (mvs_gaussian_splatting_b200.loss) + backward(), camera + ground-truth image from "
-                   "pinned host memory (prefetched one step ahead on a copy stream), loss copied back to pinned "
-                   "memory every step; Gaussian parameters resident in HBM (model state)"
-                   + ("; N > 1: ShardedViewRasterizer.forward/backward on each rank's parameter slice" if sharded else "")}
+    return {"value": V * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
+            "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4 * L,
+            "api": ("ShardedViewRasterizer.forward / .backward on this rank's parameter slice" if sr is not None else
+                    "GaussianRasterizer(settings)(...) under autograd") +
+                   " + l1_loss (mvs_gaussian_splatting_b200.loss) per rendered view + backward; the batch's camera blocks and "
+                   "this rank's ground-truth images come from pinned host memory every step (prefetched one step ahead on a "
+                   "copy stream), the losses are copied back to pinned memory every step; Gaussian parameters resident in "
+                   "HBM (model state)"}
 
 
 def run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer):
@@ -864,9 +1111,10 @@ def run_forward_only(args):
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
     _native.lib()
-    W, H, P, D = args.width, args.height, args.points, args.sh_degree
+    W, H, D = args.width, args.height, args.sh_degree
+    P = args.points if args.points is not None else 6_000_000
     M = (D + 1) ** 2 if D == 0 else 16
-    cam = bench_camera(0, W, H)
+    cam = S.front_camera(W, H)
     g = S.make_gaussians(P, cam, sh_coeffs=M, seed=0)
     t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
     kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], D)

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 7
+#define GSR_ABI_VERSION 8
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -307,7 +307,15 @@ typedef struct gsr_view_slot {
     void* geom_ws;             /* P_ws-row geometry workspace of this view (may be a peer GPU's) */
     int32_t* radii_slots;      /* radii rows [slot_offset, slot_offset + Ps) of this view */
     float* dL_dmeans2D;        /* backward only: [Ps,3] of this view, always overwritten */
+    /* Optional LOCAL copies (both or neither; [Ps] rows, private to the slice owner) of what the forward produced
+     * for this view: the packed word  radius | clamped_bits << 28  and the conic + opacity.  gsr_preprocess_views
+     * writes them; gsr_preprocess_backward_views then reads THEM instead of radii_slots / conic_opacity / rgb of
+     * geom_ws, so that only the 48-byte blend accumulators are fetched from a peer's workspace.  The radii of
+     * the densification statistics (train.py:130) are  word & GSR_LOCAL_RADIUS_MASK. */
+    int32_t* radii_local;
+    float* conic_local;        /* [Ps,4] */
 } gsr_view_slot;
+#define GSR_LOCAL_RADIUS_MASK 0x0FFFFFFF
 
 GSR_API int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int width, int height,
                          const float* means3D, const float* shs, const float* colors_precomp,

@@ -9,6 +9,7 @@ of the reference's rasterizer dependency (imported at
 from __future__ import annotations
 
 import ctypes
+import functools
 import os
 import subprocess
 import threading
@@ -17,7 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -54,7 +55,11 @@ class ViewSlot(ctypes.Structure):
     """gsr_view_slot of include/gsrast_b200.h."""
     _fields_ = [("viewmatrix", ctypes.c_void_p), ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p),
                 ("tanfovx", ctypes.c_float), ("tanfovy", ctypes.c_float), ("geom_ws", ctypes.c_void_p),
-                ("radii_slots", ctypes.c_void_p), ("dL_dmeans2D", ctypes.c_void_p)]
+                ("radii_slots", ctypes.c_void_p), ("dL_dmeans2D", ctypes.c_void_p),
+                ("radii_local", ctypes.c_void_p), ("conic_local", ctypes.c_void_p)]
+
+
+LOCAL_RADIUS_MASK = 0x0FFFFFFF   # GSR_LOCAL_RADIUS_MASK
 
 
 class AdamGroup(ctypes.Structure):
@@ -238,6 +243,7 @@ def check(status: int, where: str) -> None:
         raise GsrError(status, where)
 
 
+@functools.lru_cache(maxsize=256)
 def workspace_bytes(P: int, W: int, H: int, capacity: int):
     g, b, i = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
     check(lib().gsr_workspace_bytes(P, W, H, capacity, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i)),
@@ -245,6 +251,7 @@ def workspace_bytes(P: int, W: int, H: int, capacity: int):
     return g.value, b.value, i.value
 
 
+@functools.lru_cache(maxsize=256)
 def workspace_layout(P: int, W: int, H: int, capacity: int) -> Layout:
     out = Layout()
     check(lib().gsr_workspace_layout(P, W, H, capacity, ctypes.byref(out)), "gsr_workspace_layout")

@@ -534,6 +534,10 @@ int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int wi
         args[v].tanfovx = a.tanfovx; args[v].tanfovy = a.tanfovy;
         args[v].radii = a.radii_slots;
         args[v].gv = offset_rows(geom_view(a.geom_ws, L), (size_t)slot_offset);
+        if ((a.radii_local == nullptr) != (a.conic_local == nullptr) || !aligned16(a.conic_local))
+            return GSR_ERR_INVALID_ARGUMENT;
+        args[v].radii_local = a.radii_local;
+        args[v].conic_local = reinterpret_cast<float4*>(a.conic_local);
     }
     return launch_preprocess_views(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp, opacities, scales,
                                    scale_modifier, rotations, cov3D_precomp, n_views, args,
@@ -572,6 +576,10 @@ int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int 
         args[v].radii = a.radii_slots;
         args[v].gv = offset_rows(geom_view(a.geom_ws, L), (size_t)slot_offset);
         args[v].dL_dmeans2D = a.dL_dmeans2D;
+        if ((a.radii_local == nullptr) != (a.conic_local == nullptr) || !aligned16(a.conic_local))
+            return GSR_ERR_INVALID_ARGUMENT;
+        args[v].radii_local = a.radii_local;
+        args[v].conic_local = reinterpret_cast<const float4*>(a.conic_local);
     }
     return launch_preprocess_backward_views(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp != nullptr,
                                             scales, scale_modifier, rotations, cov3D_precomp, n_views, args, dL_dcolors,

@@ -33,6 +33,8 @@ struct BwdView {
     const float4* conic_opacity;
     const float4* rgb;
     float* dL_dmeans2D;
+    const int32_t* radii_local;   // optional local copies written by the multi-view forward (gsr_view_slot):
+    const float4* conic_local;    // radius | clamped << 28, conic + opacity; read instead of radii / conic_opacity / rgb
 };
 
 struct BwdParams {
@@ -153,8 +155,12 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     const int warp_base = blockIdx.x * kBwdThreads + warp * 32;
     const bool valid = idx < p.P;
     uint32_t visbits = 0;  // bit v: view v sees this Gaussian
-    for (int v = 0; v < p.n_views; ++v)
-        if (valid && p.v[v].radii[idx] > 0) visbits |= 1u << v;
+    for (int v = 0; v < p.n_views; ++v) {
+        if (!valid) break;
+        const int r = (kMulti && p.v[v].radii_local) ? (__ldg(p.v[v].radii_local + idx) & GSR_LOCAL_RADIUS_MASK)
+                                                     : p.v[v].radii[idx];
+        if (r > 0) visbits |= 1u << v;
+    }
     const bool vis_any = visbits != 0;
     const unsigned vmask = __ballot_sync(0xffffffffu, vis_any);
     const bool do_sh = (p.dL_dsh != nullptr) && !p.colors_precomp;
@@ -269,8 +275,13 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
             if (kMulti) {
                 const float4* accp = reinterpret_cast<const float4*>(V.grad_accum + (size_t)idx * 12);
                 a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
-                con = V.conic_opacity[idx];
-                if (do_sh) clamped_bits = __float_as_uint(V.rgb[idx].w);
+                if (V.radii_local) {   // forward rows kept locally: only the accumulators come from the view's owner
+                    con = __ldg(V.conic_local + idx);
+                    clamped_bits = (uint32_t)__ldg(V.radii_local + idx) >> 28;
+                } else {
+                    con = V.conic_opacity[idx];
+                    if (do_sh) clamped_bits = __float_as_uint(V.rgb[idx].w);
+                }
             }
             if (kRaw) opacity = con.w;
             const float S1 = a0.x, S2 = a0.y;
@@ -554,6 +565,7 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
         o.focal_y = (float)g.H / (2.0f * a.tanfovy);
         o.radii = a.radii; o.grad_accum = a.gv.grad_accum; o.conic_opacity = a.gv.conic_opacity; o.rgb = a.gv.rgb;
         o.dL_dmeans2D = a.dL_dmeans2D;
+        o.radii_local = a.radii_local; o.conic_local = a.conic_local;
     }
     StageScope scope(kStagePreprocessBwd, s);
     const unsigned blocks = (unsigned)((P + kBwdThreads - 1) / kBwdThreads);

@@ -174,6 +174,8 @@ struct ForwardViewArgs {
     float tanfovx, tanfovy;
     int32_t* radii;
     GeomView gv;
+    int32_t* radii_local = nullptr;   // optional local copies (gsr_view_slot): radius | clamped << 28, conic + opacity
+    float4* conic_local = nullptr;
 };
 int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                             const float* colors_precomp, const float* opacities, const float* scales,
@@ -189,6 +191,8 @@ struct BackwardViewArgs {
     const int32_t* radii;
     GeomView gv;
     float* dL_dmeans2D;
+    const int32_t* radii_local = nullptr;   // when set: read instead of radii / gv.conic_opacity / gv.rgb
+    const float4* conic_local = nullptr;
 };
 int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                                      int colors_precomp, const float* scales, float scale_modifier,

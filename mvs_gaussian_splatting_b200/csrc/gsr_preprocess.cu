@@ -36,6 +36,8 @@ struct PreView {
     float tanfovx, tanfovy, focal_x, focal_y;
     int32_t* radii;
     GeomView gv;
+    int32_t* radii_local;   // optional local copies for the slice owner's backward (gsr_view_slot)
+    float4* conic_local;
 };
 
 struct PreParams {
@@ -318,12 +320,17 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
         V.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
         // the depth array doubles as the key of the per-Gaussian depth sort: culled rows sink to the end
         V.gv.depths[idx] = alive ? depth : __uint_as_float(0xFFFFFFFFu);
+        float4 conic = make_float4(0.f, 0.f, 0.f, 0.f);
         if (alive) {
             V.gv.means2D[idx] = make_float2(px, py);
-            V.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
-                                                  __fmul_rn(ca, det_inv),
-                                                  kRaw ? act_opacity(__ldg(p.opacities + idx)) : __ldg(p.opacities + idx));
+            conic = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv), __fmul_rn(ca, det_inv),
+                                kRaw ? act_opacity(__ldg(p.opacities + idx)) : __ldg(p.opacities + idx));
+            V.gv.conic_opacity[idx] = conic;
             V.gv.rgb[idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
+        }
+        if (V.radii_local) {   // what the slice owner's backward needs again, kept on this GPU
+            V.radii_local[idx] = alive ? (int32_t)((uint32_t)rad | (clamped << 28)) : 0;
+            if (alive) V.conic_local[idx] = conic;
         }
     }
     if (lane == 0 && vis && V.gv.info) atomicAdd(&V.gv.info->num_visible, __popc(vis));
@@ -388,6 +395,7 @@ int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* mea
         o.focal_x = (float)g.W / (2.0f * a.tanfovx);
         o.focal_y = (float)g.H / (2.0f * a.tanfovy);
         o.radii = a.radii; o.gv = a.gv;
+        o.radii_local = a.radii_local; o.conic_local = a.conic_local;
     }
     const int blocks = (P + kPreThreads - 1) / kPreThreads;
     StageScope scope(kStagePreprocess, s);

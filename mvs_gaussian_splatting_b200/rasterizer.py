@@ -138,7 +138,25 @@ class RasterContext:
         return ws[off:off + nbytes].view(dt).view(shape)
 
 
+_settings_cache: dict = {}    # id(settings) -> (settings, device, dense tensors); a training loop reuses its cameras
+
+
 def _settings_tensors(rs: GaussianRasterizationSettings, device):
+    """(view, proj, campos, bg) as dense float32 device tensors.  Cached per settings OBJECT (the entry keeps the
+    object alive, so an id cannot be recycled): settings are immutable NamedTuples, and when their tensors are
+    already dense the cached entries ARE those tensors — a caller that refreshes a camera block in place is seen."""
+    hit = _settings_cache.get(id(rs))
+    if hit is not None and hit[0] is rs and hit[1] == device:
+        return hit[2]
+    out = _settings_tensors_uncached(rs, device)
+    if all(o is t for o, t in zip(out, (rs.viewmatrix, rs.projmatrix, rs.campos, rs.bg))):   # no copies were made
+        if len(_settings_cache) >= 64:
+            _settings_cache.pop(next(iter(_settings_cache)))
+        _settings_cache[id(rs)] = (rs, device, out)
+    return out
+
+
+def _settings_tensors_uncached(rs: GaussianRasterizationSettings, device):
     view = _dense(rs.viewmatrix, device)
     proj = _dense(rs.projmatrix, device)
     campos = _dense(rs.campos, device)

@@ -1,4 +1,5 @@
-"""Gaussian-sharded multi-view step: N ranks, rank r owns parameter slice r and renders view r.
+"""Gaussian-sharded multi-view step: N ranks, a batch of V views per step (V a multiple of N); rank r owns
+parameter slice r and renders views r, r+N, ... (V = N: one view per rank).
 
 Why.  Replicated-parameter data parallelism (multiview.py) must all-reduce 59 floats = 236 B per
 Gaussian and step; at 3 M Gaussians that is 708 MB against a 2.3 ms step (measured: 1.3 ms at 2
@@ -44,7 +45,7 @@ from . import _native
 from .rasterizer import (GaussianRasterizationSettings, RasterContext, _dense, _pinned_info, _ptr, _render_stage,
                          _settings_tensors)
 
-__all__ = ["ShardPlan", "all_to_all_rows", "ShardedViewRasterizer", "GEOMETRY_ARRAYS"]
+__all__ = ["ShardPlan", "ViewPlan", "all_to_all_rows", "ShardedViewRasterizer", "GEOMETRY_ARRAYS"]
 
 SLICE_ALIGN = 128  # rows; keeps every per-Gaussian array of a slice 16-byte aligned (needs a multiple of 4)
 
@@ -71,6 +72,29 @@ class ShardPlan:
     def slot_stride(self, rank: int) -> int:
         """Row stride between the per-view slots of rank's send workspace."""
         return max(SLICE_ALIGN, -(-self.sizes[rank] // SLICE_ALIGN) * SLICE_ALIGN)
+
+
+class ViewPlan:
+    """Which rank renders which view of a V-view batch ("rank r takes views r, r+n, ..."):
+    view v is rendered by rank v % N as its local view v // N."""
+
+    def __init__(self, n_views: int, world: int):
+        if world < 1 or n_views < 1 or n_views % world:
+            raise ValueError("the number of views per step must be a positive multiple of the world size")
+        self.V, self.world, self.L = n_views, world, n_views // world
+
+    def owner(self, v: int) -> int:
+        return v % self.world
+
+    def local_index(self, v: int) -> int:
+        return v // self.world
+
+    def local_views(self, rank: int) -> List[int]:
+        return [rank + l * self.world for l in range(self.L)]
+
+    def order(self, rank: int) -> List[int]:
+        """All V views starting at the rank's own, so that at any moment the ranks address different peers."""
+        return [(rank + k) % self.V for k in range(self.V)]
 
 
 def all_to_all_rows(pairs: Sequence, group=None) -> None:
@@ -111,74 +135,104 @@ def _ws_arrays(ws: torch.Tensor, L: _native.Layout, P: int) -> Dict[str, torch.T
 
 
 class ShardedViewRasterizer:
-    """One instance per rank.  `forward` takes THIS rank's parameter slice and the N cameras of the
-    step and returns the image and radii of view `rank`; `backward` takes dL/dpixel of that image and
-    returns the parameter gradients of the slice summed over all N views, plus the per-view
-    dL/dmeans2D rows of the slice ([N, Ps, 3], for the densification statistics of
-    scene/gaussian_model.py:775-777).  SH + scale/rotation inputs (the training configuration)."""
+    """One instance per rank.  A step renders a BATCH of V views (V a multiple of the world size N; BASELINE.json
+    configs[3]: 8 views over 2 / 4 / 8 GPUs): rank r owns parameter slice r and renders views r, r+N, r+2N, ...
+    ("rank r takes views r, r+n, ...").  `forward` takes THIS rank's parameter slice and the V cameras
+    and returns the images and radii of the rank's L = V/N views; `backward` takes dL/dpixel of those images and
+    returns the parameter gradients of the slice summed over all V views, plus the per-view dL/dmeans2D rows of
+    the slice ([V, Ps, 3]) that `densification_stats` (train.py:130-131, scene/gaussian_model.py:775-777) consumes
+    together with the per-view radii of the slice.  SH + scale/rotation inputs (the training configuration).
 
-    def __init__(self, P: int, M: int, width: int, height: int, device, group=None, exchange: str = "peer"):
-        if not (dist.is_available() and dist.is_initialized()):
-            raise RuntimeError("torch.distributed must be initialised (one process per GPU)")
+    With one process and no process group (world 1) the same algorithm runs on one GPU with plain local
+    workspaces (exchange "local"): the multi-view kernels read the parameters once for the whole batch — the
+    single-GPU point of the scaling curve."""
+
+    def __init__(self, P: int, M: int, width: int, height: int, device, group=None, exchange: str = "peer",
+                 n_views: Optional[int] = None):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
-        if exchange not in ("peer", "nccl"):
-            raise ValueError("exchange must be 'peer' or 'nccl'")
+        if dist.is_available() and dist.is_initialized():
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        else:
+            self.world, self.rank = 1, 0
+        if self.world == 1:
+            exchange = "local"
+        if exchange not in ("peer", "nccl", "local"):
+            raise ValueError("exchange must be 'peer', 'nccl' or 'local'")
         self.group, self.exchange = group, exchange
-        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        V = self.world if n_views is None else int(n_views)
+        self.views = ViewPlan(V, self.world)
+        self.L = self.views.L
+        self.V = V
         self.P, self.M, self.W, self.H = P, M, width, height
         self.plan = ShardPlan(P, self.world)
         self.Ps = self.plan.sizes[self.rank]
         self.start = self.plan.starts[self.rank]
         self.lib = _native.lib()
-        dev = self.device
+        dev, L = self.device, self.L
         self.L_full = _native.workspace_layout(P, width, height, 0)
         self.geom_bytes, _, self.image_bytes = _native.workspace_bytes(P, width, height, 0)
-        if exchange == "peer":
-            import torch.distributed._symmetric_memory as symm_mem
-            # TWO workspaces, used on alternate steps: the rows a peer stores into my workspace for step k+1 must
-            # not land while any rank still reads step k's.  With one buffer that takes a barrier at the top of
-            # every step; with two, the buffer written in step k+1 was last read in step k-1, and every rank has
-            # passed step k's barriers — which follow its step k-1 reads in stream order — before anyone stores.
-            self.radii_off = (self.geom_bytes + 255) // 256 * 256
-            self.half = (self.radii_off + 4 * max(P, 1) + 255) // 256 * 256
-            self.symm = symm_mem.empty(2 * self.half, dtype=torch.uint8, device=dev)
-            self.hdl = symm_mem.rendezvous(self.symm, group if group is not None else dist.group.WORLD)
-            self.peer_base = [int(x) for x in self.hdl.buffer_ptrs]
+        self.radii_off = (self.geom_bytes + 255) // 256 * 256
+        self.half = (self.radii_off + 4 * max(P, 1) + 255) // 256 * 256      # one view: geometry workspace + radii
+        if exchange in ("peer", "local"):
+            # 2 x L view workspaces, the two sets used on alternate steps: the rows a peer stores into my workspace
+            # for step k+1 must not land while any rank still reads step k's.  With one set that takes a barrier at
+            # the top of every step; with two, the set written in step k+1 was last read in step k-1, and every rank
+            # has passed step k's barriers — which follow its step k-1 reads in stream order — before anyone stores.
+            nbuf = 2 if exchange == "peer" else 1
+            if exchange == "peer":
+                import torch.distributed._symmetric_memory as symm_mem
+                self.symm = symm_mem.empty(nbuf * L * self.half, dtype=torch.uint8, device=dev)
+                self.hdl = symm_mem.rendezvous(self.symm, group if group is not None else dist.group.WORLD)
+                self.peer_base = [int(x) for x in self.hdl.buffer_ptrs]
+            else:
+                self.symm = torch.empty(nbuf * L * self.half, dtype=torch.uint8, device=dev)
+                self.hdl, self.peer_base = None, [self.symm.data_ptr()]
             self._bufs = []
-            for b in (0, self.half):
-                ws = self.symm[b:b + self.geom_bytes]
-                self._bufs.append((ws, self.symm[b + self.radii_off:b + self.radii_off + 4 * P].view(torch.int32),
-                                   _ws_arrays(ws, self.L_full, P)))
-            self.parity = 1
-            self.geom_ws, self.radii_ws, self.full = self._bufs[self.parity]
+            for b in range(nbuf):
+                views = []
+                for l in range(L):
+                    o = (b * L + l) * self.half
+                    ws = self.symm[o:o + self.geom_bytes]
+                    views.append((ws, self.symm[o + self.radii_off:o + self.radii_off + 4 * P].view(torch.int32),
+                                  _ws_arrays(ws, self.L_full, P)))
+                self._bufs.append(views)
+            self.nbuf, self.parity = nbuf, nbuf - 1
         else:
             self.stride = self.plan.slot_stride(self.rank)
-            self.P_send = self.world * self.stride
+            self.P_send = V * self.stride
             gb_send, _, _ = _native.workspace_bytes(self.P_send, width, height, 0)
             self.send_ws = torch.empty(gb_send, dtype=torch.uint8, device=dev)
             self.send_radii = torch.zeros(self.P_send, dtype=torch.int32, device=dev)
             self.send = _ws_arrays(self.send_ws, _native.workspace_layout(self.P_send, width, height, 0), self.P_send)
-            self.geom_ws = torch.empty(self.geom_bytes, dtype=torch.uint8, device=dev)
-            self.radii_ws = torch.empty(P, dtype=torch.int32, device=dev)
-            self.full = _ws_arrays(self.geom_ws, self.L_full, P)
-        # parameter gradients of the slice (summed over views) and per-view dL/dmeans2D
+            views = []
+            for l in range(L):
+                ws = torch.empty(self.geom_bytes, dtype=torch.uint8, device=dev)
+                views.append((ws, torch.empty(P, dtype=torch.int32, device=dev), _ws_arrays(ws, self.L_full, P)))
+            self._bufs, self.nbuf, self.parity = [views], 1, 0
+        # parameter gradients of the slice (summed over views), per-view dL/dmeans2D, and the slice owner's local
+        # copies of the forward rows its backward needs again (gsr_view_slot.radii_local / conic_local)
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         Ps = max(self.Ps, 1)
         self.grads = dict(means3D=f(Ps, 3), shs=f(Ps, M, 3), opacities=f(Ps, 1), scales=f(Ps, 3), rotations=f(Ps, 4))
-        self.grad_means2D = f(self.world, Ps, 3)
+        self.grad_means2D = f(V, Ps, 3)
+        self.radii_local = torch.zeros((V, Ps), dtype=torch.int32, device=dev)
+        self.conic_local = f(V, Ps, 4)
         self._state = None
 
     # ------------------------------------------------------------------------------------------
+    def local_views(self) -> List[int]:
+        """Global indices of the views this rank renders, in the order `forward` returns them."""
+        return self.views.local_views(self.rank)
+
     def _slot(self, v: int) -> slice:
         return slice(v * self.stride, v * self.stride + self.Ps)
 
     def _view_order(self):
-        """Views starting at the rank's own, so that at any moment the ranks address different peers."""
-        return [(self.rank + k) % self.world for k in range(self.world)]
+        return self.views.order(self.rank)
 
-    def _view_slots(self, chunk, cams, cameras, scal):
+    def _view_slots(self, chunk, cams, tanfov):
         """gsr_view_slot array for the views of `chunk` (+ the workspace row count and first row, which
         are the same for every view of a transport)."""
         arr = (_native.ViewSlot * len(chunk))()
@@ -186,27 +240,32 @@ class ShardedViewRasterizer:
         for n, v in enumerate(chunk):
             view, proj, campos, _ = cams[v]
             ws_ptr, P_ws, row0, radii_ptr = self._target(v)
-            tfx, tfy = (float(cameras[v].tanfovx), float(cameras[v].tanfovy)) if cameras is not None else scal[v][1:]
-            arr[n] = _native.ViewSlot(view.data_ptr(), proj.data_ptr(), campos.data_ptr(), tfx, tfy, ws_ptr.value,
-                                      radii_ptr.value, self.grad_means2D[v].data_ptr())
+            arr[n] = _native.ViewSlot(view.data_ptr(), proj.data_ptr(), campos.data_ptr(), tanfov[v][0], tanfov[v][1],
+                                      ws_ptr, radii_ptr, self.grad_means2D[v].data_ptr(),
+                                      self.radii_local[v].data_ptr(), self.conic_local[v].data_ptr())
         return arr, P_ws, row0
 
     def _target(self, v: int):
-        """(geom_ws pointer, rows in it, first row, radii pointer) a slot call for view v addresses."""
-        if self.exchange == "peer":
-            base = self.peer_base[v] + self.parity * self.half
-            return (ctypes.c_void_p(base), self.P, self.start,
-                    ctypes.c_void_p(base + self.radii_off + 4 * self.start))
-        return (_ptr(self.send_ws), self.P_send, v * self.stride,
-                ctypes.c_void_p(self.send_radii.data_ptr() + 4 * v * self.stride))
+        """(geom_ws address, rows in it, first row, radii address) a slot call for view v addresses: the workspace
+        of the rank that renders v (rank v % N, its local view v // N), or this rank's staging slot."""
+        if self.exchange in ("peer", "local"):
+            base = self.peer_base[self.views.owner(v)] + (self.parity * self.L + self.views.local_index(v)) * self.half
+            return base, self.P, self.start, base + self.radii_off + 4 * self.start
+        return (self.send_ws.data_ptr(), self.P_send, v * self.stride,
+                self.send_radii.data_ptr() + 4 * v * self.stride)
+
+    def _camera_tensors(self, cameras):
+        """(view, proj, campos, bg) device tensors per camera."""
+        return [_settings_tensors(c, self.device) for c in cameras]   # cached per settings object (rasterizer.py)
 
     def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
         """params: means3D [Ps,3], shs [Ps,M,3], opacities [Ps,1], scales [Ps,3], rotations [Ps,4] of
-        slice `rank` (ShardPlan.rows).  cameras[v]: settings of view v (same image size, sh_degree,
-        scale_modifier on every rank).  Returns (color [3,H,W], radii [P] int32 of view `rank`)."""
-        N, r, dev, L = self.world, self.rank, self.device, self.lib
-        if len(cameras) != N:
-            raise ValueError("one camera per rank required")
+        slice `rank` (ShardPlan.rows).  cameras[v]: settings of view v, v = 0..V-1 (same image size, sh_degree,
+        scale_modifier on every rank).  Returns (color [L,3,H,W], radii [L,P] int32) of views `local_views()`."""
+        N, r, dev, lib = self.world, self.rank, self.device, self.lib
+        V, L = self.V, self.L
+        if len(cameras) != V:
+            raise ValueError(f"{V} cameras per step required ({L} per rank)")
         P, Ps, W, H, M = self.P, self.Ps, self.W, self.H, self.M
         rs = cameras[r]
         if int(rs.image_width) != W or int(rs.image_height) != H:
@@ -216,76 +275,110 @@ class ShardedViewRasterizer:
             raise ValueError("parameter slice does not match ShardPlan.rows(rank)")
         debug = 1 if rs.debug else 0
         D = int(rs.sh_degree)
-        cams = [_settings_tensors(c, dev) for c in cameras]   # (view, proj, campos, bg) per view
+        cams = self._camera_tensors(cameras)   # (view, proj, campos, bg) per view
+        tanfov = [(float(c.tanfovx), float(c.tanfovy)) for c in cameras]
         dev_idx = dev.index if dev.index is not None else torch.cuda.current_device()
-        ctx = RasterContext()
-        ctx.P, ctx.D, ctx.M, ctx.W, ctx.H, ctx.reruns = P, D, M, W, H, 0
-        peer = self.exchange == "peer"
+        staged = self.exchange == "nccl"
         with torch.cuda.device(dev):
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            ctx.geom_ws = self.geom_ws
-            ctx.image_ws = torch.empty(self.image_bytes, dtype=torch.uint8, device=dev)
-            color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
-            if peer:   # no barrier here: this step's rows go to the workspace last read two steps ago (see __init__)
-                self.parity ^= 1
-                self.geom_ws, self.radii_ws, self.full = self._bufs[self.parity]
-                ctx.geom_ws = self.geom_ws
+            # no barrier here: this step's rows go to the workspace set last read two steps ago (see __init__)
+            self.parity = (self.parity + 1) % self.nbuf
+            bufs = self._bufs[self.parity]
             order = self._view_order()
-            step = _native.MAX_VIEWS if peer else 1   # staged (nccl) slots sit at different rows: one view per call
-            for c0 in range(0, N, step):
+            step = 1 if staged else _native.MAX_VIEWS   # staged slots sit at different rows: one view per call
+            for c0 in range(0, V, step):
                 chunk = order[c0:c0 + step]
-                slots, P_ws, row0 = self._view_slots(chunk, cams, cameras, None)
-                _native.check(L.gsr_preprocess_views(
+                slots, P_ws, row0 = self._view_slots(chunk, cams, tanfov)
+                _native.check(lib.gsr_preprocess_views(
                     P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["opacities"]),
                     _ptr(p["scales"]), float(rs.scale_modifier), _ptr(p["rotations"]), None, len(chunk), slots,
                     stream, debug), "gsr_preprocess_views")
-            if peer:
-                self.hdl.barrier(channel=1)   # all slices of this rank's view have landed
-            else:
-                pairs = [([self.send[name][self._slot(v)] for v in range(N)],
-                          [self.full[name][self.plan.rows(j)] for j in range(N)]) for name in GEOMETRY_ARRAYS]
-                pairs.append(([self.send_radii[self._slot(v)] for v in range(N)],
-                              [self.radii_ws[self.plan.rows(j)] for j in range(N)]))
+            if self.exchange == "peer":
+                self.hdl.barrier(channel=1)   # all slices of this rank's views have landed
+            elif staged:
+                pairs = []
+                for l in range(L):
+                    full, radii_ws = bufs[l][2], bufs[l][1]
+                    for name in GEOMETRY_ARRAYS:
+                        pairs.append(([self.send[name][self._slot(j + l * N)] for j in range(N)],
+                                      [full[name][self.plan.rows(j)] for j in range(N)]))
+                    pairs.append(([self.send_radii[self._slot(j + l * N)] for j in range(N)],
+                                  [radii_ws[self.plan.rows(j)] for j in range(N)]))
                 all_to_all_rows(pairs, self.group)
             info = _pinned_info(dev_idx)
-            _native.check(L.gsr_depth_order(P, W, H, _ptr(ctx.geom_ws), ctypes.c_void_p(info.data_ptr()), stream,
-                                            debug), "gsr_depth_order")
-            _render_stage(L, ctx, P, W, H, cams[r][3], self.radii_ws, color, info, None, dev, dev_idx, stream, debug)
-            radii = self.radii_ws.clone()     # the workspace copy is overwritten by the next step
-        self._state = (ctx, p, cams, [(float(c.scale_modifier), float(c.tanfovx), float(c.tanfovy)) for c in cameras],
-                       D, debug)
-        return color, radii
+            ctxs, colors = [], torch.empty((L, 3, H, W), dtype=torch.float32, device=dev)
+            for l in range(L):
+                v = r + l * N
+                ctx = RasterContext()
+                ctx.P, ctx.D, ctx.M, ctx.W, ctx.H, ctx.reruns = P, D, M, W, H, 0
+                ctx.geom_ws = bufs[l][0]
+                ctx.image_ws = torch.empty(self.image_bytes, dtype=torch.uint8, device=dev)
+                _native.check(lib.gsr_depth_order(P, W, H, _ptr(ctx.geom_ws), ctypes.c_void_p(info.data_ptr()), stream,
+                                                  debug), "gsr_depth_order")
+                _render_stage(lib, ctx, P, W, H, cams[v][3], bufs[l][1], colors[l], info, None, dev, dev_idx, stream,
+                              debug)
+                ctxs.append(ctx)
+            # the workspace copies are overwritten two steps later: hand out stable radii
+            radii = torch.stack([bufs[l][1] for l in range(L)]) if L > 1 else bufs[0][1].clone().unsqueeze(0)
+        self._state = (ctxs, p, cams, tanfov, float(rs.scale_modifier), D, debug)
+        return colors, radii
 
     def backward(self, dL_dpix: torch.Tensor):
-        """Returns (grads, grad_means2D): grads[name] = dL/d(parameter rows of this slice) summed over
-        the N views (buffers owned by this object, overwritten by the next call); grad_means2D [N,Ps,3]."""
+        """dL_dpix: [L,3,H,W] (or [3,H,W] when L == 1).  Returns (grads, grad_means2D): grads[name] =
+        dL/d(parameter rows of this slice) summed over the V views (buffers owned by this object, overwritten by
+        the next call); grad_means2D [V,Ps,3], one block per view."""
         if self._state is None:
             raise RuntimeError("backward() needs a preceding forward()")
-        ctx, p, cams, scal, D, debug = self._state
-        N, r, dev, L = self.world, self.rank, self.device, self.lib
-        P, Ps, W, H, M = self.P, self.Ps, self.W, self.H, self.M
+        ctxs, p, cams, tanfov, scale_modifier, D, debug = self._state
+        N, r, dev, lib = self.world, self.rank, self.device, self.lib
+        P, Ps, W, H, M, V, L = self.P, self.Ps, self.W, self.H, self.M, self.V, self.L
         g = _dense(dL_dpix, dev)
-        if g is None or tuple(g.shape) != (3, H, W):
-            raise RuntimeError("dL_dpix must be [3,H,W]")
+        if g is not None and g.dim() == 3 and L == 1:
+            g = g.unsqueeze(0)
+        if g is None or tuple(g.shape) != (L, 3, H, W):
+            raise RuntimeError(f"dL_dpix must be [{L},3,{H},{W}]")
+        staged = self.exchange == "nccl"
         with torch.cuda.device(dev):
             stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-            _native.check(L.gsr_blend_backward(P, W, H, _ptr(cams[r][3]), _ptr(ctx.geom_ws), _ptr(ctx.binning_ws),
-                                               ctx.capacity, _ptr(ctx.image_ws), _ptr(g), stream, debug),
-                          "gsr_blend_backward")
+            for l, ctx in enumerate(ctxs):
+                _native.check(lib.gsr_blend_backward(P, W, H, _ptr(cams[r + l * N][3]), _ptr(ctx.geom_ws),
+                                                     _ptr(ctx.binning_ws), ctx.capacity, _ptr(ctx.image_ws), _ptr(g[l]),
+                                                     stream, debug), "gsr_blend_backward")
             if self.exchange == "peer":
                 self.hdl.barrier(channel=2)   # every view's accumulators are complete
-            else:
-                all_to_all_rows([([self.full["grad_accum"][self.plan.rows(j)] for j in range(N)],
-                                  [self.send["grad_accum"][self._slot(v)] for v in range(N)])], self.group)
+            elif staged:
+                bufs = self._bufs[self.parity]
+                all_to_all_rows([([bufs[l][2]["grad_accum"][self.plan.rows(j)] for j in range(N)],
+                                  [self.send["grad_accum"][self._slot(j + l * N)] for j in range(N)])
+                                 for l in range(L)], self.group)
             G = self.grads
             order = self._view_order()
-            step = _native.MAX_VIEWS if self.exchange == "peer" else 1
-            for c0 in range(0, N, step):
+            step = 1 if staged else _native.MAX_VIEWS
+            for c0 in range(0, V, step):
                 chunk = order[c0:c0 + step]
-                slots, P_ws, row0 = self._view_slots(chunk, cams, None, scal)
-                _native.check(L.gsr_preprocess_backward_views(
+                slots, P_ws, row0 = self._view_slots(chunk, cams, tanfov)
+                _native.check(lib.gsr_preprocess_backward_views(
                     P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["scales"]),
-                    scal[r][0], _ptr(p["rotations"]), None, len(chunk), slots, None, _ptr(G["opacities"]),
+                    scale_modifier, _ptr(p["rotations"]), None, len(chunk), slots, None, _ptr(G["opacities"]),
                     _ptr(G["means3D"]), None, _ptr(G["shs"]), _ptr(G["scales"]), _ptr(G["rotations"]),
                     1 if c0 > 0 else 0, stream, debug), "gsr_preprocess_backward_views")
         return G, self.grad_means2D
+
+    def slice_radii(self) -> torch.Tensor:
+        """[V, Ps] int32: the radii of this rank's slice in each view of the last forward (train.py:130 reads
+        `radii` of the rendered view; here every view of the batch contributes)."""
+        return self.radii_local & _native.LOCAL_RADIUS_MASK
+
+    def densification_stats(self, max_radii2D: torch.Tensor, xyz_gradient_accum: torch.Tensor, denom: torch.Tensor):
+        """train.py:130-131 + scene/gaussian_model.py:775-777 for the slice, once per view of the batch in view
+        order: max_radii2D = max(., radii_v) and xyz_gradient_accum += |dL/dmeans2D_v[:, :2]|, denom += 1 on the rows
+        view v sees.  In place on the slice owner's [Ps] / [Ps,1] / [Ps,1] statistics; call after `backward`."""
+        if self.Ps == 0:
+            return
+        radii = self.slice_radii()
+        with torch.cuda.device(self.device):
+            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            for v in range(self.V):
+                _native.check(self.lib.gsr_densification_stats(
+                    self.Ps, _ptr(radii[v]), _ptr(self.grad_means2D[v]), _ptr(max_radii2D), _ptr(xyz_gradient_accum),
+                    _ptr(denom), stream), "gsr_densification_stats")

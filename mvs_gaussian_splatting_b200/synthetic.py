@@ -99,6 +99,16 @@ def ring_cameras(n: int, width: int, height: int, radius: float = 4.0, centre=(0
     return cams
 
 
+def batch_cameras(n: int, width: int, height: int):
+    """Cameras of an n-view training batch over the scene `make_gaussians` builds for the front camera: view 0
+    alone is the front camera (the single-view workload); a batch of n > 1 views sits on SURVEY §8(d)'s ring
+    of radius 4 around the scene axis, every camera looking at the scene centre — distinct views, different
+    instance counts per view."""
+    if n == 1:
+        return [front_camera(width, height)]
+    return ring_cameras(n, width, height)
+
+
 def make_gaussians(P: int, cam: Camera, sh_coeffs: int = 16, seed: int = 0, sigma_px: float = 0.62,
                    huge_frac: float = 0.0005, needle_frac: float = 0.005, behind_frac: float = 0.10):
     """SURVEY §8d scene: 90 % of the means uniform in the view-frustum slab z in [1, 20] (x, y

@@ -18,7 +18,7 @@ from mvs_gaussian_splatting_b200.loss import l1_loss  # noqa: E402
 
 dev = torch.device("cuda:0")
 P, W, H, D, M = 3_000_000, 1920, 1080, 3, 16
-cam = bench.bench_camera(0, W, H)
+cam = S.front_camera(W, H)
 g = S.make_gaussians(P, cam, sh_coeffs=M, seed=0)
 params = {k: torch.from_numpy(v).to(dev).requires_grad_(True) for k, v in g.items()}
 kw = S.settings_kwargs(cam, [0.0, 0.0, 0.0], D)
