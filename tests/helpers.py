@@ -58,7 +58,7 @@ def close(a, b, scale=None, rel=REL_TOL):
 GRAD_K = 1.0   # multiples of the running rounding-error bound u*e accepted per element (see grad_check)
 
 
-def gradient_reference(O, cam, g, bg, sh_degree, dL, threads=8, zero_fragile=True, **kw):
+def gradient_reference(O, cam, g, bg, sh_degree, dL, threads=8, zero_fragile=True, run_backward=True, **kw):
     """The references a gradient test compares with, sharing ONE set of integer decisions:
       ref32 — the binary32 oracle (forward + backward): radii / lists / image are compared with it;
       refre — the running-error build (binary64 values `v` + per-element bound `e` on what a binary32
@@ -73,9 +73,22 @@ def gradient_reference(O, cam, g, bg, sh_degree, dL, threads=8, zero_fragile=Tru
     dL = np.array(dL, np.float32, copy=True)
     if zero_fragile:
         dL[:, fragile] = 0.0
-    O.backward(ref32, dL)
-    O.backward(refre, dL)
+    if run_backward:
+        O.backward(ref32, dL)
+        O.backward(refre, dL)
     return dL, ref32, refre, fragile
+
+
+def flipped_pixels(n_c, T_c, ref32, refre):
+    """Pixels where a skip / stop decision actually DIFFERS between the three evaluations in play — the CUDA path
+    (its n_contrib [H,W] uint32 and final_T [H,W]), the binary32 oracle and the binary64 running-error oracle the
+    gradients are compared with (it decides on its own binary64 values).  Observable: a flipped stop changes
+    n_contrib, a flipped skip changes final_T by at least the factor 1 - 1/255.  Always a subset of `fragile`
+    (asserted by the callers); everywhere else the three differentiate the same function."""
+    T_r, n_r = ref32["fwd"]["final_T"], ref32["fwd"]["n_contrib"]
+    T_e, n_e = refre["fwd"]["final_T"]["v"], refre["fwd"]["n_contrib"]
+    tol = 1e-3 * T_r + 1e-7
+    return (n_c != n_r) | (np.abs(T_c - T_r) > tol) | (n_e != n_r) | (np.abs(T_e - T_r) > tol)
 
 
 def grad_check(a, re, rel=REL_TOL, k=GRAD_K):

@@ -6,9 +6,11 @@ point lists and tile ranges; image and gradient tensors within 1e-4 relative (fp
 
 Pixels the oracle flags `fragile` (a skip/stop decision sits within 1e-4 relative of its
 threshold — or, in the running-error build, within its own binary32 rounding error of it — so a
-different but valid exp() rounding may legally flip it) are excluded from the image comparison and
-carry zero upstream gradient in the backward comparison; their share is asserted to be small, and
-tests/test_gpu_fragile.py looks at the gradients THROUGH them.
+different but valid exp() rounding may legally flip it) are excluded from the image comparison.  In
+the backward comparison dL/dpixel is zeroed only on the pixels where such a decision ACTUALLY differs
+between the CUDA path, the binary32 oracle and the binary64 running-error oracle (helpers.flipped_pixels:
+a fraction of a percent, asserted to lie inside the fragile set); fragile pixels whose decisions agree
+carry gradient like any other.  tests/test_gpu_fragile.py looks at the flipped ones.
 
 Gradients: every element within max(1e-4 relative, running rounding-error bound of the reference
 algorithm in binary32) of the binary64 value — helpers.grad_check.
@@ -110,16 +112,30 @@ def test_backward_gradients(cuda, oracle, P, W, H, D, M, seed):
 
 def check_backward(cuda, oracle, P, W, H, D, M, seed, threads=8):
     import torch
-    from mvs_gaussian_splatting_b200 import GaussianRasterizer
+    from mvs_gaussian_splatting_b200 import GaussianRasterizer, rasterize_forward
     cam, g = Hh.make_case(P, W, H, seed=seed, sh_coeffs=M)
     bg = [0.3, 0.2, 0.7]
     rng = np.random.default_rng(100 + seed)
-    dL, ref, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D, rng.normal(size=(3, H, W)), threads=threads)
-    assert fragile.mean() < 0.06
+    dL, ref, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D, rng.normal(size=(3, H, W)), threads=threads,
+                                                    zero_fragile=False, run_backward=False)
+    assert fragile.mean() < 0.15
 
     rs = Hh.settings_for(cam, bg, D, cuda)
     t = Hh.to_dev(g, cuda, requires_grad=True)
     means2D = torch.zeros_like(t["means3D"], requires_grad=True)
+    color, radii, ctx, _ = rasterize_forward(t["means3D"], t["shs"], None, t["opacities"], t["scales"], t["rotations"],
+                                             None, rs)
+    torch.cuda.synchronize()
+    # dL/dpixel is zero ONLY where a skip / stop decision actually differs between the CUDA path, the binary32 oracle
+    # and the binary64 running-error oracle (a fraction of a percent, all inside the flagged `fragile` set); fragile
+    # pixels whose decisions agree carry gradient like any other pixel
+    flipped = Hh.flipped_pixels(ctx.array("n_contrib").cpu().numpy().view(np.uint32).reshape(H, W),
+                                ctx.array("final_T").cpu().numpy().reshape(H, W), ref, refre)
+    assert not (flipped & ~fragile).any(), "a decision flipped on a pixel the oracle did not flag"
+    assert flipped.mean() < 0.005, flipped.mean()
+    dL[:, flipped] = 0.0
+    oracle.backward(ref, dL)
+    oracle.backward(refre, dL)
     color, radii = GaussianRasterizer(rs)(means3D=t["means3D"], means2D=means2D, shs=t["shs"], colors_precomp=None,
                                           opacities=t["opacities"], scales=t["scales"], rotations=t["rotations"],
                                           cov3D_precomp=None)

@@ -6,7 +6,7 @@ TAG=${1:-r02b}
 OUT=gpurun_out
 mkdir -p $OUT
 rm -f $OUT/grad_report.txt
-timeout 1500 python -m pytest tests -m gpu -q -x --timeout 900 > $OUT/${TAG}_pytest_gpu.log 2>&1
+timeout 1500 python -m pytest tests -m gpu -q --timeout 900 > $OUT/${TAG}_pytest_gpu.log 2>&1
 echo "pytest exit $?" | tee -a $OUT/${TAG}_pytest_gpu.log
 tail -25 $OUT/${TAG}_pytest_gpu.log
 cp $OUT/grad_report.txt $OUT/${TAG}_grad_report.txt 2>/dev/null; cat $OUT/${TAG}_grad_report.txt 2>/dev/null
