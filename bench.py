@@ -297,15 +297,19 @@ def stage_rooflines(stage_ms, counts, peaks, clocks):
     Bytes and FLOPs per unit are the figures of SURVEY 8(d), restated in DESIGN.md."""
     P, Pv, R, tiles = counts["P"], counts["P_visible"], counts["R"], counts["tiles"]
     E, C, En = counts["pairs_evaluated"], counts["pairs_blended"], counts["sum_n_contrib"]
-    keybits = 32 + max(1, math.ceil(math.log2(max(tiles, 2))))
+    keybits = 32 + max(1, math.ceil(math.log2(max(tiles / max(counts.get("views_rendered_by_this_rank", 1), 1), 2))))
+    tile_key_bytes = 2.0 if keybits <= 48 else 4.0
     hbm = {
         "preprocess": 52.0 * P + 259.0 * Pv,
-        "depth_sort": 68.0 * P,          # one histogram read + 4 passes x (8 B read + 8 B write)
-        "scan": 12.0 * P,                # order + gathered tiles_touched read, offsets written
-        "emit_keys": 12.0 * R + 24.0 * Pv,
-        # tile-bit sort only (the depth order comes from depth_sort): histogram read + passes x (12 r + 12 w)
-        "radix_sort": (8.0 + 24.0 * math.ceil((keybits - 32) / 8)) * R,
-        "tile_ranges": 8.0 * R + 8.0 * tiles,
+        # counts + histograms: depths and tiles_touched read (8 P); pass 1 reads P keys and writes the P_visible
+        # (key, index) pairs it keeps, passes 2-4 move P_visible pairs (8 B read + 8 B write)
+        "depth_sort": 12.0 * P + 56.0 * Pv,
+        # prefix sum + emission in one kernel: order, radii, means2D read per visible Gaussian; one
+        # (tile id, index) entry written per instance (2 + 4 B up to 65536 tiles)
+        "emit_keys": 16.0 * Pv + (tile_key_bytes + 4.0) * R,
+        "tile_ranges": 12.0 * tiles,     # per-tile counts read, [start, end) written
+        # tile-bit sort only (the depth order comes from depth_sort): passes x (entry read + entry written)
+        "radix_sort": 2.0 * (tile_key_bytes + 4.0) * math.ceil((keybits - 32) / 8) * R,
         "preprocess_backward": 303.0 * Pv + 240.0 * P,
     }
     flops = {
@@ -366,7 +370,7 @@ def _event_stats(events, world, dist, torch, dev):
         tt = torch.tensor(vals, device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         vals = [float(x) for x in tt.tolist()]
-    return vals
+    return vals + [[round(float(x), 3) for x in per]]
 
 
 def run_b200_arm(args):
@@ -464,7 +468,7 @@ def run_b200_arm(args):
     barrier()
     launches = _native.launch_count() - n0
     clocks = sampler.result()
-    ms_step, ms_median, ms_p90 = _event_stats(events, world, dist, torch, dev)
+    ms_step, ms_median, ms_p90, ms_all = _event_stats(events, world, dist, torch, dev)
     value = V * 1e3 / ms_step
     # ---- second pass: the same K steps with the library's per-stage event pairs switched on ----
     _native.stage_timing_enable(True)
@@ -532,6 +536,7 @@ def run_b200_arm(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": warmup, "ms_per_step": ms_step, "ms_per_step_median": ms_median, "ms_per_step_p90": ms_p90,
+        "ms_per_step_rank0": ms_all,
         "ms_per_view": ms_step / V, "higher_is_better": True,
         "scaling": "weak" if (args.views is None and world == 1) or V == world else "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",

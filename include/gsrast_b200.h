@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define GSR_ABI_VERSION 8
+#define GSR_ABI_VERSION 9
 #define GSR_MAX_VIEWS 16   /* views one multi-view call can take */
 
 #if defined(__GNUC__)
@@ -72,24 +72,27 @@ typedef struct gsr_layout {
     size_t g_conic_opacity; /* f32[P,4] conic A,B,C + opacity                                  */
     size_t g_rgb;           /* f32[P,4] r,g,b + clamped bits (as u32 in .w, bit c = channel c) */
     size_t g_tiles_touched; /* u32[P]                                                          */
-    size_t g_point_offsets; /* u32[P]   inclusive prefix sum of tiles_touched in DEPTH order     */
     size_t g_info;          /* gsr_forward_info (device copy)                                  */
     size_t g_grad_accum;    /* f32[P,12] backward blend accumulators                           */
-    size_t g_order_keys;    /* u32[P]   depth bits ascending (stable), culled (0xFFFFFFFF) last  */
+    size_t g_order_keys;    /* u32[P]   depth bits of the num_visible visible Gaussians, ascending (stable) */
     size_t g_order;         /* u32[P]   Gaussian index of depth-order slot k                     */
     size_t g_order_keys_alt;/* u32[P]   sort ping-pong                                           */
     size_t g_order_alt;     /* u32[P]                                                            */
     size_t g_sort_ctl;      /* u32[...] histograms, tickets, look-back status                    */
     size_t geom_bytes;
     /* binning workspace, per tile instance (capacity entries each) */
-    size_t b_keys_unsorted; /* u64[C]  (tile << 32) | depth bits, emitted in DEPTH order         */
+    size_t b_keys_unsorted; /* K[C]    tile id of every instance, emitted in DEPTH order; K = u16 up to
+                               65536 tiles, else u32 (b_key_bytes).  The reference's 64-bit key
+                               (tile << 32) | depth bits is gsr_materialize_keys(): its low half is
+                               depths[index], which no stage of the render path needs to move         */
     size_t b_vals_unsorted; /* u32[C]  Gaussian index                                          */
-    size_t b_keys;          /* u64[C]  sorted                                                  */
+    size_t b_keys;          /* K[C]    sorted by tile (stable)                                 */
     size_t b_point_list;    /* u32[C]  sorted                                                  */
-    size_t b_keys_alt;      /* u64[C]  radix-sort ping-pong buffer                             */
+    size_t b_keys_alt;      /* K[C]    radix-sort ping-pong buffer                             */
     size_t b_vals_alt;      /* u32[C]                                                          */
-    size_t b_sort_ctl;      /* u32[...] histograms, tickets, look-back status                    */
+    size_t b_sort_ctl;      /* u32[...] histograms, tickets, per-tile counts, look-back status   */
     size_t binning_bytes;
+    size_t b_key_bytes;     /* sizeof(K): 2 or 4                                               */
     /* image workspace */
     size_t i_ranges;        /* u32[tiles,2] [start,end) into point_list                        */
     size_t i_final_T;       /* f32[H*W]                                                        */
@@ -330,6 +333,14 @@ GSR_API int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int
                          float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D, float* dL_dcov3D,
                          float* dL_dsh, float* dL_dscales, float* dL_drots, int accumulate, void* stream,
                          int debug);
+
+/* The reference's sorted / unsorted 64-bit key list (binningState.point_list_keys[_unsorted]: (tile << 32) |
+ * depth bits) of the last gsr_forward_render on these workspaces, written to d_keys[0 .. num_rendered) (device
+ * memory, instance_capacity entries).  sorted = 0: emission order (Gaussians in depth order, each one's tiles
+ * row-major — a per-Gaussian-block permutation of the reference's index-order list); sorted = 1: the sorted list.
+ * For parity tests and debugging: the render path stores only tile ids and indices. */
+GSR_API int gsr_materialize_keys(int P, int width, int height, void* geom_ws, void* binning_ws,
+                         int64_t instance_capacity, int sorted, uint64_t* d_keys, void* stream);
 
 /* Replaces `_C.mark_visible`: present[i] = 1 iff Gaussian i passes the near-plane test. */
 GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,

@@ -18,7 +18,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # GSRAST_B200_LIB: A/B builds of the same ABI during kernel tuning (never a different backend)
 LIB_PATH = os.environ.get("GSRAST_B200_LIB") or os.path.join(_HERE, "lib", "libgsrast_b200.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 GSR_OK = 0
 GSR_ERR_INVALID_ARGUMENT = 1
@@ -37,7 +37,7 @@ EXPORTS = (
     "gsr_forward_geometry_raw", "gsr_backward_raw", "gsr_activate",
     "gsr_adam_step", "gsr_densification_stats",
     "gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward",
-    "gsr_ply_unpack", "gsr_ply_pack",
+    "gsr_ply_unpack", "gsr_ply_pack", "gsr_materialize_keys",
 )
 PLY_MAX_PROPS = 96
 MAX_ADAM_GROUPS = 16
@@ -75,11 +75,11 @@ class ForwardInfo(ctypes.Structure):
 
 class Layout(ctypes.Structure):
     _fields_ = [(n, ctypes.c_size_t) for n in (
-        "g_depths", "g_means2D", "g_conic_opacity", "g_rgb", "g_tiles_touched", "g_point_offsets",
+        "g_depths", "g_means2D", "g_conic_opacity", "g_rgb", "g_tiles_touched",
         "g_info", "g_grad_accum", "g_order_keys", "g_order", "g_order_keys_alt", "g_order_alt", "g_sort_ctl",
         "geom_bytes",
         "b_keys_unsorted", "b_vals_unsorted", "b_keys", "b_point_list", "b_keys_alt", "b_vals_alt",
-        "b_sort_ctl", "binning_bytes",
+        "b_sort_ctl", "binning_bytes", "b_key_bytes",
         "i_ranges", "i_final_T", "i_n_contrib", "image_bytes")]
 
 
@@ -178,6 +178,8 @@ def lib() -> ctypes.CDLL:
             _i, _vp, _i]                 # accumulate stream debug
         L.gsr_blend_pair_counts.argtypes = [_i, _i, _i, _vp, _vp, _i64, _vp, _vp, _vp]
         L.gsr_blend_pair_counts.restype = _i
+        L.gsr_materialize_keys.argtypes = [_i, _i, _i, _vp, _vp, _i64, _i, _vp, _vp]
+        L.gsr_materialize_keys.restype = _i
         L.gsr_stage_count.restype = _i
         L.gsr_stage_name.restype = ctypes.c_char_p
         L.gsr_stage_name.argtypes = [_i]

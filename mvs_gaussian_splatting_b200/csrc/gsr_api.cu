@@ -74,7 +74,6 @@ void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
     L->g_conic_opacity = take(16 * p);
     L->g_rgb = take(16 * p);
     L->g_tiles_touched = take(4 * p);
-    L->g_point_offsets = take(4 * p);
     L->g_info = take(sizeof(gsr_forward_info));
     L->g_grad_accum = take(48 * p);
     L->g_order_keys = take(4 * p);
@@ -84,14 +83,16 @@ void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L) {
     L->g_sort_ctl = take(4 * depth_sort_ctl_entries(p));
     L->geom_bytes = o;
     o = 0;
-    L->b_keys_unsorted = take(8 * c);
+    const size_t kb = (size_t)tile_key_bytes(g.tiles);
+    L->b_keys_unsorted = take(kb * c);
     L->b_vals_unsorted = take(4 * c);
-    L->b_keys = take(8 * c);
+    L->b_keys = take(kb * c);
     L->b_point_list = take(4 * c);
-    L->b_keys_alt = take(8 * c);
+    L->b_keys_alt = take(kb * c);
     L->b_vals_alt = take(4 * c);
-    L->b_sort_ctl = take(4 * tile_sort_ctl_entries(c));
+    L->b_sort_ctl = take(4 * tile_sort_ctl_entries(c, p, (size_t)g.tiles));
     L->binning_bytes = o;
+    L->b_key_bytes = kb;
     o = 0;
     L->i_ranges = take(8 * (size_t)g.tiles);
     L->i_final_T = take(4 * (size_t)W * H);
@@ -109,7 +110,6 @@ GeomView geom_view(void* ws, const gsr_layout& L) {
     v.conic_opacity = at<float4>(ws, L.g_conic_opacity);
     v.rgb = at<float4>(ws, L.g_rgb);
     v.tiles_touched = at<uint32_t>(ws, L.g_tiles_touched);
-    v.point_offsets = at<uint32_t>(ws, L.g_point_offsets);
     v.info = at<gsr_forward_info>(ws, L.g_info);
     v.grad_accum = at<float>(ws, L.g_grad_accum);
     v.order_keys = at<uint32_t>(ws, L.g_order_keys);
@@ -121,11 +121,11 @@ GeomView geom_view(void* ws, const gsr_layout& L) {
 }
 BinView bin_view(void* ws, const gsr_layout& L) {
     BinView v;
-    v.keys_unsorted = at<uint64_t>(ws, L.b_keys_unsorted);
+    v.keys_unsorted = at<char>(ws, L.b_keys_unsorted);
     v.vals_unsorted = at<uint32_t>(ws, L.b_vals_unsorted);
-    v.keys = at<uint64_t>(ws, L.b_keys);
+    v.keys = at<char>(ws, L.b_keys);
     v.point_list = at<uint32_t>(ws, L.b_point_list);
-    v.keys_alt = at<uint64_t>(ws, L.b_keys_alt);
+    v.keys_alt = at<char>(ws, L.b_keys_alt);
     v.vals_alt = at<uint32_t>(ws, L.b_vals_alt);
     v.sort_ctl = at<uint32_t>(ws, L.b_sort_ctl);
     return v;
@@ -144,7 +144,7 @@ static int check_dims(int P, int W, int H, int64_t cap) {
     if (P < 0 || W <= 0 || H <= 0 || cap < 0) return GSR_ERR_INVALID_ARGUMENT;
     if (cap >= (1ll << 30) || P >= (1 << 30)) return GSR_ERR_UNSUPPORTED;  // 30-bit look-back counts
     const Grid g = make_grid(W, H);
-    if ((int64_t)g.gx * g.gy > (1ll << 30)) return GSR_ERR_UNSUPPORTED;
+    if (g.gx > 65535 || g.gy > 65535 || (int64_t)g.gx * g.gy > (1ll << 30)) return GSR_ERR_UNSUPPORTED;
     return GSR_OK;
 }
 
@@ -176,7 +176,7 @@ int64_t gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxe
 int gsr_stage_count(void) { return kStageCount; }
 
 const char* gsr_stage_name(int stage) {
-    static const char* names[kStageCount] = {"preprocess", "depth_sort", "scan", "emit_keys", "radix_sort", "tile_ranges",
+    static const char* names[kStageCount] = {"preprocess", "depth_sort", "emit_keys", "tile_ranges", "radix_sort",
                                              "blend_forward", "blend_backward", "preprocess_backward"};
     return (stage >= 0 && stage < kStageCount) ? names[stage] : "";
 }
@@ -672,6 +672,18 @@ int gsr_blend_pair_counts(int P, int width, int height, void* geom_ws, void* bin
     return launch_blend_pair_counts(make_grid(width, height), geom_view(geom_ws, L), bin_view(binning_ws, L),
                                     image_view(image_ws, L), reinterpret_cast<unsigned long long*>(d_counters),
                                     static_cast<cudaStream_t>(stream));
+}
+
+int gsr_materialize_keys(int P, int width, int height, void* geom_ws, void* binning_ws, int64_t instance_capacity,
+                         int sorted, uint64_t* d_keys, void* stream) {
+    int st = check_dims(P, width, height, instance_capacity);
+    if (st != GSR_OK) return st;
+    if (!geom_ws || !binning_ws || !aligned16(geom_ws) || !aligned16(binning_ws)) return GSR_ERR_WORKSPACE;
+    if (!d_keys) return GSR_ERR_INVALID_ARGUMENT;
+    gsr_layout L;
+    compute_layout(P, width, height, instance_capacity, &L);
+    return launch_materialize_keys(P, make_grid(width, height), geom_view(geom_ws, L), bin_view(binning_ws, L),
+                                   instance_capacity, sorted != 0, d_keys, static_cast<cudaStream_t>(stream));
 }
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

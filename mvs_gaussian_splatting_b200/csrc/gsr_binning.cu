@@ -4,16 +4,23 @@
 // The reference emits one 64-bit (tile << 32 | depth bits) key per tile instance in Gaussian order
 // and sorts all R of them over 32 + log2(tiles) bits.  The sorted result is fully determined by
 // the (tile, depth bits, Gaussian index) order, which factorises; this file produces the SAME sorted
-// key list / point_list / ranges with far less traffic:
-//   1. stable LSD radix sort of the P per-Gaussian (depth bits -> index) pairs, 4 x 8 bits
-//      (culled Gaussians carry key 0xFFFFFFFF and sink to the end; P-sized, mostly L2-resident);
-//   2. single-pass prefix sum of tiles_touched in that order;
-//   3. key emission in (depth, index) order — the unsorted list is a permutation of the reference's;
-//   4. stable radix sort of the R instances on the TILE bits only (2 passes for <= 65536 tiles).
+// point_list / ranges (and, on request, the same 64-bit key lists) with far less traffic:
+//   1. one read of the depths: digit histograms of the VISIBLE Gaussians, their count and R = sum(tiles_touched);
+//   2. stable LSD radix sort of the per-Gaussian (depth bits -> index) pairs, 4 x 8 bits; the first pass
+//      drops the culled Gaussians, so passes 2-4 move P_visible pairs (P-sized, L2-resident);
+//   3. ONE kernel for the prefix sum over the depth-ordered tile counts AND the key emission: chunk offsets by
+//      decoupled look-back, entries written with a load-balanced search (every thread writes consecutive list
+//      positions: coalesced), per-tile instance counts by RED.  An instance is stored as its TILE id only
+//      (u16 up to 65536 tiles, else u32) + the Gaussian index: 6 bytes, not 12 — the depth bits of the
+//      reference's key are a function of the index (depths[idx]) and the tile sort below never looks at them;
+//   4. exclusive scan of the per-tile counts = the tile ranges (identifyTileRanges without reading a key)
+//      and, folded over the digits, the histograms of the tile-bit passes (no histogram pass over the instances);
+//   5. stable radix sort of the R instances on the tile bits only (2 passes up to 65536 tiles).
+// The reference's 64-bit key lists are materialised from (tile, depths[idx]) by gsr_materialize_keys for the
+// parity tests and debugging; nothing on the render path reads them.
 // Every radix pass is ONE kernel: chunk histograms are chained with decoupled look-back (ticketed
 // chunks, 2 flag bits + 30 count bits per (chunk, digit) status word), keys are ranked per warp with
-// one ballot per digit bit, reordered through shared memory and written as coalesced per-digit runs.  Digit
-// histograms of all passes of a sort come from one read of the keys.
+// one ballot per digit bit, reordered through shared memory and written as coalesced per-digit runs.
 //
 // Everything is integer work bound by HBM / L2.  The instance count R lives on the DEVICE
 // (info->num_rendered); kernels are launched for the caller's instance_capacity and bound themselves
@@ -80,90 +87,39 @@ __device__ __forceinline__ uint32_t effective_n(const uint32_t* __restrict__ r_p
     return r <= cap ? r : 0u;
 }
 
-// Publishes the overflow flag for the host.
+// Publishes the overflow flag for the host (zero-capacity path; otherwise tile_offsets_kernel does it).
 __global__ void publish_info_kernel(uint32_t cap, gsr_forward_info* info) {
     info->overflow = (uint32_t)info->num_rendered > cap ? 1 : 0;
 }
 
-// =========================== prefix sum in depth order =====================================
-// out[k] = sum_{j <= k} tiles_touched[order[j]]; single pass, decoupled look-back over ticketed
-// chunks (status word: flag << 32 | value; flag 1 = chunk aggregate, 2 = inclusive prefix).
-constexpr int kScanItems = 8;
-constexpr int kScanChunk = kBlk * kScanItems;
-
-__global__ void __launch_bounds__(kBlk) scan_sorted_tiles_kernel(int P, const uint32_t* __restrict__ order,
-                                                                 const uint32_t* __restrict__ tiles_touched,
-                                                                 uint32_t* __restrict__ out,
-                                                                 unsigned long long* status, uint32_t* ticket,
-                                                                 gsr_forward_info* info) {
-    __shared__ uint32_t s_warp[kBlk / 32 + 1];
-    __shared__ uint32_t s_b, s_prefix;
-    if (threadIdx.x == 0) s_b = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t b = s_b;
-    const size_t i0 = (size_t)b * kScanChunk + (size_t)threadIdx.x * kScanItems;
-    uint32_t v[kScanItems];
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k) v[k] = 0;
-    if (i0 + kScanItems <= (size_t)P) {
-        const uint4 a = *reinterpret_cast<const uint4*>(order + i0);
-        const uint4 c = *reinterpret_cast<const uint4*>(order + i0 + 4);
-        const uint32_t id[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-#pragma unroll
-        for (int k = 0; k < kScanItems; ++k) v[k] = __ldg(tiles_touched + id[k]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < kScanItems; ++k)
-            if (i0 + k < (size_t)P) v[k] = __ldg(tiles_touched + order[i0 + k]);
+// Decoupled look-back over ticketed chunks (status word: flag << 32 | value; flag 1 = chunk aggregate,
+// 2 = inclusive prefix).  Called by warp 0 of chunk b with the chunk total; returns the exclusive prefix.
+__device__ __forceinline__ uint32_t lookback_prefix(unsigned long long* status, uint32_t b, uint32_t total) {
+    const unsigned lane = lane_id();
+    uint32_t prefix = 0;
+    if (b == 0) {
+        if (lane == 0) st_relaxed64(status, (2ull << 32) | total);
+        return 0;
     }
-    uint32_t sum = 0;
-#pragma unroll
-    for (int k = 0; k < kScanItems; ++k) sum += v[k];
-    uint32_t total;
-    const uint32_t ex = block_excl_scan(sum, s_warp, total);
-
-    if (threadIdx.x < 32) {  // warp 0: publish, then look back 32 chunks at a time
-        const unsigned lane = lane_id();
-        uint32_t prefix = 0;
-        if (b == 0) {
-            if (lane == 0) st_relaxed64(status, (2ull << 32) | total);
-        } else {
-            if (lane == 0) st_relaxed64(status + b, (1ull << 32) | total);
-            int base = (int)b - 1;
-            while (true) {
-                const int j = base - (int)lane;
-                unsigned long long s = 2ull << 32;  // before the first chunk: inclusive 0
-                if (j >= 0) {
-                    do { s = ld_relaxed64(status + j); } while ((s >> 32) == 0);
-                }
-                const unsigned incl = __ballot_sync(0xffffffffu, (s >> 32) == 2);
-                const int first = __ffs(incl) - 1;  // nearest chunk holding an inclusive prefix, or -1
-                uint32_t val = (first < 0 || (int)lane <= first) ? (uint32_t)s : 0u;
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-                prefix += val;
-                if (first >= 0) break;
-                base -= 32;
-            }
-            if (lane == 0) st_relaxed64(status + b, (2ull << 32) | (prefix + total));
+    if (lane == 0) st_relaxed64(status + b, (1ull << 32) | total);
+    int base = (int)b - 1;
+    while (true) {
+        const int j = base - (int)lane;
+        unsigned long long s = 2ull << 32;  // before the first chunk: inclusive 0
+        if (j >= 0) {
+            do { s = ld_relaxed64(status + j); } while ((s >> 32) == 0);
         }
-        if (lane == 0) s_prefix = prefix;
-    }
-    __syncthreads();
-    uint32_t run = s_prefix + ex;
-    uint32_t o[kScanItems];
+        const unsigned incl = __ballot_sync(0xffffffffu, (s >> 32) == 2);
+        const int first = __ffs(incl) - 1;  // nearest chunk holding an inclusive prefix, or -1
+        uint32_t val = (first < 0 || (int)lane <= first) ? (uint32_t)s : 0u;
 #pragma unroll
-    for (int k = 0; k < kScanItems; ++k) { run += v[k]; o[k] = run; }
-    if (i0 + kScanItems <= (size_t)P) {
-        *reinterpret_cast<uint4*>(out + i0) = make_uint4(o[0], o[1], o[2], o[3]);
-        *reinterpret_cast<uint4*>(out + i0 + 4) = make_uint4(o[4], o[5], o[6], o[7]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < kScanItems; ++k)
-            if (i0 + k < (size_t)P) out[i0 + k] = o[k];
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        prefix += val;
+        if (first >= 0) break;
+        base -= 32;
     }
-    if ((size_t)b * kScanChunk + kScanChunk >= (size_t)P && threadIdx.x == kBlk - 1)
-        info->num_rendered = (int32_t)run;  // last chunk, last thread: grand total R
+    if (lane == 0) st_relaxed64(status + b, (2ull << 32) | (prefix + total));
+    return prefix;
 }
 
 // =========================== stable LSD radix sort, one kernel per pass ====================
@@ -173,6 +129,9 @@ __global__ void __launch_bounds__(kBlk) scan_sorted_tiles_kernel(int P, const ui
 #ifndef GSR_SORT_MINBLOCKS
 #define GSR_SORT_MINBLOCKS 2
 #endif
+#ifndef GSR_TILE_SORT_MINBLOCKS
+#define GSR_TILE_SORT_MINBLOCKS 2
+#endif
 constexpr int kSortItems = GSR_SORT_ITEMS;      // per thread
 constexpr int kSortChunk = kBlk * kSortItems;   // 6144 items per ticket
 constexpr int kSortWarps = kBlk / 32;
@@ -181,57 +140,70 @@ constexpr int kMaxBins = 256;
 constexpr int kMaxPasses = 4;
 constexpr uint32_t kFlagAgg = 1u << 30, kFlagIncl = 2u << 30, kValMask = (1u << 30) - 1u;
 
-// Digit histograms of ALL passes of one sort from a single read of the keys: hist[pass][digit].
-// Shared atomics, with a vote so that warps whose digit is constant (culled keys, high depth bytes)
-// issue one add instead of 32 serialised ones.
-template <typename K>
-__global__ void __launch_bounds__(kBlk) radix_hist_kernel(const K* __restrict__ keys, const uint32_t* __restrict__ n_ptr,
-                                                          uint32_t n_host, uint32_t cap, int shift0, int bits,
-                                                          int npass, uint32_t* __restrict__ hist) {
+// One read of the per-Gaussian depths (+ tiles_touched): digit histograms of all four passes of the depth
+// sort over the VISIBLE Gaussians (culled ones carry the key 0xFFFFFFFF and are dropped by the first pass),
+// their count -> info->num_visible and R = sum(tiles_touched) -> info->num_rendered.  Shared atomics, with a
+// vote so that warps whose digit is constant (the high depth bytes) issue one add instead of 32 serialised ones.
+__global__ void __launch_bounds__(kBlk) depth_hist_kernel(const uint32_t* __restrict__ keys,
+                                                          const uint32_t* __restrict__ tiles_touched, uint32_t n,
+                                                          uint32_t* __restrict__ hist, gsr_forward_info* info) {
     __shared__ uint32_t s_h[kMaxPasses][kMaxBins];
+    __shared__ uint32_t s_sum[2];
     for (int i = threadIdx.x; i < kMaxPasses * kMaxBins; i += kBlk) (&s_h[0][0])[i] = 0;
+    if (threadIdx.x < 2) s_sum[threadIdx.x] = 0;
     __syncthreads();
-    const uint32_t n = n_ptr ? effective_n(n_ptr, cap) : n_host;
-    const uint32_t mask = (1u << bits) - 1u;
     const unsigned lane = lane_id();
+    uint32_t nvis = 0, nren = 0;
     // whole warps iterate together (the uniformity vote needs converged lanes): round n up to a warp multiple
     const size_t stride = (size_t)gridDim.x * kBlk;
     const size_t n_up = ((size_t)n + 31) & ~(size_t)31;
     for (size_t i = (size_t)blockIdx.x * kBlk + threadIdx.x; i < n_up; i += stride) {
-        const bool valid = i < n;
-        const K key = valid ? keys[i] : (K)0;
+        const uint32_t key = i < n ? keys[i] : kInvalidDepthKey;
+        const bool valid = key != kInvalidDepthKey;
+        if (valid) { ++nvis; nren += __ldg(tiles_touched + i); }
         const bool full = __all_sync(0xffffffffu, valid);
-        for (int p = 0; p < npass; ++p) {
-            const uint32_t d = (uint32_t)(key >> (shift0 + p * bits)) & mask;
+#pragma unroll
+        for (int p = 0; p < kMaxPasses; ++p) {
+            const uint32_t d = (key >> (8 * p)) & 255u;
             const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
-            if (full && __all_sync(0xffffffffu, d == d0)) {  // constant digit (culled keys, high depth bytes)
+            if (full && __all_sync(0xffffffffu, d == d0)) {
                 if (lane == 0) atomicAdd(&s_h[p][d0], 32u);
             } else if (valid) {
                 atomicAdd(&s_h[p][d], 1u);
             }
         }
     }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        nvis += __shfl_xor_sync(0xffffffffu, nvis, d);
+        nren += __shfl_xor_sync(0xffffffffu, nren, d);
+    }
+    if (lane == 0 && nvis) { atomicAdd(&s_sum[0], nvis); atomicAdd(&s_sum[1], nren); }
     __syncthreads();
-    const int bins = 1 << bits;
-    for (int i = threadIdx.x; i < npass * bins; i += kBlk) {
-        const int p = i / bins, d = i - p * bins;
-        const uint32_t c = s_h[p][d];
-        if (c) atomicAdd(hist + p * kMaxBins + d, c);
+    for (int i = threadIdx.x; i < kMaxPasses * kMaxBins; i += kBlk) {
+        const uint32_t c = (&s_h[0][0])[i];
+        if (c) atomicAdd(hist + i, c);
+    }
+    if (threadIdx.x == 0 && s_sum[0]) {
+        atomicAdd(&info->num_visible, (int32_t)s_sum[0]);
+        atomicAdd(&info->num_rendered, (int32_t)s_sum[1]);
     }
 }
 
-// One pass.  kIdentityVal: the payload of item i is i itself (first pass of the depth sort), so no
-// payload array is read.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.
-template <typename K, bool kIdentityVal, int kBits>
-__global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+// One pass.  kFirst: first pass of the depth sort — the payload of item i is i itself (no payload array is
+// read) and items whose key is 0xFFFFFFFF (culled Gaussians) are dropped, so the output holds the visible
+// ones only.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.  hist: global digit
+// counts of the items this pass keeps.
+template <typename K, bool kFirst, int kBits, int kMinBlocks>
+__global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                           K* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                           const uint32_t* __restrict__ n_ptr, uint32_t n_host, uint32_t cap,
                                                           int shift, const uint32_t* __restrict__ hist,
                                                           uint32_t* status, uint32_t* ticket) {
     extern __shared__ __align__(16) unsigned char s_raw[];
-    K* s_keys = reinterpret_cast<K*>(s_raw);                                          // [kSortChunk]
-    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw + sizeof(K) * kSortChunk);   // [kSortChunk]
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_raw);                            // [kSortChunk]
     uint32_t* s_cnt = s_vals + kSortChunk;                                            // [kSortWarps][bins]
+    K* s_keys = reinterpret_cast<K*>(s_cnt + kSortWarps * (1 << kBits));              // [kSortChunk]
     __shared__ uint32_t s_binstart[kMaxBins];  // exclusive start of each digit inside this chunk
     __shared__ uint32_t s_gbase[kMaxBins];     // global position of sorted-chunk item i of digit d: s_gbase[d] + i
     __shared__ uint32_t s_warp[kBlk / 32 + 1];
@@ -245,7 +217,6 @@ __global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(co
     const uint32_t b = s_b;
     const size_t start = (size_t)b * kSortChunk;
     if (start >= n) return;
-    const uint32_t count = (uint32_t)min((size_t)kSortChunk, (size_t)n - start);
 
     const int warp = threadIdx.x >> 5;
     const unsigned lane = lane_id();
@@ -259,7 +230,7 @@ __global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(co
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         const size_t i = wbase + (size_t)k * 32 + lane;
-        key[k] = i < n ? keys_in[i] : (K)0;
+        key[k] = i < n ? keys_in[i] : (K)(kFirst ? kInvalidDepthKey : 0);
     }
     // Rank inside the warp: lanes holding the same digit are found with one ballot per digit bit
     // (pipelined votes; MATCH.ANY costs ~150 cycles a piece on sm_100), the lowest such lane bumps the
@@ -267,7 +238,7 @@ __global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(co
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         const size_t i = wbase + (size_t)k * 32 + lane;
-        const bool valid = i < n;
+        const bool valid = kFirst ? (uint32_t)key[k] != kInvalidDepthKey : i < n;
         const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
         unsigned peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
@@ -295,8 +266,8 @@ __global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(co
         }
         if (b != 0) st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagAgg | h);
     }
-    uint32_t total;
-    const uint32_t binstart = block_excl_scan(h, s_warp, total);  // position of digit d in the sorted chunk
+    uint32_t count, total;
+    const uint32_t binstart = block_excl_scan(h, s_warp, count);  // position of digit d in the sorted chunk; items kept
     const uint32_t gh = ((int)threadIdx.x < bins) ? __ldg(hist + threadIdx.x) : 0u;
     const uint32_t gstart = block_excl_scan(gh, s_warp, total);   // global start of digit d
     if ((int)threadIdx.x < bins) {
@@ -337,11 +308,12 @@ __global__ void __launch_bounds__(kBlk, GSR_SORT_MINBLOCKS) radix_pass_kernel(co
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         const size_t i = wbase + (size_t)k * 32 + lane;
-        if (i < n) {
+        const bool valid = kFirst ? (uint32_t)key[k] != kInvalidDepthKey : i < n;
+        if (valid) {
             const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
             const uint32_t pos = s_binstart[d] + my[d] + rank[k];
             s_keys[pos] = key[k];
-            s_vals[pos] = kIdentityVal ? (uint32_t)i : __ldg(vals_in + i);
+            s_vals[pos] = kFirst ? (uint32_t)i : __ldg(vals_in + i);
         }
     }
     __syncthreads();
@@ -364,88 +336,149 @@ constexpr size_t radix_pass_smem(int bits) {
     return (sizeof(K) + 4) * (size_t)kSortChunk + sizeof(uint32_t) * kSortWarps * ((size_t)1 << bits);
 }
 
-// =========================== key emission (duplicateWithKeys) =============================
-// One lane per Gaussian IN DEPTH ORDER (slot k of the per-Gaussian sort); rects of up to kSmallRect
-// tiles are written by the owning lane, larger ones cooperatively by the whole warp (coalesced, and
-// a screen-filling splat no longer serialises thousands of stores on one thread).  Entry t of a
-// rect (row-major, y outer) goes to offsets[k-1] + t.
-constexpr int kSmallRect = 4;
+// =========================== prefix sum + key emission (duplicateWithKeys) ==================
+// One chunk = kEmitSlots consecutive slots of the depth order per thread (one 16-byte load of `order`).  Per slot:
+// the splat's tile rect from (radii, means2D) — its area IS tiles_touched.  The chunk's first list position comes
+// from a decoupled look-back over the chunk totals (the reference's InclusiveSum, never stored).  Entries are then
+// written by a load-balanced search: list position p of the chunk belongs to the last slot whose exclusive offset
+// is <= p, so consecutive threads write consecutive positions whatever the rect sizes (a screen-filling splat is
+// spread over the whole CTA).  Entry t of a rect (row-major, y outer) is tile (y0 + t / w) * gx + x0 + t % w.
+constexpr int kEmitSlots = 4;
+constexpr int kEmitChunk = kBlk * kEmitSlots;
 
-__global__ void __launch_bounds__(256) emit_keys_kernel(int P, int gx, int gy, const uint32_t* __restrict__ order_keys,
-                                                        const uint32_t* __restrict__ order,
-                                                        const int32_t* __restrict__ radii,
-                                                        const float2* __restrict__ means2D,
-                                                        const uint32_t* __restrict__ offsets,
-                                                        const gsr_forward_info* __restrict__ info, uint32_t cap,
-                                                        uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (effective_n(reinterpret_cast<const uint32_t*>(&info->num_rendered), cap) == 0u) return;
-    int x0 = 0, y0 = 0, w = 0, count = 0;
-    uint32_t off = 0, dbits = 0, idx = 0;
-    if (k < P) {
-        dbits = order_keys[k];
-        if (dbits != kInvalidDepthKey) {
-            idx = order[k];
-            const int r = radii[idx];
-            const float2 m = means2D[idx];
-            int x1, y1;
-            tile_rect(m.x, m.y, r, gx, gy, x0, y0, x1, y1);
-            w = x1 - x0;
-            count = w * (y1 - y0);
-            off = k == 0 ? 0u : offsets[k - 1];
-        }
+template <typename TK>
+__global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const uint32_t* __restrict__ order,
+                                                         const int32_t* __restrict__ radii,
+                                                         const float2* __restrict__ means2D,
+                                                         const gsr_forward_info* __restrict__ info, uint32_t cap,
+                                                         unsigned long long* status, uint32_t* ticket,
+                                                         TK* __restrict__ keys, uint32_t* __restrict__ vals,
+                                                         uint32_t* __restrict__ tile_count) {
+    __shared__ uint32_t s_excl[kEmitChunk];   // chunk-local exclusive list offset of each slot
+    __shared__ uint32_t s_xy[kEmitChunk];     // x0 | y0 << 16
+    __shared__ uint32_t s_w[kEmitChunk];      // rect width in tiles
+    __shared__ uint32_t s_idx[kEmitChunk];    // Gaussian index
+    __shared__ uint32_t s_warp[kBlk / 32 + 1];
+    __shared__ uint32_t s_b, s_prefix;
+    if (effective_n(reinterpret_cast<const uint32_t*>(&info->num_rendered), cap) == 0u) return;  // empty or overflow
+    const uint32_t nvis = (uint32_t)__ldg(&info->num_visible);
+    if (threadIdx.x == 0) s_b = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t b = s_b;
+    const uint32_t k0 = b * kEmitChunk + threadIdx.x * kEmitSlots;
+    if (b * kEmitChunk >= nvis) return;
+
+    uint32_t id[kEmitSlots], cnt[kEmitSlots];
+    if (k0 + kEmitSlots <= nvis) {
+        const uint4 a = *reinterpret_cast<const uint4*>(order + k0);
+        id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < kEmitSlots; ++j) id[j] = k0 + j < nvis ? order[k0 + j] : 0xFFFFFFFFu;
     }
-    if (count > 0 && count <= kSmallRect) {
-        for (int t = 0; t < count; ++t) {
-            const int y = y0 + t / w, x = x0 + t - (t / w) * w;
-            keys[off + t] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
-            vals[off + t] = idx;
-        }
+    int rr[kEmitSlots];
+    float2 mm[kEmitSlots];
+#pragma unroll
+    for (int j = 0; j < kEmitSlots; ++j) {
+        const bool on = id[j] != 0xFFFFFFFFu;
+        rr[j] = on ? __ldg(radii + id[j]) : 0;
+        mm[j] = on ? __ldg(means2D + id[j]) : make_float2(0.f, 0.f);
     }
-    unsigned big = __ballot_sync(0xffffffffu, count > kSmallRect);
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-        const int bw = __shfl_sync(0xffffffffu, w, src), bcount = __shfl_sync(0xffffffffu, count, src);
-        const uint32_t boff = __shfl_sync(0xffffffffu, off, src), bd = __shfl_sync(0xffffffffu, dbits, src);
-        const uint32_t bidx = __shfl_sync(0xffffffffu, idx, src);
-        for (int t = lane_id(); t < bcount; t += 32) {
-            const int yy = t / bw;
-            const int y = by0 + yy, x = bx0 + t - yy * bw;
-            keys[boff + t] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | bd;
-            vals[boff + t] = bidx;
-        }
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < kEmitSlots; ++j) {
+        int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+        if (rr[j] > 0) tile_rect(mm[j].x, mm[j].y, rr[j], gx, gy, x0, y0, x1, y1);
+        const uint32_t w = (uint32_t)(x1 - x0);
+        cnt[j] = w * (uint32_t)(y1 - y0);
+        const int sl = threadIdx.x * kEmitSlots + j;
+        s_xy[sl] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+        s_w[sl] = w ? w : 1u;
+        s_idx[sl] = id[j];
+        sum += cnt[j];
+    }
+    uint32_t total;
+    uint32_t ex = block_excl_scan(sum, s_warp, total);
+#pragma unroll
+    for (int j = 0; j < kEmitSlots; ++j) {
+        s_excl[threadIdx.x * kEmitSlots + j] = ex;
+        ex += cnt[j];
+    }
+    if (threadIdx.x < 32) {
+        const uint32_t prefix = lookback_prefix(status, b, total);
+        if (threadIdx.x == 0) s_prefix = prefix;
+    }
+    __syncthreads();
+    const uint32_t goff = s_prefix;
+    for (uint32_t p = threadIdx.x; p < total; p += kBlk) {
+        // last slot s with s_excl[s] <= p (slots of zero area share their successor's offset and are skipped)
+        int lo = 0;
+#pragma unroll
+        for (int step = kEmitChunk / 2; step > 0; step >>= 1)
+            if (s_excl[lo + step] <= p) lo += step;
+        const uint32_t t = p - s_excl[lo];
+        const uint32_t w = s_w[lo], xy = s_xy[lo];
+        const uint32_t yy = t / w;
+        const uint32_t tile = ((xy >> 16) + yy) * (uint32_t)gx + (xy & 0xFFFFu) + (t - yy * w);
+        keys[goff + p] = (TK)tile;
+        vals[goff + p] = s_idx[lo];
+        atomicAdd(tile_count + tile, 1u);
     }
 }
 
-// =========================== tile ranges ==================================================
-// Two sorted keys per thread (one 16-byte load); the predecessor of the pair comes from the
-// neighbouring lane, lane 0 fetches it.
-__global__ void __launch_bounds__(256) tile_ranges_kernel(const uint64_t* __restrict__ keys,
-                                                          const uint32_t* __restrict__ r_ptr, uint32_t cap,
-                                                          uint2* __restrict__ ranges) {
+// =========================== tile ranges + tile-pass histograms =============================
+// Exclusive scan of the per-tile instance counts: ranges[t] = [start, end) into the sorted list (what the
+// reference's identifyTileRanges finds by comparing neighbouring keys), and the digit histograms of the tile-bit
+// radix passes folded out of the same counts.  One CTA (tiles is a few thousand to a few hundred thousand).
+constexpr int kOffsThreads = 1024;
+__global__ void __launch_bounds__(kOffsThreads) tile_offsets_kernel(int tiles, const uint32_t* __restrict__ tile_count,
+                                                                    uint2* __restrict__ ranges, int npass, int bits,
+                                                                    uint32_t* __restrict__ hist, uint32_t cap,
+                                                                    gsr_forward_info* info) {
+    __shared__ uint32_t s_h[kMaxPasses][kMaxBins];
+    __shared__ uint32_t s_wsum[kOffsThreads / 32 + 1];
+    for (int i = threadIdx.x; i < kMaxPasses * kMaxBins; i += kOffsThreads) (&s_h[0][0])[i] = 0;
+    if (threadIdx.x == 0) info->overflow = (uint32_t)info->num_rendered > cap ? 1 : 0;
+    __syncthreads();
+    const uint32_t mask = (1u << bits) - 1u;
+    const unsigned lane = lane_id();
+    const int warp = threadIdx.x >> 5;
+    uint32_t carry = 0;  // instances of the tiles before `base` (kept identical in every thread)
+    for (int base = 0; base < tiles; base += kOffsThreads) {
+        const int t = base + (int)threadIdx.x;
+        const uint32_t c = t < tiles ? tile_count[t] : 0u;
+        const uint32_t incl = warp_incl_scan(c);
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t w = s_wsum[lane];
+            const uint32_t wi = warp_incl_scan(w);
+            s_wsum[lane] = wi - w;
+            if (lane == 31) s_wsum[kOffsThreads / 32] = wi;
+        }
+        __syncthreads();
+        const uint32_t begin = carry + s_wsum[warp] + incl - c;
+        carry += s_wsum[kOffsThreads / 32];
+        if (t < tiles) {
+            ranges[t] = c ? make_uint2(begin, begin + c) : make_uint2(0u, 0u);  // empty tiles: (0, 0) as the reference leaves them
+            if (c)
+                for (int p = 0; p < npass; ++p) atomicAdd(&s_h[p][((uint32_t)t >> (p * bits)) & mask], c);
+        }
+        __syncthreads();
+    }
+    for (int i = threadIdx.x; i < npass * kMaxBins; i += kOffsThreads) hist[i] = (&s_h[0][0])[i];
+}
+
+// The reference's 64-bit key of list entry i: (tile << 32) | depth bits of its Gaussian (tests / debugging).
+template <typename TK>
+__global__ void __launch_bounds__(256) materialize_keys_kernel(const TK* __restrict__ tile_keys,
+                                                               const uint32_t* __restrict__ vals,
+                                                               const uint32_t* __restrict__ depth_bits,
+                                                               const uint32_t* __restrict__ r_ptr, uint32_t cap,
+                                                               uint64_t* __restrict__ out) {
     const uint32_t n = effective_n(r_ptr, cap);
-    const uint32_t i = 2u * (blockIdx.x * blockDim.x + threadIdx.x);
-    uint32_t t0 = 0xffffffffu, t1 = 0xffffffffu;
-    if (i + 1 < n) {
-        const ulonglong2 kk = *reinterpret_cast<const ulonglong2*>(keys + i);
-        t0 = (uint32_t)(kk.x >> 32);
-        t1 = (uint32_t)(kk.y >> 32);
-    } else if (i < n) {
-        t0 = (uint32_t)(keys[i] >> 32);
-    }
-    uint32_t tp = __shfl_up_sync(0xffffffffu, t1, 1);
-    if (lane_id() == 0 && i > 0 && i < n) tp = (uint32_t)(keys[i - 1] >> 32);
-    if (i < n) {
-        if (i == 0) ranges[t0].x = 0;
-        else if (tp != t0) { ranges[tp].y = i; ranges[t0].x = i; }
-        if (i == n - 1) ranges[t0].y = n;
-    }
-    if (i + 1 < n) {
-        if (t0 != t1) { ranges[t0].y = i + 1; ranges[t1].x = i + 1; }
-        if (i + 1 == n - 1) ranges[t1].y = n;
-    }
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ((uint64_t)tile_keys[i] << 32) | __ldg(depth_bits + vals[i]);
 }
 
 int higher_msb(uint32_t n) {  // number of bits needed to represent values < n (at least 1)
@@ -462,100 +495,162 @@ void tile_sort_plan(int tile_bits, int& passes, int& bits) {
 }
 
 size_t chunks_of(size_t n) { return (n + kSortChunk - 1) / kSortChunk; }
+size_t emit_chunks_of(size_t n) { return (n + kEmitChunk - 1) / kEmitChunk; }
+
+constexpr int kDepthMin = GSR_SORT_MINBLOCKS, kTileMin = GSR_TILE_SORT_MINBLOCKS;
 
 // Tile-bit passes are instantiated for 4..8-bit digits (the digit width is a compile-time constant so
-// the ballot ranking unrolls without predicate spills).
-template <int kBits>
-void launch_tile_pass_bits(unsigned grid, size_t smem, cudaStream_t s, const uint64_t* kin, const uint32_t* vin,
-                           uint64_t* kout, uint32_t* vout, const uint32_t* r_ptr, uint32_t cap, int shift,
-                           const uint32_t* hist, uint32_t* status, uint32_t* ticket) {
-    radix_pass_kernel<uint64_t, false, kBits><<<grid, kBlk, smem, s>>>(kin, vin, kout, vout, r_ptr, 0u, cap, shift, hist,
-                                                                      status, ticket);
+// the ballot ranking unrolls without predicate spills) and for 16- / 32-bit tile keys.
+template <typename TK, int kBits>
+cudaError_t tile_pass_bits(unsigned grid, cudaStream_t s, const TK* kin, const uint32_t* vin, TK* kout, uint32_t* vout,
+                           const uint32_t* r_ptr, uint32_t cap, int shift, const uint32_t* hist, uint32_t* status,
+                           uint32_t* ticket, bool attr_only) {
+    auto* fn = radix_pass_kernel<TK, false, kBits, kTileMin>;
+    const size_t smem = radix_pass_smem<TK>(kBits);
+    if (attr_only) return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    fn<<<grid, kBlk, smem, s>>>(kin, vin, kout, vout, r_ptr, 0u, cap, shift, hist, status, ticket);
+    return cudaSuccess;
 }
-void launch_tile_pass(int bits, unsigned grid, size_t smem, cudaStream_t s, const uint64_t* kin, const uint32_t* vin,
-                      uint64_t* kout, uint32_t* vout, const uint32_t* r_ptr, uint32_t cap, int shift,
-                      const uint32_t* hist, uint32_t* status, uint32_t* ticket) {
+template <typename TK>
+cudaError_t tile_pass(int bits, unsigned grid, cudaStream_t s, const TK* kin, const uint32_t* vin, TK* kout,
+                      uint32_t* vout, const uint32_t* r_ptr, uint32_t cap, int shift, const uint32_t* hist,
+                      uint32_t* status, uint32_t* ticket, bool attr_only = false) {
     switch (bits) {
-        case 4: launch_tile_pass_bits<4>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
-        case 5: launch_tile_pass_bits<5>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
-        case 6: launch_tile_pass_bits<6>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
-        case 7: launch_tile_pass_bits<7>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
-        default: launch_tile_pass_bits<8>(grid, smem, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket); break;
+        case 4: return tile_pass_bits<TK, 4>(grid, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket, attr_only);
+        case 5: return tile_pass_bits<TK, 5>(grid, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket, attr_only);
+        case 6: return tile_pass_bits<TK, 6>(grid, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket, attr_only);
+        case 7: return tile_pass_bits<TK, 7>(grid, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket, attr_only);
+        default: return tile_pass_bits<TK, 8>(grid, s, kin, vin, kout, vout, r_ptr, cap, shift, hist, status, ticket, attr_only);
     }
 }
-cudaError_t set_tile_pass_attributes() {
+cudaError_t set_pass_attributes() {
     cudaError_t e = cudaSuccess;
     const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, true, 8>, attr, (int)radix_pass_smem<uint32_t>(8));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, false, 8>, attr, (int)radix_pass_smem<uint32_t>(8));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 4>, attr, (int)radix_pass_smem<uint64_t>(4));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 5>, attr, (int)radix_pass_smem<uint64_t>(5));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 6>, attr, (int)radix_pass_smem<uint64_t>(6));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 7>, attr, (int)radix_pass_smem<uint64_t>(7));
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint64_t, false, 8>, attr, (int)radix_pass_smem<uint64_t>(8));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, true, 8, kDepthMin>, attr, (int)radix_pass_smem<uint32_t>(8));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(radix_pass_kernel<uint32_t, false, 8, kDepthMin>, attr, (int)radix_pass_smem<uint32_t>(8));
+    for (int bits = 4; bits <= 8 && e == cudaSuccess; ++bits) {
+        e = tile_pass<uint16_t>(bits, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, true);
+        if (e == cudaSuccess)
+            e = tile_pass<uint32_t>(bits, 0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, nullptr, nullptr, nullptr, true);
+    }
     return e;
+}
+cudaError_t ensure_pass_attributes() {
+    static unsigned long long attr_devices = 0;
+    return first_use_on_current_device(&attr_devices) ? set_pass_attributes() : cudaSuccess;
+}
+
+// ---- control regions (u32 words) --------------------------------------------------------------------
+// geometry:  [hist kMaxPasses*kMaxBins][tickets 8][pass status 4 x chunks(P) x kMaxBins]
+// binning:   [hist kMaxPasses*kMaxBins][tickets 8][tile_count tiles, padded][emit status 2 x emit_chunks(P)]
+//            [pass status passes x chunks(cap) x kMaxBins]
+constexpr size_t kCtlHeader = (size_t)kMaxPasses * kMaxBins + 8;
+size_t pad4(size_t n) { return (n + 3) & ~(size_t)3; }
+
+struct TileCtl {
+    uint32_t *hist, *tickets, *tile_count, *status;
+    unsigned long long* emit_status;
+    size_t head_words;  // everything before the pass status words
+};
+TileCtl tile_ctl(uint32_t* ctl, size_t P, size_t tiles) {
+    TileCtl c;
+    c.hist = ctl;
+    c.tickets = ctl + kMaxPasses * kMaxBins;
+    c.tile_count = ctl + kCtlHeader;
+    size_t o = kCtlHeader + pad4(tiles);
+    c.emit_status = reinterpret_cast<unsigned long long*>(ctl + o);
+    o += 2 * (emit_chunks_of(P) + 1);
+    c.status = ctl + o;
+    c.head_words = o;
+    return c;
+}
+
+template <typename TK>
+int binning_impl(int P, const Grid& g, const int32_t* radii, GeomView gv, BinView bv, uint32_t cap, ImageView iv,
+                 cudaStream_t s, int debug) {
+    const uint32_t* r_ptr = reinterpret_cast<const uint32_t*>(&gv.info->num_rendered);
+    int passes, bits;
+    tile_sort_plan(higher_msb((uint32_t)g.tiles), passes, bits);
+    const size_t nchunk = chunks_of((size_t)cap);
+    const TileCtl c = tile_ctl(bv.sort_ctl, (size_t)P, (size_t)g.tiles);
+    GSR_CUDA(cudaMemsetAsync(bv.sort_ctl, 0, sizeof(uint32_t) * (c.head_words + (size_t)passes * nchunk * kMaxBins), s));
+    TK* k_unsorted = reinterpret_cast<TK*>(bv.keys_unsorted);
+    TK* k_main = reinterpret_cast<TK*>(bv.keys);
+    TK* k_alt = reinterpret_cast<TK*>(bv.keys_alt);
+    {
+        StageScope scope(kStageEmitKeys, s);
+        emit_scan_kernel<TK><<<(unsigned)emit_chunks_of((size_t)P), kBlk, 0, s>>>(
+            g.gx, g.gy, gv.order, radii, gv.means2D, gv.info, cap, c.emit_status, c.tickets + 7, k_unsorted,
+            bv.vals_unsorted, c.tile_count);
+        GSR_AFTER_LAUNCH(s, debug);
+    }
+    {
+        StageScope scope(kStageTileRanges, s);
+        tile_offsets_kernel<<<1, kOffsThreads, 0, s>>>(g.tiles, c.tile_count, iv.ranges, passes, bits, c.hist, cap, gv.info);
+        GSR_AFTER_LAUNCH(s, debug);
+    }
+    StageScope scope(kStageSort, s);
+    // the unsorted lists stay intact; the last pass lands in (keys, point_list)
+    const TK* kin = k_unsorted;
+    const uint32_t* vin = bv.vals_unsorted;
+    bool to_main = (passes & 1) != 0;
+    for (int pass = 0; pass < passes; ++pass) {
+        TK* kout = to_main ? k_main : k_alt;
+        uint32_t* vout = to_main ? bv.point_list : bv.vals_alt;
+        GSR_CUDA(tile_pass<TK>(bits, (unsigned)nchunk, s, kin, vin, kout, vout, r_ptr, cap, pass * bits,
+                               c.hist + pass * kMaxBins, c.status + (size_t)pass * nchunk * kMaxBins, c.tickets + pass));
+        GSR_AFTER_LAUNCH(s, debug);
+        kin = kout;
+        vin = vout;
+        to_main = !to_main;
+    }
+    return GSR_OK;
 }
 
 }  // namespace
 
-// ---- control regions (u32 words): [hist kMaxPasses*kMaxBins][tickets 8][status ...] ----------
-constexpr size_t kCtlHeader = (size_t)kMaxPasses * kMaxBins + 8;
-
-size_t depth_sort_ctl_entries(size_t P) {
-    const size_t scan_status = 2 * ((P + kScanChunk - 1) / kScanChunk + 1);  // u64 words
-    return kCtlHeader + 4 * chunks_of(P) * kMaxBins + scan_status + 2;
+size_t depth_sort_ctl_entries(size_t P) { return kCtlHeader + 4 * chunks_of(P) * kMaxBins; }
+size_t tile_sort_ctl_entries(size_t cap, size_t P, size_t tiles) {
+    return kCtlHeader + pad4(tiles) + 2 * (emit_chunks_of(P) + 1) + (size_t)kMaxPasses * chunks_of(cap) * kMaxBins;
 }
-size_t tile_sort_ctl_entries(size_t cap) { return kCtlHeader + (size_t)kMaxPasses * chunks_of(cap) * kMaxBins; }
+int tile_key_bytes(int tiles) { return tiles <= 65536 ? 2 : 4; }
 
-// Per-Gaussian stage after preprocess: depth-order sort of all P (key, index) pairs, then the prefix
-// sum of tiles_touched in that order (writes info->num_rendered).
+// Per-Gaussian stage after preprocess: counts (num_visible, num_rendered) and the depth-order sort of the
+// visible (key, index) pairs; (order_keys, order)[0 .. num_visible) on return.
 int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
-    static unsigned long long attr_devices = 0;
-    if (first_use_on_current_device(&attr_devices)) GSR_CUDA(set_tile_pass_attributes());
+    GSR_CUDA(ensure_pass_attributes());
     const size_t nchunk = chunks_of((size_t)P);
     uint32_t* ctl = gv.sort_ctl;
     uint32_t* hist = ctl;
     uint32_t* tickets = ctl + kMaxPasses * kMaxBins;
     uint32_t* status = ctl + kCtlHeader;
-    uint32_t* scan_status = status + 4 * nchunk * kMaxBins;
-    scan_status += ((reinterpret_cast<uintptr_t>(scan_status) & 7) ? 1 : 0);
     GSR_CUDA(cudaMemsetAsync(ctl, 0, sizeof(uint32_t) * depth_sort_ctl_entries((size_t)P), s));
-    {
-        StageScope scope(kStageDepthSort, s);
-        const int hblocks = (int)min((size_t)(148 * 8), ((size_t)P + kBlk - 1) / kBlk);
-        radix_hist_kernel<uint32_t><<<hblocks, kBlk, 0, s>>>(reinterpret_cast<const uint32_t*>(gv.depths), nullptr,
-                                                            (uint32_t)P, 0u, 0, 8, 4, hist);
+    StageScope scope(kStageDepthSort, s);
+    const int hblocks = (int)min((size_t)(148 * 8), ((size_t)P + kBlk - 1) / kBlk);
+    depth_hist_kernel<<<hblocks, kBlk, 0, s>>>(reinterpret_cast<const uint32_t*>(gv.depths), gv.tiles_touched,
+                                               (uint32_t)P, hist, gv.info);
+    GSR_AFTER_LAUNCH(s, debug);
+    const size_t smem = radix_pass_smem<uint32_t>(8);
+    const uint32_t* nvis_ptr = reinterpret_cast<const uint32_t*>(&gv.info->num_visible);
+    // depths (identity payload, culled dropped) -> A -> B -> A -> B: 4 passes end in (order_keys, order)
+    const uint32_t* kin = reinterpret_cast<const uint32_t*>(gv.depths);
+    const uint32_t* vin = nullptr;
+    uint32_t* kout = gv.order_keys_alt;
+    uint32_t* vout = gv.order_alt;
+    for (int pass = 0; pass < 4; ++pass) {
+        if (pass == 0)
+            radix_pass_kernel<uint32_t, true, 8, kDepthMin><<<(unsigned)nchunk, kBlk, smem, s>>>(
+                kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 0, hist, status, tickets);
+        else
+            radix_pass_kernel<uint32_t, false, 8, kDepthMin><<<(unsigned)nchunk, kBlk, smem, s>>>(
+                kin, vin, kout, vout, nvis_ptr, 0u, (uint32_t)P, 8 * pass, hist + pass * kMaxBins,
+                status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
         GSR_AFTER_LAUNCH(s, debug);
-        const size_t smem = radix_pass_smem<uint32_t>(8);
-        // depths (identity payload) -> A -> B -> A -> B ... 4 passes end in (order_keys, order)
-        const uint32_t* kin = reinterpret_cast<const uint32_t*>(gv.depths);
-        const uint32_t* vin = nullptr;
-        uint32_t* kout = gv.order_keys_alt;
-        uint32_t* vout = gv.order_alt;
-        for (int pass = 0; pass < 4; ++pass) {
-            if (pass == 0)
-                radix_pass_kernel<uint32_t, true, 8><<<(unsigned)nchunk, kBlk, smem, s>>>(
-                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, hist + pass * kMaxBins,
-                    status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
-            else
-                radix_pass_kernel<uint32_t, false, 8><<<(unsigned)nchunk, kBlk, smem, s>>>(
-                    kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 8 * pass, hist + pass * kMaxBins,
-                    status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
-            GSR_AFTER_LAUNCH(s, debug);
-            kin = kout;
-            vin = vout;
-            const bool to_main = (kout == gv.order_keys_alt);
-            kout = to_main ? gv.order_keys : gv.order_keys_alt;
-            vout = to_main ? gv.order : gv.order_alt;
-        }
-    }
-    {
-        StageScope scope(kStageScan, s);
-        const unsigned blocks = (unsigned)(((size_t)P + kScanChunk - 1) / kScanChunk);
-        scan_sorted_tiles_kernel<<<blocks, kBlk, 0, s>>>(P, gv.order, gv.tiles_touched, gv.point_offsets,
-                                                        reinterpret_cast<unsigned long long*>(scan_status), tickets + 4,
-                                                        gv.info);
-        GSR_AFTER_LAUNCH(s, debug);
+        kin = kout;
+        vin = vout;
+        const bool to_main = (kout == gv.order_keys_alt);
+        kout = to_main ? gv.order_keys : gv.order_keys_alt;
+        vout = to_main ? gv.order : gv.order_alt;
     }
     return GSR_OK;
 }
@@ -563,52 +658,32 @@ int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
 int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinView bv, int64_t cap64,
                    ImageView iv, cudaStream_t s, int debug) {
     const uint32_t cap = (uint32_t)cap64;
-    const uint32_t* r_ptr = reinterpret_cast<const uint32_t*>(&gv.info->num_rendered);
-    publish_info_kernel<<<1, 1, 0, s>>>(cap, gv.info);
-    GSR_AFTER_LAUNCH(s, debug);
-    GSR_CUDA(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)g.tiles, s));
+    if (cap == 0) {
+        publish_info_kernel<<<1, 1, 0, s>>>(cap, gv.info);
+        GSR_AFTER_LAUNCH(s, debug);
+        GSR_CUDA(cudaMemsetAsync(iv.ranges, 0, sizeof(uint2) * (size_t)g.tiles, s));
+        return GSR_OK;
+    }
+    GSR_CUDA(ensure_pass_attributes());
+    return tile_key_bytes(g.tiles) == 2 ? binning_impl<uint16_t>(P, g, radii, gv, bv, cap, iv, s, debug)
+                                        : binning_impl<uint32_t>(P, g, radii, gv, bv, cap, iv, s, debug);
+}
+
+int launch_materialize_keys(int P, const Grid& g, GeomView gv, BinView bv, int64_t cap64, int sorted, uint64_t* out,
+                            cudaStream_t s) {
+    (void)P;
+    const uint32_t cap = (uint32_t)cap64;
     if (cap == 0) return GSR_OK;
-
-    {
-        StageScope scope(kStageEmitKeys, s);
-        emit_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, g.gx, g.gy, gv.order_keys, gv.order, radii, gv.means2D,
-                                                         gv.point_offsets, gv.info, cap, bv.keys_unsorted,
-                                                         bv.vals_unsorted);
-        GSR_AFTER_LAUNCH(s, debug);
-    }
-
-    int passes, bits;
-    tile_sort_plan(higher_msb((uint32_t)g.tiles), passes, bits);
-    const size_t nchunk = chunks_of((size_t)cap);
-    uint32_t* ctl = bv.sort_ctl;
-    uint32_t* hist = ctl;
-    uint32_t* tickets = ctl + kMaxPasses * kMaxBins;
-    uint32_t* status = ctl + kCtlHeader;
-    GSR_CUDA(cudaMemsetAsync(ctl, 0, sizeof(uint32_t) * (kCtlHeader + (size_t)passes * nchunk * kMaxBins), s));
-    {
-        StageScope scope(kStageSort, s);
-        const int hblocks = (int)min((size_t)(148 * 8), ((size_t)cap + kBlk - 1) / kBlk);
-        radix_hist_kernel<uint64_t><<<hblocks, kBlk, 0, s>>>(bv.keys_unsorted, r_ptr, 0u, cap, 32, bits, passes, hist);
-        GSR_AFTER_LAUNCH(s, debug);
-        const size_t smem = radix_pass_smem<uint64_t>(bits);
-        // the unsorted lists stay intact; the last pass lands in (keys, point_list)
-        const uint64_t* kin = bv.keys_unsorted;
-        const uint32_t* vin = bv.vals_unsorted;
-        bool to_main = (passes & 1) != 0;
-        for (int pass = 0; pass < passes; ++pass) {
-            uint64_t* kout = to_main ? bv.keys : bv.keys_alt;
-            uint32_t* vout = to_main ? bv.point_list : bv.vals_alt;
-            launch_tile_pass(bits, (unsigned)nchunk, smem, s, kin, vin, kout, vout, r_ptr, cap, 32 + pass * bits,
-                             hist + pass * kMaxBins, status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
-            GSR_AFTER_LAUNCH(s, debug);
-            kin = kout;
-            vin = vout;
-            to_main = !to_main;
-        }
-    }
-    StageScope scope(kStageTileRanges, s);
-    tile_ranges_kernel<<<(cap + 511) / 512, 256, 0, s>>>(bv.keys, r_ptr, cap, iv.ranges);
-    GSR_AFTER_LAUNCH(s, debug);
+    const uint32_t* r_ptr = reinterpret_cast<const uint32_t*>(&gv.info->num_rendered);
+    const uint32_t* dbits = reinterpret_cast<const uint32_t*>(gv.depths);
+    const void* tk = sorted ? (const void*)bv.keys : (const void*)bv.keys_unsorted;
+    const uint32_t* vals = sorted ? bv.point_list : bv.vals_unsorted;
+    const unsigned grid = (cap + 255) / 256;
+    if (tile_key_bytes(g.tiles) == 2)
+        materialize_keys_kernel<uint16_t><<<grid, 256, 0, s>>>(static_cast<const uint16_t*>(tk), vals, dbits, r_ptr, cap, out);
+    else
+        materialize_keys_kernel<uint32_t><<<grid, 256, 0, s>>>(static_cast<const uint32_t*>(tk), vals, dbits, r_ptr, cap, out);
+    GSR_AFTER_LAUNCH(s, 0);
     return GSR_OK;
 }
 

@@ -40,7 +40,7 @@ int cuda_fail(cudaError_t e);  // records e for gsr_last_cuda_error(), returns G
 
 // ---- optional per-stage device timing (gsr_stage_timing_*; off by default) -----------------
 enum Stage {
-    kStagePreprocess = 0, kStageDepthSort, kStageScan, kStageEmitKeys, kStageSort, kStageTileRanges, kStageBlendFwd,
+    kStagePreprocess = 0, kStageDepthSort, kStageEmitKeys, kStageTileRanges, kStageSort, kStageBlendFwd,
     kStageBlendBwd, kStagePreprocessBwd, kStageCount
 };
 bool stage_timing_on();
@@ -80,21 +80,20 @@ struct GeomView {
     float4* conic_opacity;
     float4* rgb;  // .w carries the clamped bits
     uint32_t* tiles_touched;
-    uint32_t* point_offsets;   // inclusive prefix of tiles_touched in DEPTH order (slot k of `order`)
     gsr_forward_info* info;
     float* grad_accum;  // [P,12]
-    uint32_t* order_keys;      // [P] depth bits, ascending; culled Gaussians (0xFFFFFFFF) last
-    uint32_t* order;           // [P] Gaussian index of slot k
+    uint32_t* order_keys;      // [num_visible] depth bits of the visible Gaussians, ascending (stable)
+    uint32_t* order;           // [num_visible] Gaussian index of depth-order slot k
     uint32_t* order_keys_alt;  // ping-pong partners of the per-Gaussian sort
     uint32_t* order_alt;
     uint32_t* sort_ctl;        // histograms, tickets, look-back status words
 };
-struct BinView {
-    uint64_t* keys_unsorted;
+struct BinView {           // tile keys are u16 up to 65536 tiles, else u32 (tile_key_bytes)
+    void* keys_unsorted;   // tile id of every instance, emitted in DEPTH order
     uint32_t* vals_unsorted;
-    uint64_t* keys;
+    void* keys;            // sorted by tile (stable)
     uint32_t* point_list;
-    uint64_t* keys_alt;   // radix-sort ping-pong partner of (keys, point_list)
+    void* keys_alt;        // radix-sort ping-pong partner of (keys, point_list)
     uint32_t* vals_alt;
     uint32_t* sort_ctl;   // histograms, tickets, look-back status words
 };
@@ -108,7 +107,7 @@ struct ImageView {
 inline GeomView offset_rows(GeomView v, size_t r) {
     v.depths += r; v.means2D += r; v.conic_opacity += r; v.rgb += r; v.tiles_touched += r;
     v.grad_accum += 12 * r;
-    v.info = nullptr;  // slot calls do not maintain num_visible (the workspace may be a peer's)
+    v.info = nullptr;  // the counts are taken by the depth-order stage of the rank that renders the view
     return v;
 }
 void compute_layout(int P, int W, int H, int64_t cap, gsr_layout* L);
@@ -119,7 +118,8 @@ ImageView image_view(void* ws, const gsr_layout& L);
 // u32 entries of the control regions of the per-Gaussian depth sort (+ prefix sum) and of the
 // per-instance tile sort.
 size_t depth_sort_ctl_entries(size_t P);
-size_t tile_sort_ctl_entries(size_t cap);
+size_t tile_sort_ctl_entries(size_t cap, size_t P, size_t tiles);
+int tile_key_bytes(int tiles);   // 2 up to 65536 tiles, else 4
 
 struct RawMode;
 // ---- stage launchers (each returns a gsr_status) ------------------------------------------
@@ -130,9 +130,14 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
                       float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug,
                       const struct RawMode& rm);
 
-// Depth-order sort of the P (depth bits, index) pairs + prefix sum of tiles_touched in that order;
-// writes info->num_rendered on the device.
+// Counts (info->num_visible, info->num_rendered, on the device) and the depth-order sort of the visible
+// (depth bits, index) pairs.
 int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug);
+
+// The reference's 64-bit (tile << 32 | depth bits) key of every list entry, unsorted (emission order) or sorted,
+// rebuilt from the stored tile ids and depths[index] (tests / debugging; nothing on the render path reads it).
+int launch_materialize_keys(int P, const Grid& g, GeomView gv, BinView bv, int64_t cap, int sorted, uint64_t* out,
+                            cudaStream_t s);
 
 int launch_binning(int P, const Grid& g, const int32_t* radii, GeomView gv, BinView bv,
                    int64_t cap, ImageView iv, cudaStream_t s, int debug);

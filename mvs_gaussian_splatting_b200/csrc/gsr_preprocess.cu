@@ -333,7 +333,6 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
             if (alive) V.conic_local[idx] = conic;
         }
     }
-    if (lane == 0 && vis && V.gv.info) atomicAdd(&V.gv.info->num_visible, __popc(vis));
   }  // views
 }
 

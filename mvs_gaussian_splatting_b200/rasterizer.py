@@ -108,23 +108,34 @@ class RasterContext:
         return _native.workspace_layout(self.P, self.W, self.H, self.capacity)
 
     def array(self, name: str) -> torch.Tensor:
-        """Typed view of one workspace array (tests / tools only)."""
+        """Typed view of one workspace array (tests / tools only).  "keys" / "keys_unsorted" are the reference's
+        64-bit (tile << 32 | depth bits) lists: the render path stores tile ids and indices only, so they are
+        rebuilt on request by gsr_materialize_keys into a new tensor ([capacity] int64, first num_rendered valid)."""
         L = self.layout()
         P, C, W, H = max(self.P, 1), max(self.capacity, 1), self.W, self.H
         tiles = ((W + 15) // 16) * ((H + 15) // 16)
+        if name in ("keys", "keys_unsorted"):
+            dev = self.geom_ws.device
+            out = torch.zeros(C, dtype=torch.int64, device=dev)
+            with torch.cuda.device(dev):
+                stream = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+                _native.check(_native.lib().gsr_materialize_keys(
+                    self.P, W, H, _ptr(self.geom_ws), _ptr(self.binning_ws), self.capacity,
+                    1 if name == "keys" else 0, _ptr(out), stream), "gsr_materialize_keys")
+            return out
+        tk = torch.int16 if L.b_key_bytes == 2 else torch.int32
         spec = {
             "depths": (self.geom_ws, L.g_depths, torch.float32, (P,)),
             "means2D": (self.geom_ws, L.g_means2D, torch.float32, (P, 2)),
             "conic_opacity": (self.geom_ws, L.g_conic_opacity, torch.float32, (P, 4)),
             "rgb": (self.geom_ws, L.g_rgb, torch.float32, (P, 4)),
             "tiles_touched": (self.geom_ws, L.g_tiles_touched, torch.int32, (P,)),
-            "point_offsets": (self.geom_ws, L.g_point_offsets, torch.int32, (P,)),
             "grad_accum": (self.geom_ws, L.g_grad_accum, torch.float32, (P, 12)),
             "order_keys": (self.geom_ws, L.g_order_keys, torch.int32, (P,)),
             "order": (self.geom_ws, L.g_order, torch.int32, (P,)),
-            "keys_unsorted": (self.binning_ws, L.b_keys_unsorted, torch.int64, (C,)),
+            "tiles_unsorted": (self.binning_ws, L.b_keys_unsorted, tk, (C,)),
             "values_unsorted": (self.binning_ws, L.b_vals_unsorted, torch.int32, (C,)),
-            "keys": (self.binning_ws, L.b_keys, torch.int64, (C,)),
+            "tiles_sorted": (self.binning_ws, L.b_keys, tk, (C,)),
             "point_list": (self.binning_ws, L.b_point_list, torch.int32, (C,)),
             "ranges": (self.image_ws, L.i_ranges, torch.int32, (tiles, 2)),
             "final_T": (self.image_ws, L.i_final_T, torch.float32, (H, W)),

@@ -40,7 +40,7 @@ def test_status_strings(native):
         assert L.gsr_status_string(code)
     assert L.gsr_last_cuda_error() == b""
     names = [L.gsr_stage_name(i).decode() for i in range(L.gsr_stage_count())]
-    assert names == ["preprocess", "depth_sort", "scan", "emit_keys", "radix_sort", "tile_ranges", "blend_forward",
+    assert names == ["preprocess", "depth_sort", "emit_keys", "tile_ranges", "radix_sort", "blend_forward",
                      "blend_backward", "preprocess_backward"]
 
 
@@ -49,14 +49,15 @@ def test_workspace_sizes_and_layout(native):
     g, b, i = native.workspace_bytes(P, W, H, C)
     L = native.workspace_layout(P, W, H, C)
     assert (g, b, i) == (L.geom_bytes, L.binning_bytes, L.image_bytes)
-    # per Gaussian: depth 4 + mean2D 8 + conic 16 + rgb 16 + tiles 4 + offsets 4 + accumulators 48
-    # + depth-order sort (key, index) x 2 = 16, plus the sort's control words (1 KB per 4096 Gaussians x 4 passes)
-    assert g >= 116 * P and g < 118 * P + (1 << 20)
-    # per instance: three (u64 key, u32 value) pairs
-    assert b >= 36 * C
+    # per Gaussian: depth 4 + mean2D 8 + conic 16 + rgb 16 + tiles 4 + accumulators 48
+    # + depth-order sort (key, index) x 2 = 16, plus the sort's control words (1 KB per 6144 Gaussians x 4 passes)
+    assert g >= 112 * P and g < 114 * P + (1 << 20)
+    # per instance: three (u16 tile id, u32 Gaussian index) pairs (up to 65536 tiles; u32 tile ids beyond)
+    assert L.b_key_bytes == 2 and b >= 18 * C and b < 19 * C + (1 << 20)
+    assert native.workspace_layout(P, 8192, 8192, C).b_key_bytes == 4
     tiles = 50 * 50
     assert i >= 8 * tiles + 8 * W * H
-    offs = [L.g_depths, L.g_means2D, L.g_conic_opacity, L.g_rgb, L.g_tiles_touched, L.g_point_offsets, L.g_info,
+    offs = [L.g_depths, L.g_means2D, L.g_conic_opacity, L.g_rgb, L.g_tiles_touched, L.g_info,
             L.g_grad_accum, L.g_order_keys, L.g_order, L.g_order_keys_alt, L.g_order_alt, L.g_sort_ctl]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs)
     # the geometry and image layouts do not depend on the instance capacity

@@ -89,7 +89,12 @@ def check_forward(cuda, oracle, P, W, H, D, M, seed, threads=8):
         dbits = pre["depths"].view(np.uint32)
         want_order = np.flatnonzero(vis)[np.argsort(dbits[vis], kind="stable")]
         np.testing.assert_array_equal(order[:nvis], want_order)
-        np.testing.assert_array_equal(np.sort(order[nvis:]), np.flatnonzero(~vis))
+        # culled Gaussians are dropped by the first pass of the depth sort: the order holds the visible ones only
+        np.testing.assert_array_equal(ctx.array("order_keys").cpu().numpy().view(np.uint32)[:nvis], dbits[want_order])
+        # what the render path stores per instance is the tile id (the key's high half) + the index
+        tk = ctx.array("tiles_sorted").cpu().numpy()
+        np.testing.assert_array_equal(tk.view(np.uint16 if tk.dtype == np.int16 else np.uint32)[:R].astype(np.uint64),
+                                      binned["keys"] >> np.uint64(32))
         np.testing.assert_array_equal(ctx.array("keys").cpu().numpy().view(np.uint64)[:R], binned["keys"])
         np.testing.assert_array_equal(ctx.array("point_list").cpu().numpy().view(np.uint32)[:R], binned["point_list"])
     np.testing.assert_array_equal(ctx.array("ranges").cpu().numpy().view(np.uint32), binned["ranges"])

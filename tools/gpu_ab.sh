@@ -1,0 +1,16 @@
+#!/bin/bash
+# usage: tools/gpu_ab.sh TAG [pytest-targets|-] lib...  — parity tests on the default library, then config-3 stage times per variant
+TAG=$1; shift
+TESTS=$1; shift
+OUT=gpurun_out; mkdir -p $OUT
+if [ "$TESTS" != "-" ]; then
+  timeout 1200 python -m pytest $TESTS -m gpu -q -x --timeout 900 > $OUT/${TAG}_pytest.log 2>&1
+  echo "pytest exit $?"; tail -15 $OUT/${TAG}_pytest.log
+fi
+for lib in default "$@"; do
+  for i in 1 2; do
+    if [ "$lib" = default ]; then unset GSRAST_B200_LIB; else export GSRAST_B200_LIB=$PWD/build/variants/$lib.so; fi
+    timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-extras 2> $OUT/${TAG}_ab.err | python -c "
+import sys,json; d=json.loads(sys.stdin.read()); print('$lib', round(d['ms_per_step'],4), 'e2e', round(d['e2e']['ms_per_step'],3), {k:round(v['ms'],3) for k,v in d['stages'].items()})" || tail -5 $OUT/${TAG}_ab.err
+  done
+done 2>&1 | tee $OUT/${TAG}_ab.txt
