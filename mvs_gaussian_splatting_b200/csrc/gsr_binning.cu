@@ -59,22 +59,24 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
     return v;
 }
 
-// Block-wide exclusive scan of one value per thread (256 threads); returns the exclusive prefix and
-// the block total through `total`.  s_warp: 9 words.
+// Block-wide exclusive scan of one value per thread (kThreads threads); returns the exclusive prefix and
+// the block total through `total`.  s_warp: kThreads / 32 + 1 words.
 constexpr int kBlk = 256;
+template <int kThreads = kBlk>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp, uint32_t& total) {
+    constexpr int kW = kThreads / 32;
     const uint32_t incl = warp_incl_scan(v);
     const int warp = threadIdx.x >> 5;
     if (lane_id() == 31) s_warp[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-        uint32_t w = lane_id() < kBlk / 32 ? s_warp[lane_id()] : 0u;
+        uint32_t w = lane_id() < kW ? s_warp[lane_id()] : 0u;
         uint32_t wi = warp_incl_scan(w);
-        if (lane_id() < kBlk / 32) s_warp[lane_id()] = wi - w;
-        if (lane_id() == kBlk / 32 - 1) s_warp[kBlk / 32] = wi;
+        if (lane_id() < kW) s_warp[lane_id()] = wi - w;
+        if (lane_id() == kW - 1) s_warp[kW] = wi;
     }
     __syncthreads();
-    total = s_warp[kBlk / 32];
+    total = s_warp[kW];
     const uint32_t r = s_warp[warp] + incl - v;
     __syncthreads();
     return r;
@@ -92,39 +94,15 @@ __global__ void publish_info_kernel(uint32_t cap, gsr_forward_info* info) {
     info->overflow = (uint32_t)info->num_rendered > cap ? 1 : 0;
 }
 
-// Decoupled look-back over ticketed chunks (status word: flag << 32 | value; flag 1 = chunk aggregate,
-// 2 = inclusive prefix).  Called by warp 0 of chunk b with the chunk total; returns the exclusive prefix.
-__device__ __forceinline__ uint32_t lookback_prefix(unsigned long long* status, uint32_t b, uint32_t total) {
-    const unsigned lane = lane_id();
-    uint32_t prefix = 0;
-    if (b == 0) {
-        if (lane == 0) st_relaxed64(status, (2ull << 32) | total);
-        return 0;
-    }
-    if (lane == 0) st_relaxed64(status + b, (1ull << 32) | total);
-    int base = (int)b - 1;
-    while (true) {
-        const int j = base - (int)lane;
-        unsigned long long s = 2ull << 32;  // before the first chunk: inclusive 0
-        if (j >= 0) {
-            do { s = ld_relaxed64(status + j); } while ((s >> 32) == 0);
-        }
-        const unsigned incl = __ballot_sync(0xffffffffu, (s >> 32) == 2);
-        const int first = __ffs(incl) - 1;  // nearest chunk holding an inclusive prefix, or -1
-        uint32_t val = (first < 0 || (int)lane <= first) ? (uint32_t)s : 0u;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-        prefix += val;
-        if (first >= 0) break;
-        base -= 32;
-    }
-    if (lane == 0) st_relaxed64(status + b, (2ull << 32) | (prefix + total));
-    return prefix;
-}
-
 // =========================== stable LSD radix sort, one kernel per pass ====================
+// A/B on B200 (config 3, tools/gpu_ab.sh): 256 threads x 8/12/16/20/24/32 items, 384 x 16, 512 x 8/12/16/20, 768 x 12,
+// 1024 x 8, at 1-4 CTAs/SM.  The passes are latency-bound (dependent ballot / shared-atomic chains per key, three
+// CTA barriers and a look-back per chunk), so twice the warps on half the keys per thread wins: 512 x 16 at 2 CTAs/SM.
 #ifndef GSR_SORT_ITEMS
-#define GSR_SORT_ITEMS 24   // A/B on B200 (config 3): 8/12/16/20/24/32 items -> 24 at 2 CTAs/SM is fastest and spill-free
+#define GSR_SORT_ITEMS 16
+#endif
+#ifndef GSR_SORT_REORDER_FIRST
+#define GSR_SORT_REORDER_FIRST 1   // shared-memory reorder before (1) or after (0) the look-back; measured per configuration
 #endif
 #ifndef GSR_SORT_MINBLOCKS
 #define GSR_SORT_MINBLOCKS 2
@@ -132,9 +110,15 @@ __device__ __forceinline__ uint32_t lookback_prefix(unsigned long long* status, 
 #ifndef GSR_TILE_SORT_MINBLOCKS
 #define GSR_TILE_SORT_MINBLOCKS 2
 #endif
+constexpr int kMaxBinsC = 256;
+#ifndef GSR_SORT_THREADS
+#define GSR_SORT_THREADS 512
+#endif
+constexpr int kSortThreads = GSR_SORT_THREADS;
 constexpr int kSortItems = GSR_SORT_ITEMS;      // per thread
-constexpr int kSortChunk = kBlk * kSortItems;   // 6144 items per ticket
-constexpr int kSortWarps = kBlk / 32;
+constexpr int kSortChunk = kSortThreads * kSortItems;   // 8192 items per ticket
+constexpr int kSortWarps = kSortThreads / 32;
+static_assert(kSortThreads >= kMaxBinsC && kSortThreads <= 1024 && kSortThreads % 32 == 0, "one thread per digit");
 constexpr int kSortWarpSpan = 32 * kSortItems;  // consecutive items owned by one warp
 constexpr int kMaxBins = 256;
 constexpr int kMaxPasses = 4;
@@ -195,7 +179,7 @@ __global__ void __launch_bounds__(kBlk) depth_hist_kernel(const uint32_t* __rest
 // ones only.  status: [chunks][bins] words, zeroed before the launch; ticket: zeroed.  hist: global digit
 // counts of the items this pass keeps.
 template <typename K, bool kFirst, int kBits, int kMinBlocks>
-__global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+__global__ void __launch_bounds__(kSortThreads, kMinBlocks) radix_pass_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                                                           K* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                                                           const uint32_t* __restrict__ n_ptr, uint32_t n_host, uint32_t cap,
                                                           int shift, const uint32_t* __restrict__ hist,
@@ -206,13 +190,13 @@ __global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* _
     K* s_keys = reinterpret_cast<K*>(s_cnt + kSortWarps * (1 << kBits));              // [kSortChunk]
     __shared__ uint32_t s_binstart[kMaxBins];  // exclusive start of each digit inside this chunk
     __shared__ uint32_t s_gbase[kMaxBins];     // global position of sorted-chunk item i of digit d: s_gbase[d] + i
-    __shared__ uint32_t s_warp[kBlk / 32 + 1];
+    __shared__ uint32_t s_warp[kSortThreads / 32 + 1];
     __shared__ uint32_t s_b;
 
     constexpr int bins = 1 << kBits;
     const uint32_t n = n_ptr ? effective_n(n_ptr, cap) : n_host;
     if (threadIdx.x == 0) s_b = atomicAdd(ticket, 1u);
-    for (int d = threadIdx.x; d < bins * kSortWarps; d += kBlk) s_cnt[d] = 0;
+    for (int d = threadIdx.x; d < bins * kSortWarps; d += kSortThreads) s_cnt[d] = 0;
     __syncthreads();
     const uint32_t b = s_b;
     const size_t start = (size_t)b * kSortChunk;
@@ -267,11 +251,27 @@ __global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* _
         if (b != 0) st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagAgg | h);
     }
     uint32_t count, total;
-    const uint32_t binstart = block_excl_scan(h, s_warp, count);  // position of digit d in the sorted chunk; items kept
+    const uint32_t binstart = block_excl_scan<kSortThreads>(h, s_warp, count);  // position of digit d in the sorted chunk; items kept
     const uint32_t gh = ((int)threadIdx.x < bins) ? __ldg(hist + threadIdx.x) : 0u;
-    const uint32_t gstart = block_excl_scan(gh, s_warp, total);   // global start of digit d
+    const uint32_t gstart = block_excl_scan<kSortThreads>(gh, s_warp, total);   // global start of digit d
+    if ((int)threadIdx.x < bins) s_binstart[threadIdx.x] = binstart;
+    __syncthreads();
+#if GSR_SORT_REORDER_FIRST
+    // reorder through shared memory: chunk-sorted position = binstart[d] + warp offset + rank
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const size_t i = wbase + (size_t)k * 32 + lane;
+        const bool valid = kFirst ? (uint32_t)key[k] != kInvalidDepthKey : i < n;
+        if (valid) {
+            const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
+            const uint32_t pos = s_binstart[d] + my[d] + rank[k];
+            s_keys[pos] = key[k];
+            s_vals[pos] = kFirst ? (uint32_t)i : __ldg(vals_in + i);
+        }
+    }
     if ((int)threadIdx.x < bins) {
-        // decoupled look-back, kWin predecessors per round trip
+        // decoupled look-back, kWin predecessors per round trip (done before the shared-memory reorder: the sooner
+        // this chunk's inclusive prefix is out, the shorter its successors' walks — measured both ways)
         constexpr int kWin = 16;
         uint32_t excl = 0;
         int prev = (int)b - 1;
@@ -299,11 +299,42 @@ __global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* _
             }
         }
         st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagIncl | (excl + h));
-        s_binstart[threadIdx.x] = binstart;
+        s_gbase[threadIdx.x] = gstart + excl - binstart;
+    }
+#else
+    if ((int)threadIdx.x < bins) {
+        // decoupled look-back, kWin predecessors per round trip (done before the shared-memory reorder: the sooner
+        // this chunk's inclusive prefix is out, the shorter its successors' walks — measured both ways)
+        constexpr int kWin = 16;
+        uint32_t excl = 0;
+        int prev = (int)b - 1;
+        bool done = (b == 0);
+        const uint32_t* col = status + threadIdx.x;
+        while (!done) {
+            uint32_t sw[kWin];
+#pragma unroll
+            for (int j = 0; j < kWin; ++j) {
+                const int idx = prev - j;
+                sw[j] = idx >= 0 ? ld_relaxed(col + (size_t)idx * bins) : kFlagIncl;
+            }
+            bool halt = false;
+#pragma unroll
+            for (int j = 0; j < kWin; ++j) {
+                const uint32_t f = sw[j] >> 30;
+                if (!halt && !done) {
+                    if (f == 0) halt = true;  // not published yet: retry from here
+                    else {
+                        excl += sw[j] & kValMask;
+                        --prev;
+                        if (f == 2) done = true;
+                    }
+                }
+            }
+        }
+        st_relaxed(status + (size_t)b * bins + threadIdx.x, kFlagIncl | (excl + h));
         s_gbase[threadIdx.x] = gstart + excl - binstart;
     }
     __syncthreads();
-
     // reorder through shared memory: chunk-sorted position = binstart[d] + warp offset + rank
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
@@ -316,11 +347,12 @@ __global__ void __launch_bounds__(kBlk, kMinBlocks) radix_pass_kernel(const K* _
             s_vals[pos] = kFirst ? (uint32_t)i : __ldg(vals_in + i);
         }
     }
+#endif
     __syncthreads();
     // coalesced runs: consecutive threads hold consecutive items of the same digit
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
-        const uint32_t i = (uint32_t)k * kBlk + threadIdx.x;
+        const uint32_t i = (uint32_t)k * kSortThreads + threadIdx.x;
         if (i < count) {
             const K kk = s_keys[i];
             const uint32_t d = (uint32_t)(kk >> shift) & mask;
@@ -339,12 +371,59 @@ constexpr size_t radix_pass_smem(int bits) {
 // =========================== prefix sum + key emission (duplicateWithKeys) ==================
 // One chunk = kEmitSlots consecutive slots of the depth order per thread (one 16-byte load of `order`).  Per slot:
 // the splat's tile rect from (radii, means2D) — its area IS tiles_touched.  The chunk's first list position comes
-// from a decoupled look-back over the chunk totals (the reference's InclusiveSum, never stored).  Entries are then
-// written by a load-balanced search: list position p of the chunk belongs to the last slot whose exclusive offset
-// is <= p, so consecutive threads write consecutive positions whatever the rect sizes (a screen-filling splat is
-// spread over the whole CTA).  Entry t of a rect (row-major, y outer) is tile (y0 + t / w) * gx + x0 + t % w.
+// from a decoupled look-back over the chunk totals (the reference's InclusiveSum, never stored): the chunk
+// publishes its total as soon as it is known and only asks for its prefix AFTER it has expanded its rects into a
+// shared staging window — the expansion needs no global position, so the predecessors' totals have landed by then.
+// Entry t of a rect (row-major, y outer) is tile (y0 + t / w) * gx + x0 + t % w; rects of up to kEmitSmall tiles are
+// expanded by the owning lane, larger ones by the whole warp (a screen-filling splat no longer serialises thousands
+// of stores on one thread).  The staged window then goes out with coalesced stores, one RED per entry counting the
+// instances of its tile.
 constexpr int kEmitSlots = 4;
 constexpr int kEmitChunk = kBlk * kEmitSlots;
+constexpr int kEmitSmall = 12;
+// The per-tile instance counters are kept in kTileReplicas copies (chunk b adds to copy b mod kTileReplicas) and
+// summed by tile_offsets_kernel: 8 M REDs into the ~250 cache lines of one copy saturate the L2 slices that hold the
+// busy screen-centre tiles (ncu: hottest slice at 88 % while the average sits at 28 %).
+constexpr int kTileReplicas = 16;
+
+__device__ __forceinline__ void publish_aggregate(unsigned long long* status, uint32_t b, uint32_t total) {
+    st_relaxed64(status + b, ((b == 0 ? 2ull : 1ull) << 32) | total);
+}
+// Exclusive prefix of chunk b (warp 0, after publish_aggregate); upgrades the chunk's word to an inclusive prefix.
+__device__ __forceinline__ uint32_t lookback_prefix(unsigned long long* status, uint32_t b, uint32_t total) {
+    if (b == 0) return 0;
+    const unsigned lane = lane_id();
+    uint32_t prefix = 0;
+    int base = (int)b - 1;
+    while (true) {
+        const int j = base - (int)lane;
+        unsigned long long s = 2ull << 32;  // before the first chunk: inclusive 0
+        if (j >= 0) {
+            do { s = ld_relaxed64(status + j); } while ((s >> 32) == 0);
+        }
+        const unsigned incl = __ballot_sync(0xffffffffu, (s >> 32) == 2);
+        const int first = __ffs(incl) - 1;  // nearest chunk holding an inclusive prefix, or -1
+        uint32_t val = (first < 0 || (int)lane <= first) ? (uint32_t)s : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
+        prefix += val;
+        if (first >= 0) break;
+        base -= 32;
+    }
+    if (lane == 0) st_relaxed64(status + b, (2ull << 32) | (prefix + total));
+    return prefix;
+}
+
+// Writes the entries [t0, t1) of one rect into the staging window at s_* + pos0 (pos0 = slot of entry t0).
+template <typename TK>
+__device__ __forceinline__ void stage_run(TK* s_tile, uint32_t* s_val, uint32_t pos0, uint32_t t0, uint32_t t1,
+                                          uint32_t step, uint32_t x0, uint32_t y0, uint32_t w, uint32_t gx, uint32_t idx) {
+    for (uint32_t t = t0; t < t1; t += step) {
+        const uint32_t yy = t / w;
+        s_tile[pos0 + (t - t0)] = (TK)((y0 + yy) * gx + x0 + (t - yy * w));
+        s_val[pos0 + (t - t0)] = idx;
+    }
+}
 
 template <typename TK>
 __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const uint32_t* __restrict__ order,
@@ -353,11 +432,10 @@ __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const u
                                                          const gsr_forward_info* __restrict__ info, uint32_t cap,
                                                          unsigned long long* status, uint32_t* ticket,
                                                          TK* __restrict__ keys, uint32_t* __restrict__ vals,
-                                                         uint32_t* __restrict__ tile_count) {
-    __shared__ uint32_t s_excl[kEmitChunk];   // chunk-local exclusive list offset of each slot
-    __shared__ uint32_t s_xy[kEmitChunk];     // x0 | y0 << 16
-    __shared__ uint32_t s_w[kEmitChunk];      // rect width in tiles
-    __shared__ uint32_t s_idx[kEmitChunk];    // Gaussian index
+                                                         uint32_t* __restrict__ tile_count, uint32_t replica_stride) {
+    constexpr int kStage = sizeof(TK) == 2 ? 6144 : 4096;   // staged entries: 36 KB / 32 KB of shared memory
+    __shared__ uint32_t s_val[kStage];
+    __shared__ TK s_tile[kStage];
     __shared__ uint32_t s_warp[kBlk / 32 + 1];
     __shared__ uint32_t s_b, s_prefix;
     if (effective_n(reinterpret_cast<const uint32_t*>(&info->num_rendered), cap) == 0u) return;  // empty or overflow
@@ -367,8 +445,9 @@ __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const u
     const uint32_t b = s_b;
     const uint32_t k0 = b * kEmitChunk + threadIdx.x * kEmitSlots;
     if (b * kEmitChunk >= nvis) return;
+    const unsigned lane = lane_id();
 
-    uint32_t id[kEmitSlots], cnt[kEmitSlots];
+    uint32_t id[kEmitSlots];
     if (k0 + kEmitSlots <= nvis) {
         const uint4 a = *reinterpret_cast<const uint4*>(order + k0);
         id[0] = a.x; id[1] = a.y; id[2] = a.z; id[3] = a.w;
@@ -384,6 +463,7 @@ __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const u
         rr[j] = on ? __ldg(radii + id[j]) : 0;
         mm[j] = on ? __ldg(means2D + id[j]) : make_float2(0.f, 0.f);
     }
+    uint32_t xy[kEmitSlots], ww[kEmitSlots], cnt[kEmitSlots], ex[kEmitSlots];
     uint32_t sum = 0;
 #pragma unroll
     for (int j = 0; j < kEmitSlots; ++j) {
@@ -391,38 +471,53 @@ __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const u
         if (rr[j] > 0) tile_rect(mm[j].x, mm[j].y, rr[j], gx, gy, x0, y0, x1, y1);
         const uint32_t w = (uint32_t)(x1 - x0);
         cnt[j] = w * (uint32_t)(y1 - y0);
-        const int sl = threadIdx.x * kEmitSlots + j;
-        s_xy[sl] = (uint32_t)x0 | ((uint32_t)y0 << 16);
-        s_w[sl] = w ? w : 1u;
-        s_idx[sl] = id[j];
+        xy[j] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+        ww[j] = w ? w : 1u;
         sum += cnt[j];
     }
     uint32_t total;
-    uint32_t ex = block_excl_scan(sum, s_warp, total);
+    uint32_t run = block_excl_scan(sum, s_warp, total);
+    if (threadIdx.x == 0) publish_aggregate(status, b, total);   // successors can add it up from now on
 #pragma unroll
-    for (int j = 0; j < kEmitSlots; ++j) {
-        s_excl[threadIdx.x * kEmitSlots + j] = ex;
-        ex += cnt[j];
-    }
-    if (threadIdx.x < 32) {
-        const uint32_t prefix = lookback_prefix(status, b, total);
-        if (threadIdx.x == 0) s_prefix = prefix;
-    }
-    __syncthreads();
-    const uint32_t goff = s_prefix;
-    for (uint32_t p = threadIdx.x; p < total; p += kBlk) {
-        // last slot s with s_excl[s] <= p (slots of zero area share their successor's offset and are skipped)
-        int lo = 0;
+    for (int j = 0; j < kEmitSlots; ++j) { ex[j] = run; run += cnt[j]; }
+
+    for (uint32_t w0 = 0; w0 < total; w0 += kStage) {   // one window for all but pathological chunks
+        const uint32_t w1 = min(w0 + (uint32_t)kStage, total);
+        if (w0) __syncthreads();   // the previous window has been copied out
 #pragma unroll
-        for (int step = kEmitChunk / 2; step > 0; step >>= 1)
-            if (s_excl[lo + step] <= p) lo += step;
-        const uint32_t t = p - s_excl[lo];
-        const uint32_t w = s_w[lo], xy = s_xy[lo];
-        const uint32_t yy = t / w;
-        const uint32_t tile = ((xy >> 16) + yy) * (uint32_t)gx + (xy & 0xFFFFu) + (t - yy * w);
-        keys[goff + p] = (TK)tile;
-        vals[goff + p] = s_idx[lo];
-        atomicAdd(tile_count + tile, 1u);
+        for (int j = 0; j < kEmitSlots; ++j) {
+            // the part [t0, t1) of this slot's entries that falls into the window
+            const uint32_t lo = max(ex[j], w0), hi = min(ex[j] + cnt[j], w1);
+            const bool any = lo < hi;
+            const bool small = any && cnt[j] <= (uint32_t)kEmitSmall;
+            if (small)
+                stage_run(s_tile, s_val, lo - w0, lo - ex[j], hi - ex[j], 1u, xy[j] & 0xFFFFu, xy[j] >> 16, ww[j],
+                          (uint32_t)gx, id[j]);
+            unsigned big = __ballot_sync(0xffffffffu, any && !small);
+            while (big) {
+                const int src = __ffs(big) - 1;
+                big &= big - 1;
+                const uint32_t bxy = __shfl_sync(0xffffffffu, xy[j], src), bw = __shfl_sync(0xffffffffu, ww[j], src);
+                const uint32_t bid = __shfl_sync(0xffffffffu, id[j], src);
+                const uint32_t bex = __shfl_sync(0xffffffffu, ex[j], src);
+                const uint32_t blo = __shfl_sync(0xffffffffu, lo, src), bhi = __shfl_sync(0xffffffffu, hi, src);
+                stage_run(s_tile, s_val, blo - w0 + lane, blo - bex + lane, bhi - bex, 32u, bxy & 0xFFFFu, bxy >> 16, bw,
+                          (uint32_t)gx, bid);
+            }
+        }
+        if (w0 == 0 && threadIdx.x < 32) {
+            const uint32_t prefix = lookback_prefix(status, b, total);
+            if (threadIdx.x == 0) s_prefix = prefix;
+        }
+        __syncthreads();
+        const uint32_t goff = s_prefix + w0;
+        uint32_t* my_count = tile_count + (size_t)(b & (kTileReplicas - 1)) * replica_stride;
+        for (uint32_t i = threadIdx.x; i < w1 - w0; i += kBlk) {
+            const TK tile = s_tile[i];
+            keys[goff + i] = tile;
+            vals[goff + i] = s_val[i];
+            atomicAdd(my_count + (uint32_t)tile, 1u);
+        }
     }
 }
 
@@ -431,10 +526,11 @@ __global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const u
 // reference's identifyTileRanges finds by comparing neighbouring keys), and the digit histograms of the tile-bit
 // radix passes folded out of the same counts.  One CTA (tiles is a few thousand to a few hundred thousand).
 constexpr int kOffsThreads = 1024;
+constexpr int kOffsPer = 8;   // rows of 1024 tiles per batch (one batch covers 1080p; 4K takes four)
 __global__ void __launch_bounds__(kOffsThreads) tile_offsets_kernel(int tiles, const uint32_t* __restrict__ tile_count,
-                                                                    uint2* __restrict__ ranges, int npass, int bits,
-                                                                    uint32_t* __restrict__ hist, uint32_t cap,
-                                                                    gsr_forward_info* info) {
+                                                                    uint32_t replica_stride, uint2* __restrict__ ranges,
+                                                                    int npass, int bits, uint32_t* __restrict__ hist,
+                                                                    uint32_t cap, gsr_forward_info* info) {
     __shared__ uint32_t s_h[kMaxPasses][kMaxBins];
     __shared__ uint32_t s_wsum[kOffsThreads / 32 + 1];
     for (int i = threadIdx.x; i < kMaxPasses * kMaxBins; i += kOffsThreads) (&s_h[0][0])[i] = 0;
@@ -443,28 +539,45 @@ __global__ void __launch_bounds__(kOffsThreads) tile_offsets_kernel(int tiles, c
     const uint32_t mask = (1u << bits) - 1u;
     const unsigned lane = lane_id();
     const int warp = threadIdx.x >> 5;
-    uint32_t carry = 0;  // instances of the tiles before `base` (kept identical in every thread)
-    for (int base = 0; base < tiles; base += kOffsThreads) {
-        const int t = base + (int)threadIdx.x;
-        const uint32_t c = t < tiles ? tile_count[t] : 0u;
-        const uint32_t incl = warp_incl_scan(c);
-        if (lane == 31) s_wsum[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            const uint32_t w = s_wsum[lane];
-            const uint32_t wi = warp_incl_scan(w);
-            s_wsum[lane] = wi - w;
-            if (lane == 31) s_wsum[kOffsThreads / 32] = wi;
+    uint32_t carry = 0;  // instances of the tiles before the current row (kept identical in every thread)
+    for (int base = 0; base < tiles; base += kOffsThreads * kOffsPer) {
+        // row k of the batch = tiles base + k * 1024 + thread: coalesced, and every load of the batch is independent
+        // of the others, so the whole batch costs one memory round trip
+        uint32_t c[kOffsPer];
+#pragma unroll
+        for (int k = 0; k < kOffsPer; ++k) c[k] = 0;
+#pragma unroll
+        for (int r = 0; r < kTileReplicas; ++r) {
+#pragma unroll
+            for (int k = 0; k < kOffsPer; ++k) {
+                const int t = base + k * kOffsThreads + (int)threadIdx.x;
+                if (t < tiles) c[k] += tile_count[(size_t)r * replica_stride + t];
+            }
         }
-        __syncthreads();
-        const uint32_t begin = carry + s_wsum[warp] + incl - c;
-        carry += s_wsum[kOffsThreads / 32];
-        if (t < tiles) {
-            ranges[t] = c ? make_uint2(begin, begin + c) : make_uint2(0u, 0u);  // empty tiles: (0, 0) as the reference leaves them
-            if (c)
-                for (int p = 0; p < npass; ++p) atomicAdd(&s_h[p][((uint32_t)t >> (p * bits)) & mask], c);
+#pragma unroll
+        for (int k = 0; k < kOffsPer; ++k) {
+            const int t = base + k * kOffsThreads + (int)threadIdx.x;
+            if (base + k * kOffsThreads >= tiles) break;   // uniform
+            const uint32_t incl = warp_incl_scan(c[k]);
+            if (lane == 31) s_wsum[warp] = incl;
+            __syncthreads();
+            if (warp == 0) {
+                const uint32_t w = s_wsum[lane];
+                const uint32_t wi = warp_incl_scan(w);
+                s_wsum[lane] = wi - w;
+                if (lane == 31) s_wsum[kOffsThreads / 32] = wi;
+            }
+            __syncthreads();
+            const uint32_t begin = carry + s_wsum[warp] + incl - c[k];
+            carry += s_wsum[kOffsThreads / 32];
+            if (t < tiles) {
+                // empty tiles: (0, 0) as the reference leaves them
+                ranges[t] = c[k] ? make_uint2(begin, begin + c[k]) : make_uint2(0u, 0u);
+                if (c[k])
+                    for (int p = 0; p < npass; ++p) atomicAdd(&s_h[p][((uint32_t)t >> (p * bits)) & mask], c[k]);
+            }
+            __syncthreads();
         }
-        __syncthreads();
     }
     for (int i = threadIdx.x; i < npass * kMaxBins; i += kOffsThreads) hist[i] = (&s_h[0][0])[i];
 }
@@ -508,7 +621,7 @@ cudaError_t tile_pass_bits(unsigned grid, cudaStream_t s, const TK* kin, const u
     auto* fn = radix_pass_kernel<TK, false, kBits, kTileMin>;
     const size_t smem = radix_pass_smem<TK>(kBits);
     if (attr_only) return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    fn<<<grid, kBlk, smem, s>>>(kin, vin, kout, vout, r_ptr, 0u, cap, shift, hist, status, ticket);
+    fn<<<grid, kSortThreads, smem, s>>>(kin, vin, kout, vout, r_ptr, 0u, cap, shift, hist, status, ticket);
     return cudaSuccess;
 }
 template <typename TK>
@@ -543,7 +656,7 @@ cudaError_t ensure_pass_attributes() {
 // ---- control regions (u32 words) --------------------------------------------------------------------
 // geometry:  [hist kMaxPasses*kMaxBins][tickets 8][pass status 4 x chunks(P) x kMaxBins]
 // binning:   [hist kMaxPasses*kMaxBins][tickets 8][tile_count tiles, padded][emit status 2 x emit_chunks(P)]
-//            [pass status passes x chunks(cap) x kMaxBins]
+//            [pass status passes x chunks(cap) x kMaxBins]      (tile_count: kTileReplicas copies)
 constexpr size_t kCtlHeader = (size_t)kMaxPasses * kMaxBins + 8;
 size_t pad4(size_t n) { return (n + 3) & ~(size_t)3; }
 
@@ -557,7 +670,7 @@ TileCtl tile_ctl(uint32_t* ctl, size_t P, size_t tiles) {
     c.hist = ctl;
     c.tickets = ctl + kMaxPasses * kMaxBins;
     c.tile_count = ctl + kCtlHeader;
-    size_t o = kCtlHeader + pad4(tiles);
+    size_t o = kCtlHeader + kTileReplicas * pad4(tiles);
     c.emit_status = reinterpret_cast<unsigned long long*>(ctl + o);
     o += 2 * (emit_chunks_of(P) + 1);
     c.status = ctl + o;
@@ -581,12 +694,12 @@ int binning_impl(int P, const Grid& g, const int32_t* radii, GeomView gv, BinVie
         StageScope scope(kStageEmitKeys, s);
         emit_scan_kernel<TK><<<(unsigned)emit_chunks_of((size_t)P), kBlk, 0, s>>>(
             g.gx, g.gy, gv.order, radii, gv.means2D, gv.info, cap, c.emit_status, c.tickets + 7, k_unsorted,
-            bv.vals_unsorted, c.tile_count);
+            bv.vals_unsorted, c.tile_count, (uint32_t)pad4((size_t)g.tiles));
         GSR_AFTER_LAUNCH(s, debug);
     }
     {
         StageScope scope(kStageTileRanges, s);
-        tile_offsets_kernel<<<1, kOffsThreads, 0, s>>>(g.tiles, c.tile_count, iv.ranges, passes, bits, c.hist, cap, gv.info);
+        tile_offsets_kernel<<<1, kOffsThreads, 0, s>>>(g.tiles, c.tile_count, (uint32_t)pad4((size_t)g.tiles), iv.ranges, passes, bits, c.hist, cap, gv.info);
         GSR_AFTER_LAUNCH(s, debug);
     }
     StageScope scope(kStageSort, s);
@@ -611,7 +724,7 @@ int binning_impl(int P, const Grid& g, const int32_t* radii, GeomView gv, BinVie
 
 size_t depth_sort_ctl_entries(size_t P) { return kCtlHeader + 4 * chunks_of(P) * kMaxBins; }
 size_t tile_sort_ctl_entries(size_t cap, size_t P, size_t tiles) {
-    return kCtlHeader + pad4(tiles) + 2 * (emit_chunks_of(P) + 1) + (size_t)kMaxPasses * chunks_of(cap) * kMaxBins;
+    return kCtlHeader + kTileReplicas * pad4(tiles) + 2 * (emit_chunks_of(P) + 1) + (size_t)kMaxPasses * chunks_of(cap) * kMaxBins;
 }
 int tile_key_bytes(int tiles) { return tiles <= 65536 ? 2 : 4; }
 
@@ -639,10 +752,10 @@ int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
     uint32_t* vout = gv.order_alt;
     for (int pass = 0; pass < 4; ++pass) {
         if (pass == 0)
-            radix_pass_kernel<uint32_t, true, 8, kDepthMin><<<(unsigned)nchunk, kBlk, smem, s>>>(
+            radix_pass_kernel<uint32_t, true, 8, kDepthMin><<<(unsigned)nchunk, kSortThreads, smem, s>>>(
                 kin, vin, kout, vout, nullptr, (uint32_t)P, 0u, 0, hist, status, tickets);
         else
-            radix_pass_kernel<uint32_t, false, 8, kDepthMin><<<(unsigned)nchunk, kBlk, smem, s>>>(
+            radix_pass_kernel<uint32_t, false, 8, kDepthMin><<<(unsigned)nchunk, kSortThreads, smem, s>>>(
                 kin, vin, kout, vout, nvis_ptr, 0u, (uint32_t)P, 8 * pass, hist + pass * kMaxBins,
                 status + (size_t)pass * nchunk * kMaxBins, tickets + pass);
         GSR_AFTER_LAUNCH(s, debug);
