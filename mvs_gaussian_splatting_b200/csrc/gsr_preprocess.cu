@@ -9,6 +9,9 @@
 //
 // All arithmetic that decides radii / tile rects / depth bits follows oracle/gs_oracle.c
 // operation for operation with non-contractable _rn intrinsics (see gsr_internal.cuh).
+#include <algorithm>
+#include <cstdlib>
+
 #include "gsr_internal.cuh"
 
 namespace gsr {
@@ -336,6 +339,201 @@ __global__ void __launch_bounds__(kPreThreads, kMulti ? 5 : 8) preprocess_kernel
   }  // views
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Persistent form of the single-view kernel with the next tile's bytes in flight (cp.async.bulk + mbarrier):
+// the per-Gaussian kernels are latency-bound, not bandwidth-bound (ncu r02a: 47 % of HBM, 56 % issue, three
+// dependent round trips per CTA: means -> rotation -> SH rows), so each CTA walks over tiles of 128 Gaussians and
+//   * the operand block of tile i+1 (xyz, scale, rotation, opacity: four contiguous runs, 5.6 KB) is requested as
+//     soon as tile i's geometry phase has read its own, and lands while tile i-1's colour phase runs;
+//   * the SH rows of tile i's SURVIVORS — known at the end of its geometry phase — are requested one 16-byte-
+//     multiple run per row (culled rows cost nothing) onto a 208-byte stride (13 sixteen-byte pieces: every
+//     quarter-warp of a 128-bit shared load touches eight different bank groups), and are consumed one iteration
+//     later, behind tile i+1's geometry phase;
+// so a tile's two dependent memory phases overlap the arithmetic of its neighbours inside one CTA, on top of what
+// the other resident CTAs hide.  Raw mode fetches its two contiguous blocks (dc | rest) per tile instead.
+// Arithmetic and its order are exactly those of preprocess_kernel (bit-identical outputs, tests/test_gpu_*).
+constexpr int kShRow4 = 13;                 // float4 pieces per staged SH row (12 used)
+struct PreTmaSmem {
+    alignas(16) float xyz[3 * kPreThreads];
+    alignas(16) float scale[3 * kPreThreads];
+    alignas(16) float4 rot[kPreThreads];
+    alignas(16) float opac[kPreThreads];
+    alignas(16) float4 sh[kPreThreads * kShRow4];   // standard: row t at sh + 13 t; raw: dc block, then rest block
+    alignas(8) uint64_t bar_opnd, bar_sh;
+    float cam[36];
+};
+
+template <bool kRaw>
+__global__ void __launch_bounds__(kPreThreads, 6) preprocess_tma_kernel(const PreParams p) {
+    __shared__ PreTmaSmem sm;
+    const PreView& V = p.v[0];
+    const int ntiles = (p.P + kPreThreads - 1) / kPreThreads;
+    const int t = threadIdx.x;
+    if (t < 16) sm.cam[t] = __ldg(V.view + t);
+    else if (t < 32) sm.cam[t] = __ldg(V.proj + t - 16);
+    else if (t < 35) sm.cam[t] = __ldg(V.campos + t - 32);
+    if (t == 0) { mbar_init(&sm.bar_opnd, 1); mbar_init(&sm.bar_sh, 1); mbar_init_fence(); }
+    __syncthreads();
+    const float* view = sm.cam;
+    const float* proj = sm.cam + 16;
+    const int row = 3 * p.M;                       // floats per SH row in global memory (a multiple of 4 here)
+    const int need = 3 * (p.D + 1) * (p.D + 1);    // floats of the active degree
+    const uint32_t need_bytes = (uint32_t)((need * 4 + 15) & ~15);
+
+    // operands of tile `tile` -> shared (full tiles by the copy engine; the ragged last tile by plain loads)
+    auto request_operands = [&](int tile) {
+        const int base = tile * kPreThreads;
+        const int n = min(kPreThreads, p.P - base);
+        if (n == kPreThreads) {
+            if (t == 0) {
+                mbar_arrive_expect_tx(&sm.bar_opnd, 44u * kPreThreads);
+                bulk_g2s(sm.xyz, p.means3D + 3 * (size_t)base, 12u * kPreThreads, &sm.bar_opnd);
+                bulk_g2s(sm.scale, p.scales + 3 * (size_t)base, 12u * kPreThreads, &sm.bar_opnd);
+                bulk_g2s(sm.rot, p.rotations + 4 * (size_t)base, 16u * kPreThreads, &sm.bar_opnd);
+                bulk_g2s(sm.opac, p.opacities + (size_t)base, 4u * kPreThreads, &sm.bar_opnd);
+            }
+        } else if (t < n) {
+            const size_t i = (size_t)base + t;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                sm.xyz[3 * t + k] = __ldg(p.means3D + 3 * i + k);
+                sm.scale[3 * t + k] = __ldg(p.scales + 3 * i + k);
+            }
+            sm.rot[t] = __ldg(reinterpret_cast<const float4*>(p.rotations) + i);
+            sm.opac[t] = __ldg(p.opacities + i);
+        }
+    };
+
+    uint32_t ph_opnd = 0, ph_sh = 0;
+    int tile = blockIdx.x;
+    if (tile < ntiles) request_operands(tile);
+    // state carried from a tile's geometry phase to its colour phase one iteration later
+    bool prev_any = false, prev_alive = false;
+    int prev_idx = 0;
+    float pmx = 0.f, pmy = 0.f, pmz = 0.f;
+
+    for (; tile < ntiles || prev_any; tile += gridDim.x) {
+        const bool cur = tile < ntiles;
+        const int base = tile * kPreThreads;
+        const int idx = base + t;
+        bool alive = false;
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        if (cur) {
+            if (p.P - base >= kPreThreads) { mbar_wait(&sm.bar_opnd, ph_opnd); ph_opnd ^= 1u; }
+            alive = idx < p.P;
+            float depth = 0, px = 0, py = 0, ca = 0, cb = 0, cc = 0, det_inv = 0;
+            int rad = 0, x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+            if (alive) {
+                mx = sm.xyz[3 * t]; my = sm.xyz[3 * t + 1]; mz = sm.xyz[3 * t + 2];
+                const float tx = xform_row_rn(view, 0, mx, my, mz);
+                const float ty = xform_row_rn(view, 1, mx, my, mz);
+                depth = xform_row_rn(view, 2, mx, my, mz);
+                alive = depth > kNearPlane;  // near-plane cull only; NaN fails too
+                if (alive) {
+                    const float hx = xform_row_rn(proj, 0, mx, my, mz);
+                    const float hy = xform_row_rn(proj, 1, mx, my, mz);
+                    const float hw = xform_row_rn(proj, 3, mx, my, mz);
+                    const float pw = __fdiv_rn(1.0f, __fadd_rn(hw, 0.0000001f));
+                    const float ndcx = __fmul_rn(hx, pw), ndcy = __fmul_rn(hy, pw);
+                    float c6[6];
+                    float4 q = sm.rot[t];
+                    float sx = sm.scale[3 * t], sy = sm.scale[3 * t + 1], sz = sm.scale[3 * t + 2];
+                    if (kRaw) {
+                        q = act_rotation(q);
+                        sx = act_scale(sx); sy = act_scale(sy); sz = act_scale(sz);
+                    }
+                    cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, q, c6);
+                    cov2d_project(tx, ty, depth, V.focal_x, V.focal_y, V.tanfovx, V.tanfovy, c6, view, ca, cb, cc);
+                    const float det = __fmaf_rn(ca, cc, -__fmul_rn(cb, cb));
+                    alive = det != 0.0f;
+                    if (alive) {
+                        det_inv = __fdiv_rn(1.0f, det);
+                        const float mid = __fmul_rn(0.5f, __fadd_rn(ca, cc));
+                        const float sq = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+                        const float lam1 = __fadd_rn(mid, sq), lam2 = __fadd_rn(mid, -sq);
+                        rad = __float2int_rz(ceilf(__fmul_rn(3.0f, __fsqrt_rn(fmaxf(lam1, lam2)))));
+                        px = __fmul_rn(__fmaf_rn(__fadd_rn(ndcx, 1.0f), (float)p.W, -1.0f), 0.5f);
+                        py = __fmul_rn(__fmaf_rn(__fadd_rn(ndcy, 1.0f), (float)p.H, -1.0f), 0.5f);
+                        tile_rect(px, py, rad, p.gx, p.gy, x0, y0, x1, y1);
+                        alive = (x1 - x0) * (y1 - y0) != 0;
+                    }
+                }
+            }
+            if (idx < p.P) {   // everything but the colour goes out now
+                V.radii[idx] = alive ? rad : 0;
+                V.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
+                V.gv.depths[idx] = alive ? depth : __uint_as_float(0xFFFFFFFFu);
+                if (alive) {
+                    V.gv.means2D[idx] = make_float2(px, py);
+                    const float op = kRaw ? act_opacity(sm.opac[t]) : sm.opac[t];
+                    V.gv.conic_opacity[idx] = make_float4(__fmul_rn(cc, det_inv), __fmul_rn(-cb, det_inv),
+                                                          __fmul_rn(ca, det_inv), op);
+                }
+            }
+        }
+        __syncthreads();   // the operand block has been read by everyone
+        if (cur && tile + (int)gridDim.x < ntiles) request_operands(tile + gridDim.x);
+
+        // ---- colour phase of the PREVIOUS tile: its SH rows were requested one iteration ago ----
+        if (prev_any) {
+            mbar_wait(&sm.bar_sh, ph_sh);
+            ph_sh ^= 1u;
+            if (prev_alive) {
+                float shr[48];
+                if (kRaw) {
+                    const float* dc = reinterpret_cast<const float*>(sm.sh);
+                    const float* rest = dc + 3 * kPreThreads;
+                    const int rr = row - 3;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) shr[k] = dc[3 * t + k];
+#pragma unroll
+                    for (int k = 3; k < 48; ++k) shr[k] = k < need ? rest[rr * t + k - 3] : 0.f;
+                } else {
+                    const float4* r4 = sm.sh + kShRow4 * t;
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) {
+                        const float4 v = 4 * j < need ? r4[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+                        shr[4 * j] = v.x; shr[4 * j + 1] = v.y; shr[4 * j + 2] = v.z; shr[4 * j + 3] = v.w;
+                    }
+                }
+                float rgb[3];
+                uint32_t clamped;
+                sh_to_rgb(p.D, __fadd_rn(pmx, -view[32]), __fadd_rn(pmy, -view[33]), __fadd_rn(pmz, -view[34]), shr, rgb,
+                          clamped);
+                V.gv.rgb[prev_idx] = make_float4(rgb[0], rgb[1], rgb[2], __uint_as_float(clamped));
+            }
+        }
+        const int nalive = __syncthreads_count(cur && alive);   // also: the SH tile has been read by everyone
+        if (cur) {
+            if (kRaw) {   // two contiguous blocks of the tile's rows (dc | rest), whoever survives
+                const int n = min(kPreThreads, p.P - base);
+                const uint32_t b_dc = 12u * (uint32_t)n, b_rest = 4u * (uint32_t)(row - 3) * (uint32_t)n;
+                float* dc = reinterpret_cast<float*>(sm.sh);
+                if (((b_dc | b_rest) & 15u) == 0) {
+                    if (t == 0) {
+                        mbar_arrive_expect_tx(&sm.bar_sh, b_dc + b_rest);
+                        bulk_g2s(dc, p.shs + 3 * (size_t)base, b_dc, &sm.bar_sh);
+                        if (b_rest) bulk_g2s(dc + 3 * kPreThreads, p.sh_rest + (size_t)base * (row - 3), b_rest, &sm.bar_sh);
+                    }
+                } else {   // ragged last tile: plain loads, then an empty phase
+                    for (int j = t; j < 3 * n; j += kPreThreads) dc[j] = __ldg(p.shs + 3 * (size_t)base + j);
+                    for (int j = t; j < (row - 3) * n; j += kPreThreads)
+                        dc[3 * kPreThreads + j] = __ldg(p.sh_rest + (size_t)base * (row - 3) + j);
+                    __syncthreads();
+                    if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, 0u);
+                }
+            } else {
+                if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, (uint32_t)nalive * need_bytes);
+                if (alive) bulk_g2s(sm.sh + kShRow4 * t, p.shs + (size_t)idx * row, need_bytes, &sm.bar_sh);
+            }
+        }
+        prev_any = cur;
+        prev_alive = alive;
+        prev_idx = idx;
+        pmx = mx; pmy = my; pmz = mz;
+    }
+}
+
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
                                     const float* __restrict__ view, uint8_t* __restrict__ present) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -398,6 +596,16 @@ int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* mea
     }
     const int blocks = (P + kPreThreads - 1) / kPreThreads;
     StageScope scope(kStagePreprocess, s);
+    // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows: the persistent bulk-copy kernel
+    static const bool use_tma = [] { const char* e = getenv("GSR_PREPROCESS_TMA"); return !e || atoi(e) != 0; }();
+    if (use_tma && n_views == 1 && shs && !colors_precomp && scales && rotations && !cov3D_precomp && (3 * M) % 4 == 0 &&
+        !views[0].radii_local) {
+        const int grid = std::min(blocks, 148 * 6);
+        if (rm.raw) preprocess_tma_kernel<true><<<grid, kPreThreads, 0, s>>>(p);
+        else preprocess_tma_kernel<false><<<grid, kPreThreads, 0, s>>>(p);
+        GSR_AFTER_LAUNCH(s, debug);
+        return GSR_OK;
+    }
     if (rm.raw) {
         if (n_views == 1) preprocess_kernel<false, true><<<blocks, kPreThreads, 0, s>>>(p);
         else preprocess_kernel<true, true><<<blocks, kPreThreads, 0, s>>>(p);
