@@ -9,6 +9,9 @@
 //   acc[0..1] = sum h*dx, sum h*dy          acc[2..4] = sum h*dx*dx, h*dx*dy, h*dy*dy
 //   acc[5]    = dL/dopacity                 acc[6..8] = dL/dcolor
 // with h = dL/dG * G and d = mean2D - pixel; the conic/mean chain-rule factors are applied here.
+#include <algorithm>
+#include <cstdlib>
+
 #include "gsr_internal.cuh"
 
 namespace gsr {
@@ -527,6 +530,349 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Persistent single-view form with the next tile's bytes in flight (cp.async.bulk + mbarrier), the backward
+// counterpart of preprocess_tma_kernel.  Visibility is known from the forward (radii), so per tile of 128 Gaussians:
+//   * the operand block (xyz, scale, rotation, the 48-byte blend accumulators, conic + opacity, colour/clamp rows:
+//     six contiguous runs, 15 KB) is requested as soon as the previous tile's geometry phase has read its own;
+//   * the SH rows of the VISIBLE Gaussians are requested one run per row onto a 208-byte stride (128-bit shared
+//     accesses touch eight bank groups per quarter-warp) and consumed one iteration later;
+//   * phase A (EWA / covariance / mean chain rules, needs the operands) of tile i and phase B (SH backward: dL/dsh
+//     formed IN PLACE over the staged row, the view-direction term of dL/dmean3D) of tile i-1 alternate, so either
+//     tile's memory phase overlaps the other's arithmetic;
+//   * dL/dsh leaves as one bulk store per row straight from the staged tile (zeros for culled rows: every row of
+//     every gradient array is written, the caller passes uninitialised memory).
+// SH backward is evaluated coefficient-major here (t_k = g . sh_k, gdir += dY_k/ddir t_k, dL/dsh_k = Y_k g), the
+// same sums as sh_backward in a different association — gradients are a tolerance item (tests/helpers.py).
+constexpr int kBwdShRow4 = 13;
+struct BwdTmaSmem {
+    alignas(16) float xyz[3 * kBwdThreads];
+    alignas(16) float scale[3 * kBwdThreads];
+    alignas(16) float4 rot[kBwdThreads];
+    alignas(16) float4 acc[3 * kBwdThreads];
+    alignas(16) float4 con[kBwdThreads];
+    alignas(16) float4 rgb[kBwdThreads];
+    alignas(16) float4 sh[kBwdThreads * kBwdShRow4];
+    alignas(8) uint64_t bar_opnd, bar_sh;
+    float cam[36];
+};
+
+// Real SH basis function k (with its constant) and its partial derivatives w.r.t. the unit direction.
+__device__ __forceinline__ void sh_basis(int k, float x, float y, float z, float& B, float& Dx, float& Dy, float& Dz) {
+    const float C0 = 0.28209479177387814f, C1 = 0.4886025119029199f;
+    const float C2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f,
+                         0.5462742152960396f};
+    const float C3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                         -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f};
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    Dx = Dy = Dz = 0.f;
+    switch (k) {
+        case 0: B = C0; break;
+        case 1: B = -C1 * y; Dy = -C1; break;
+        case 2: B = C1 * z; Dz = C1; break;
+        case 3: B = -C1 * x; Dx = -C1; break;
+        case 4: B = C2[0] * xy; Dx = C2[0] * y; Dy = C2[0] * x; break;
+        case 5: B = C2[1] * yz; Dy = C2[1] * z; Dz = C2[1] * y; break;
+        case 6: B = C2[2] * (2.f * zz - xx - yy); Dx = C2[2] * 2.f * -x; Dy = C2[2] * 2.f * -y; Dz = C2[2] * 4.f * z; break;
+        case 7: B = C2[3] * xz; Dx = C2[3] * z; Dz = C2[3] * x; break;
+        case 8: B = C2[4] * (xx - yy); Dx = C2[4] * 2.f * x; Dy = C2[4] * 2.f * -y; break;
+        case 9: B = C3[0] * y * (3.f * xx - yy); Dx = C3[0] * 6.f * xy; Dy = C3[0] * 3.f * (xx - yy); break;
+        case 10: B = C3[1] * xy * z; Dx = C3[1] * yz; Dy = C3[1] * xz; Dz = C3[1] * xy; break;
+        case 11: B = C3[2] * y * (4.f * zz - xx - yy); Dx = C3[2] * -2.f * xy; Dy = C3[2] * (-3.f * yy + 4.f * zz - xx);
+                 Dz = C3[2] * 8.f * yz; break;
+        case 12: B = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy); Dx = C3[3] * -6.f * xz; Dy = C3[3] * -6.f * yz;
+                 Dz = C3[3] * 3.f * (2.f * zz - xx - yy); break;
+        case 13: B = C3[4] * x * (4.f * zz - xx - yy); Dx = C3[4] * (-3.f * xx + 4.f * zz - yy); Dy = C3[4] * -2.f * xy;
+                 Dz = C3[4] * 8.f * xz; break;
+        case 14: B = C3[5] * z * (xx - yy); Dx = C3[5] * 2.f * xz; Dy = C3[5] * -2.f * yz; Dz = C3[5] * (xx - yy); break;
+        default: B = C3[6] * x * (xx - 3.f * yy); Dx = C3[6] * 3.f * (xx - yy); Dy = C3[6] * -6.f * xy; break;
+    }
+}
+
+// SH backward of one Gaussian, in place on its staged row (12 floats = 4 coefficients = three 16-byte pieces at a
+// time): row values in, dL/dsh out (zeros above the active degree), returns dL/d(direction).
+__device__ __forceinline__ void sh_backward_row(int deg, int row_floats, float x, float y, float z, float4* r4,
+                                                const float* g3, float* gdir) {
+    const int used = (deg + 1) * (deg + 1);
+    gdir[0] = gdir[1] = gdir[2] = 0.f;
+#pragma unroll
+    for (int grp = 0; grp < 4; ++grp) {
+        if (12 * grp >= row_floats) break;
+        float sv[12], o[12];
+        if (4 * grp < used) {
+            const float4 a = r4[3 * grp], b = r4[3 * grp + 1], c = r4[3 * grp + 2];
+            sv[0] = a.x; sv[1] = a.y; sv[2] = a.z; sv[3] = a.w; sv[4] = b.x; sv[5] = b.y; sv[6] = b.z; sv[7] = b.w;
+            sv[8] = c.x; sv[9] = c.y; sv[10] = c.z; sv[11] = c.w;
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int k = 4 * grp + kk;
+            if (k < used) {
+                float B, Dx, Dy, Dz;
+                sh_basis(k, x, y, z, B, Dx, Dy, Dz);
+                const float tk = g3[0] * sv[3 * kk] + g3[1] * sv[3 * kk + 1] + g3[2] * sv[3 * kk + 2];
+                gdir[0] += Dx * tk; gdir[1] += Dy * tk; gdir[2] += Dz * tk;
+                o[3 * kk] = B * g3[0]; o[3 * kk + 1] = B * g3[1]; o[3 * kk + 2] = B * g3[2];
+            } else {
+                o[3 * kk] = o[3 * kk + 1] = o[3 * kk + 2] = 0.f;
+            }
+        }
+        r4[3 * grp] = make_float4(o[0], o[1], o[2], o[3]);
+        r4[3 * grp + 1] = make_float4(o[4], o[5], o[6], o[7]);
+        r4[3 * grp + 2] = make_float4(o[8], o[9], o[10], o[11]);
+    }
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel(const BwdParams p) {
+    extern __shared__ __align__(16) unsigned char s_tma_raw[];
+    BwdTmaSmem& sm = *reinterpret_cast<BwdTmaSmem*>(s_tma_raw);
+    const BwdView& V = p.v[0];
+    const int ntiles = (p.P + kBwdThreads - 1) / kBwdThreads;
+    const int t = threadIdx.x;
+    if (t < 16) sm.cam[t] = __ldg(V.view + t);
+    else if (t < 32) sm.cam[t] = __ldg(V.proj + t - 16);
+    else if (t < 35) sm.cam[t] = __ldg(V.campos + t - 32);
+    if (t == 0) { mbar_init(&sm.bar_opnd, 1); mbar_init(&sm.bar_sh, 1); mbar_init_fence(); }
+    __syncthreads();
+    const float* view = sm.cam;
+    const float* proj = sm.cam + 16;
+    const float* campos = sm.cam + 32;
+    const int row = 3 * p.M;                       // a multiple of 12 here
+    const int need = 3 * (p.D + 1) * (p.D + 1);
+    const uint32_t need_bytes = (uint32_t)((need * 4 + 15) & ~15);
+
+    auto request_operands = [&](int tile) {
+        const int base = tile * kBwdThreads;
+        const int n = min(kBwdThreads, p.P - base);
+        if (n == kBwdThreads) {
+            if (t == 0) {
+                mbar_arrive_expect_tx(&sm.bar_opnd, 120u * kBwdThreads);
+                bulk_g2s(sm.xyz, p.means3D + 3 * (size_t)base, 12u * kBwdThreads, &sm.bar_opnd);
+                bulk_g2s(sm.scale, p.scales + 3 * (size_t)base, 12u * kBwdThreads, &sm.bar_opnd);
+                bulk_g2s(sm.rot, p.rotations + 4 * (size_t)base, 16u * kBwdThreads, &sm.bar_opnd);
+                bulk_g2s(sm.acc, V.grad_accum + 12 * (size_t)base, 48u * kBwdThreads, &sm.bar_opnd);
+                bulk_g2s(sm.con, V.conic_opacity + base, 16u * kBwdThreads, &sm.bar_opnd);
+                bulk_g2s(sm.rgb, V.rgb + base, 16u * kBwdThreads, &sm.bar_opnd);
+            }
+        } else if (t < n) {
+            const size_t i = (size_t)base + t;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                sm.xyz[3 * t + k] = __ldg(p.means3D + 3 * i + k);
+                sm.scale[3 * t + k] = __ldg(p.scales + 3 * i + k);
+                sm.acc[3 * t + k] = reinterpret_cast<const float4*>(V.grad_accum)[3 * i + k];
+            }
+            sm.rot[t] = __ldg(reinterpret_cast<const float4*>(p.rotations) + i);
+            sm.con[t] = V.conic_opacity[i];
+            sm.rgb[t] = V.rgb[i];
+        }
+    };
+    auto radius_of = [&](int tile) {
+        const int i = tile * kBwdThreads + t;
+        return (tile < ntiles && i < p.P) ? V.radii[i] : 0;
+    };
+
+    uint32_t ph_opnd = 0, ph_sh = 0;
+    int tile = blockIdx.x;
+    if (tile < ntiles) request_operands(tile);
+    int r_cur = radius_of(tile), r_next = radius_of(tile + (int)gridDim.x);   // radii travel one tile ahead in registers
+    // state carried from a tile's phase A to its phase B one iteration later
+    bool prev_any = false, prev_vis = false;
+    int prev_idx = 0;
+    float pm[3] = {0.f, 0.f, 0.f}, pvm[3] = {0.f, 0.f, 0.f}, pg3[3] = {0.f, 0.f, 0.f};
+
+    for (; tile < ntiles || prev_any; tile += gridDim.x) {
+        const bool cur = tile < ntiles;
+        const int base = tile * kBwdThreads;
+        const int idx = base + t;
+        const bool valid = cur && idx < p.P;
+        const bool vis = valid && r_cur > 0;
+        float mx = 0.f, my = 0.f, mz = 0.f;
+        float vm[3] = {0.f, 0.f, 0.f}, g3[3] = {0.f, 0.f, 0.f};
+        if (cur) {
+            if (p.P - base >= kBwdThreads) { mbar_wait(&sm.bar_opnd, ph_opnd); ph_opnd ^= 1u; }
+            float g2d[2] = {0.f, 0.f}, gop = 0.f, gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
+            if (vis) {
+                mx = sm.xyz[3 * t]; my = sm.xyz[3 * t + 1]; mz = sm.xyz[3 * t + 2];
+                const float4 q = sm.rot[t];
+                float s[3], c6[6], R[3][3];
+                s[0] = p.scale_modifier * sm.scale[3 * t];
+                s[1] = p.scale_modifier * sm.scale[3 * t + 1];
+                s[2] = p.scale_modifier * sm.scale[3 * t + 2];
+                cov3d(s[0], s[1], s[2], q, R, c6);
+                const float4 a0 = sm.acc[3 * t], a1 = sm.acc[3 * t + 1], a2 = sm.acc[3 * t + 2], con = sm.con[t];
+                const uint32_t clamped_bits = __float_as_uint(sm.rgb[t].w);
+                const float S1 = a0.x, S2 = a0.y;
+                const float gA = -0.5f * a0.z, gB = -a0.w, gC = -0.5f * a1.x;
+                g2d[0] = (-con.x * S1 - con.y * S2) * (0.5f * (float)p.W);
+                g2d[1] = (-con.z * S2 - con.y * S1) * (0.5f * (float)p.H);
+                gop = a1.y;
+                const float vcol[3] = {a1.z, a1.w, a2.x};
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) g3[ch] = (clamped_bits >> ch) & 1u ? 0.f : vcol[ch];
+
+                // ---- EWA projection (forward values) ----
+                float tt[3];
+                tt[0] = view[0] * mx + view[4] * my + view[8] * mz + view[12];
+                tt[1] = view[1] * mx + view[5] * my + view[9] * mz + view[13];
+                tt[2] = view[2] * mx + view[6] * my + view[10] * mz + view[14];
+                const float limx = 1.3f * V.tanfovx, limy = 1.3f * V.tanfovy;
+                const float txtz = tt[0] / tt[2], tytz = tt[1] / tt[2];
+                const float gmulx = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+                const float gmuly = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+                tt[0] = fminf(limx, fmaxf(-limx, txtz)) * tt[2];
+                tt[1] = fminf(limy, fmaxf(-limy, tytz)) * tt[2];
+                const float fx = V.focal_x, fy = V.focal_y;
+                const float j00 = fx / tt[2], j11 = fy / tt[2];
+                const float j02 = -(fx * tt[0]) / (tt[2] * tt[2]), j12 = -(fy * tt[1]) / (tt[2] * tt[2]);
+                float M0[3], M1[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    M0[k] = view[4 * k + 0] * j00 + view[4 * k + 2] * j02;
+                    M1[k] = view[4 * k + 1] * j11 + view[4 * k + 2] * j12;
+                }
+                const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+                float SM0[3], SM1[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    SM0[k] = S[k][0] * M0[0] + S[k][1] * M0[1] + S[k][2] * M0[2];
+                    SM1[k] = S[k][0] * M1[0] + S[k][1] * M1[1] + S[k][2] * M1[2];
+                }
+                const float a = M0[0] * SM0[0] + M0[1] * SM0[1] + M0[2] * SM0[2] + 0.3f;
+                const float b = M1[0] * SM0[0] + M1[1] * SM0[1] + M1[2] * SM0[2];
+                const float c = M1[0] * SM1[0] + M1[1] * SM1[1] + M1[2] * SM1[2] + 0.3f;
+                const float det = a * c - b * b;
+                const float d2inv = 1.f / (det * det + 0.0000001f);
+                float dLa = 0.f, dLb = 0.f, dLc = 0.f;
+                float gc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (d2inv != 0.f) {
+                    dLa = d2inv * (-c * c * gA + b * c * gB + (det - a * c) * gC);
+                    dLc = d2inv * (-a * a * gC + a * b * gB + (det - a * c) * gA);
+                    dLb = d2inv * (2.f * b * c * gA - (det + 2.f * b * b) * gB + 2.f * a * b * gC);
+                    gc[0] = M0[0] * M0[0] * dLa + M0[0] * M1[0] * dLb + M1[0] * M1[0] * dLc;
+                    gc[3] = M0[1] * M0[1] * dLa + M0[1] * M1[1] * dLb + M1[1] * M1[1] * dLc;
+                    gc[5] = M0[2] * M0[2] * dLa + M0[2] * M1[2] * dLb + M1[2] * M1[2] * dLc;
+                    gc[1] = 2.f * M0[0] * M0[1] * dLa + (M0[0] * M1[1] + M0[1] * M1[0]) * dLb + 2.f * M1[0] * M1[1] * dLc;
+                    gc[2] = 2.f * M0[0] * M0[2] * dLa + (M0[0] * M1[2] + M0[2] * M1[0]) * dLb + 2.f * M1[0] * M1[2] * dLc;
+                    gc[4] = 2.f * M0[2] * M0[1] * dLa + (M0[1] * M1[2] + M0[2] * M1[1]) * dLb + 2.f * M1[1] * M1[2] * dLc;
+                }
+                {
+                    float dM0[3], dM1[3];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        dM0[k] = 2.f * SM0[k] * dLa + SM1[k] * dLb;
+                        dM1[k] = 2.f * SM1[k] * dLc + SM0[k] * dLb;
+                    }
+                    float dj00 = 0.f, dj02 = 0.f, dj11 = 0.f, dj12 = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        dj00 += view[4 * k + 0] * dM0[k];
+                        dj02 += view[4 * k + 2] * dM0[k];
+                        dj11 += view[4 * k + 1] * dM1[k];
+                        dj12 += view[4 * k + 2] * dM1[k];
+                    }
+                    const float tz = 1.f / tt[2], tz2 = tz * tz, tz3 = tz2 * tz;
+                    const float dtx = gmulx * -fx * tz2 * dj02;
+                    const float dty = gmuly * -fy * tz2 * dj12;
+                    const float dtz = -fx * tz2 * dj00 - fy * tz2 * dj11 + (2.f * fx * tt[0]) * tz3 * dj02 +
+                                      (2.f * fy * tt[1]) * tz3 * dj12;
+                    vm[0] = view[0] * dtx + view[1] * dty + view[2] * dtz;
+                    vm[1] = view[4] * dtx + view[5] * dty + view[6] * dtz;
+                    vm[2] = view[8] * dtx + view[9] * dty + view[10] * dtz;
+                }
+                {   // mean2D -> mean3D through the perspective divide
+                    const float hx = proj[0] * mx + proj[4] * my + proj[8] * mz + proj[12];
+                    const float hy = proj[1] * mx + proj[5] * my + proj[9] * mz + proj[13];
+                    const float hw = proj[3] * mx + proj[7] * my + proj[11] * mz + proj[15];
+                    const float mw = 1.f / (hw + 0.0000001f);
+                    const float mul1 = hx * mw * mw, mul2 = hy * mw * mw;
+                    vm[0] += (proj[0] * mw - proj[3] * mul1) * g2d[0] + (proj[1] * mw - proj[3] * mul2) * g2d[1];
+                    vm[1] += (proj[4] * mw - proj[7] * mul1) * g2d[0] + (proj[5] * mw - proj[7] * mul2) * g2d[1];
+                    vm[2] += (proj[8] * mw - proj[11] * mul1) * g2d[0] + (proj[9] * mw - proj[11] * mul2) * g2d[1];
+                }
+                {   // cov3D -> scale, quaternion
+                    const float Gs[3][3] = {{gc[0], 0.5f * gc[1], 0.5f * gc[2]},
+                                            {0.5f * gc[1], gc[3], 0.5f * gc[4]},
+                                            {0.5f * gc[2], 0.5f * gc[4], gc[5]}};
+                    float GR[3][3], dR[3][3];
+#pragma unroll
+                    for (int a2 = 0; a2 < 3; ++a2)
+#pragma unroll
+                        for (int k = 0; k < 3; ++k)
+                            GR[a2][k] = Gs[a2][0] * R[0][k] + Gs[a2][1] * R[1][k] + Gs[a2][2] * R[2][k];
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const float rgr = R[0][k] * GR[0][k] + R[1][k] * GR[1][k] + R[2][k] * GR[2][k];
+                        gs[k] = 2.f * s[k] * rgr;
+#pragma unroll
+                        for (int a2 = 0; a2 < 3; ++a2) dR[a2][k] = 2.f * GR[a2][k] * s[k] * s[k];
+                    }
+                    const float r = q.x, x = q.y, y = q.z, z = q.w;
+                    gq[0] = 2.f * (z * (dR[1][0] - dR[0][1]) + y * (dR[0][2] - dR[2][0]) + x * (dR[2][1] - dR[1][2]));
+                    gq[1] = 2.f * (y * (dR[0][1] + dR[1][0]) + z * (dR[0][2] + dR[2][0]) + r * (dR[2][1] - dR[1][2])) -
+                            4.f * x * (dR[1][1] + dR[2][2]);
+                    gq[2] = 2.f * (x * (dR[0][1] + dR[1][0]) + r * (dR[0][2] - dR[2][0]) + z * (dR[1][2] + dR[2][1])) -
+                            4.f * y * (dR[0][0] + dR[2][2]);
+                    gq[3] = 2.f * (r * (dR[1][0] - dR[0][1]) + x * (dR[0][2] + dR[2][0]) + y * (dR[1][2] + dR[2][1])) -
+                            4.f * z * (dR[0][0] + dR[1][1]);
+                }
+            }
+            if (valid) {   // everything that does not need the SH row goes out now (zeros for culled rows)
+                const size_t i = (size_t)idx;
+                V.dL_dmeans2D[3 * i] = g2d[0]; V.dL_dmeans2D[3 * i + 1] = g2d[1]; V.dL_dmeans2D[3 * i + 2] = 0.f;
+                p.dL_dopacity[i] = gop;
+                p.dL_dscales[3 * i] = gs[0]; p.dL_dscales[3 * i + 1] = gs[1]; p.dL_dscales[3 * i + 2] = gs[2];
+                reinterpret_cast<float4*>(p.dL_drots)[i] = make_float4(gq[0], gq[1], gq[2], gq[3]);
+            }
+        }
+        __syncthreads();   // the operand block has been read by everyone
+        if (cur && tile + (int)gridDim.x < ntiles) request_operands(tile + gridDim.x);
+
+        // ---- phase B of the PREVIOUS tile: SH backward in place on the staged rows, rows out by bulk store ----
+        if (prev_any) {
+            mbar_wait(&sm.bar_sh, ph_sh);
+            ph_sh ^= 1u;
+            float4* r4 = sm.sh + kBwdShRow4 * t;
+            float gm[3] = {pvm[0], pvm[1], pvm[2]};
+            if (prev_vis) {
+                const float d0 = pm[0] - campos[0], d1 = pm[1] - campos[1], d2 = pm[2] - campos[2];
+                const float s2 = d0 * d0 + d1 * d1 + d2 * d2;
+                const float len = sqrtf(s2);
+                float gdir[3];
+                sh_backward_row(p.D, row, d0 / len, d1 / len, d2 / len, r4, pg3, gdir);
+                const float inv32 = 1.f / sqrtf(s2 * s2 * s2);
+                const float vd = d0 * gdir[0] + d1 * gdir[1] + d2 * gdir[2];
+                gm[0] += (s2 * gdir[0] - d0 * vd) * inv32;
+                gm[1] += (s2 * gdir[1] - d1 * vd) * inv32;
+                gm[2] += (s2 * gdir[2] - d2 * vd) * inv32;
+            } else {
+                for (int j = 0; j < (row >> 2); ++j) r4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            if (prev_idx < p.P) {
+                const size_t i = (size_t)prev_idx;
+                p.dL_dmeans3D[3 * i] = gm[0]; p.dL_dmeans3D[3 * i + 1] = gm[1]; p.dL_dmeans3D[3 * i + 2] = gm[2];
+                fence_async_smem();   // my row, written through the generic proxy, is read by the copy engine next
+                bulk_s2g(p.dL_dsh + i * row, r4, 4u * (uint32_t)row);
+                bulk_commit();
+                bulk_wait_read();     // the staged row may be overwritten once the engine has read it
+            }
+        }
+        const int nvis = __syncthreads_count(vis);   // also: the SH tile is free
+        if (cur) {
+            if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, (uint32_t)nvis * need_bytes);
+            if (vis) bulk_g2s(sm.sh + kBwdShRow4 * t, p.shs + (size_t)idx * row, need_bytes, &sm.bar_sh);
+        }
+        prev_any = cur;
+        prev_vis = vis;
+        prev_idx = cur ? idx : p.P;
+        pm[0] = mx; pm[1] = my; pm[2] = mz;
+        pvm[0] = vm[0]; pvm[1] = vm[1]; pvm[2] = vm[2];
+        pg3[0] = g3[0]; pg3[1] = g3[1]; pg3[2] = g3[2];
+        r_cur = r_next;
+        r_next = radius_of(tile + 2 * (int)gridDim.x);
+    }
+}
+
 constexpr size_t bwd_smem_bytes(bool multi) {
     return sizeof(float) * (36 + (size_t)(multi ? 2 : 1) * kBwdWarps * 32 * kShStride);
 }
@@ -569,6 +915,21 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     }
     StageScope scope(kStagePreprocessBwd, s);
     const unsigned blocks = (unsigned)((P + kBwdThreads - 1) / kBwdThreads);
+    // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows, every output requested: the
+    // persistent bulk-copy kernel
+    static const bool use_tma = [] { const char* e = getenv("GSR_BACKWARD_TMA"); return !e || atoi(e) != 0; }();
+    if (use_tma && !rm.raw && n_views == 1 && !accumulate && shs && !colors_precomp && scales && rotations &&
+        !cov3D_precomp && M % 4 == 0 && dL_dsh && dL_dscales && dL_drots && !dL_dcolors && !dL_dcov3D &&
+        !views[0].radii_local) {
+        static unsigned long long tma_devices = 0;
+        if (first_use_on_current_device(&tma_devices))
+            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)sizeof(BwdTmaSmem)));
+        const unsigned grid = std::min(blocks, 148u * 5u);
+        preprocess_backward_tma_kernel<<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
+        GSR_AFTER_LAUNCH(s, debug);
+        return GSR_OK;
+    }
     if (rm.raw) {
         if (n_views == 1) preprocess_backward_kernel<false, true><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
         else preprocess_backward_kernel<true, true><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
