@@ -713,28 +713,38 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         L = sr.L
     else:
         params = {k: t[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")}
-    gt1 = (0.5 + 0.25 * dL_np).clip(0, 1).astype(np.float32)
-    gt_host = torch.from_numpy(np.ascontiguousarray(np.broadcast_to(gt1, (L, 3, H, W)))).pin_memory()
+    # Ground truth travels as the dataset stores it — 8 bits per channel (the reference's readers decode PNG / JPEG
+    # and divide by 255, utils/general_utils.py PILtoTorch) — and becomes float32 on the device: a quarter of the
+    # PCIe bytes of a float upload (the reference itself keeps its float images resident, scene/cameras.py:39).
+    gt1 = np.rint((0.5 + 0.25 * dL_np).clip(0, 1) * 255.0).astype(np.uint8)
+    gt_host = torch.from_numpy(np.ascontiguousarray(np.broadcast_to(gt1, (L, 3, H, W))).copy()).pin_memory()
 
     # Per-step host inputs are prefetched one step ahead on a copy stream (double-buffered), as a data
     # loader does; the loss is copied to pinned memory asynchronously and read one step late, so the
     # host never stalls the launch queue.  Every copy still happens inside the timed region, once per step.
     copy_stream = torch.cuda.Stream(device=dev)
     main = torch.cuda.current_stream(dev)
-    slots = [dict(block=torch.empty_like(cam_host, device=dev), gt=torch.empty_like(gt_host, device=dev),
+    slots = [dict(block=torch.empty_like(cam_host, device=dev), gt_u8=torch.empty_like(gt_host, device=dev),
+                  gt=torch.empty(gt_host.shape, dtype=torch.float32, device=dev),
                   ready=torch.cuda.Event(), free=torch.cuda.Event(), loss=torch.zeros(L).pin_memory(),
-                  loss_ready=torch.cuda.Event()) for _ in range(2)]
+                  loss_ready=torch.cuda.Event(), h2d=(torch.cuda.Event(enable_timing=True),
+                                                      torch.cuda.Event(enable_timing=True))) for _ in range(2)]
     for sl in slots:
         sl["free"].record(main)
         # the settings NamedTuples are views of the slot's device block: built once per slot, refreshed by the copy
         sl["cams"] = [settings_from(sl["block"][38 * v:38 * v + 38], v) for v in range(V)]
     state = {"k": 0, "pending": None}
+    skip = set(filter(None, os.environ.get("GSR_E2E_SKIP", "").split(",")))   # diagnostic: drop pieces of the loop
 
     def prefetch(sl):
+        if "h2d" in skip:
+            return
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(sl["free"])          # the step that last used this slot is done with it
+            sl["h2d"][0].record(copy_stream)
             sl["block"].copy_(cam_host, non_blocking=True)
-            sl["gt"].copy_(gt_host, non_blocking=True)
+            sl["gt_u8"].copy_(gt_host, non_blocking=True)
+            sl["h2d"][1].record(copy_stream)
             sl["ready"].record(copy_stream)
 
     prefetch(slots[0])
@@ -742,7 +752,10 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
     def step():
         sl = slots[state["k"] & 1]
         prefetch(slots[(state["k"] + 1) & 1])           # next step's inputs travel while this step computes
-        main.wait_event(sl["ready"])
+        if "h2d" not in skip:
+            main.wait_event(sl["ready"])
+        if "mul" not in skip:
+            torch.mul(sl["gt_u8"], 1.0 / 255.0, out=sl["gt"])    # 8-bit image -> float32 on the device
         if sr is not None:
             colors, radii = sr.forward(slices, sl["cams"])
             colors.requires_grad_(True)
@@ -761,11 +774,12 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
             if world > 1:
                 for p in params.values():
                     dist.all_reduce(p.grad)
-        sl["loss"].copy_(loss.detach().reshape(L), non_blocking=True)   # D2H read of the step's result
+        if "d2h" not in skip:
+            sl["loss"].copy_(loss.detach().reshape(L), non_blocking=True)   # D2H read of the step's result
         sl["loss_ready"].record(main)
         sl["free"].record(main)
         val = None
-        if state["pending"] is not None:                 # previous step's loss, now on the host
+        if state["pending"] is not None and "d2h" not in skip:   # previous step's loss, now on the host
             state["pending"]["loss_ready"].synchronize()
             val = float(state["pending"]["loss"][0])
         state["pending"] = sl
@@ -775,12 +789,17 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
                 p.grad = None                               # train.py:142 zero_grad(set_to_none=True)
         return val
 
-    for _ in range(5 if world == 1 else 20):
+    import gc
+    for _ in range(10 if world == 1 else 20):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    n = max(30, args.steps)   # wall-clock: enough steps that one host hiccup does not move the figure
+    # wall-clock: enough steps (>= 0.15 s) that one host hiccup or the empty launch queue of the first step does not
+    # move the figure; the collector is paused as a training loop's inner iteration would not trigger it either
+    n = max(100 if V == 1 else 30, args.steps)
+    gc.collect()
+    gc.disable()
     prof = None
     if os.environ.get("GSR_E2E_PROFILE") and int(os.environ.get("RANK", "0")) == 0:
         import cProfile                                   # where the host time of an e2e step goes (stderr; perturbs the figure)
@@ -791,6 +810,8 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         step()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    gc.enable()
+    h2d_ms = 0.0 if "h2d" in skip else max(sl["h2d"][0].elapsed_time(sl["h2d"][1]) for sl in slots)   # the last two uploads
     if prof is not None:
         import pstats
         prof.disable()
@@ -800,12 +821,13 @@ def run_e2e(args, torch, dist, world, dev, t, cam_host, settings_from, dL_np, Ga
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
     return {"value": V * n / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / n, "steps": n,
-            "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel() * 4), "d2h_bytes_per_step": 4 * L,
+            "h2d_bytes_per_step": int(cam_host.numel() * 4 + gt_host.numel()), "d2h_bytes_per_step": 4 * L,
+            "h2d_ms_per_step": round(float(h2d_ms), 4),
             "api": ("ShardedViewRasterizer.forward / .backward on this rank's parameter slice" if sr is not None else
                     "GaussianRasterizer(settings)(...) under autograd") +
                    " + l1_loss (mvs_gaussian_splatting_b200.loss) per rendered view + backward; the batch's camera blocks and "
-                   "this rank's ground-truth images come from pinned host memory every step (prefetched one step ahead on a "
-                   "copy stream), the losses are copied back to pinned memory every step; Gaussian parameters resident in "
+                   "this rank's ground-truth images (8 bits per channel, as datasets store them; float32 on the device) come "
+                   "from pinned host memory every step (prefetched one step ahead on a copy stream), the losses are copied back to pinned memory every step; Gaussian parameters resident in "
                    "HBM (model state)"}
 
 

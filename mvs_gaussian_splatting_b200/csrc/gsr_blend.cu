@@ -33,6 +33,15 @@ namespace gsr {
 
 namespace {
 
+// Staging gathers (list entry -> mean + conic) of the NEXT batch issued before the walk of the current one.  A/B on
+// the B200 (config 3): backward 0.605 -> 0.592 ms at 77 registers / 6 CTAs per SM (0.620 at 5 CTAs); forward
+// 0.313 -> 0.347 ms (the seven extra registers cost the fifth CTA per SM) — so backward only.
+#ifndef GSR_BLEND_PREFETCH_FWD
+#define GSR_BLEND_PREFETCH_FWD 0
+#endif
+#ifndef GSR_BLEND_PREFETCH_BWD
+#define GSR_BLEND_PREFETCH_BWD 1
+#endif
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kAlphaMin = 1.0f / 255.0f;
 constexpr float kTmin = 0.0001f;
@@ -155,6 +164,16 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
     bool done = !c.inside;
     uint32_t n_blended = 0, stop_pos = 0, n_eval = 0, n_iter = 0;  // kCount only
 
+#if GSR_BLEND_PREFETCH_FWD
+    uint32_t n_gid = 0;
+    float2 n_m = make_float2(0.f, 0.f);
+    float4 n_co = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((int)threadIdx.x < n) {
+        n_gid = __ldg(point_list + range.x + threadIdx.x);
+        n_m = __ldg(means2D + n_gid);
+        n_co = __ldg(conic_opacity + n_gid);
+    }
+#endif
     for (int base = 0; base < n; base += kBlendThreads) {
         if (__syncthreads_count(done) == kBlendThreads) break;
         const int p = base + threadIdx.x;
@@ -163,12 +182,25 @@ __global__ void __launch_bounds__(kBlendThreads) blend_forward_kernel(
         float2 m = make_float2(0.f, 0.f);
         float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
         if (p < n) {
+#if GSR_BLEND_PREFETCH_FWD
+            gid = n_gid;
+            m = n_m;
+            const float4 co = n_co;
+#else
             gid = __ldg(point_list + range.x + p);
             m = __ldg(means2D + gid);
             const float4 co = __ldg(conic_opacity + gid);
+#endif
             op = co.w;
             keep = stage_test(m, co, c.tile_rect, a2, b2, c2, tau2);
         }
+#if GSR_BLEND_PREFETCH_FWD
+        if (p + kBlendThreads < n) {   // the next batch's gathers fly during this batch's walk
+            n_gid = __ldg(point_list + range.x + p + kBlendThreads);
+            n_m = __ldg(means2D + n_gid);
+            n_co = __ldg(conic_opacity + n_gid);
+        }
+#endif
         int total;
         const int slot = compact_slot(keep, s_wcount, total);
         if (keep) {
@@ -484,6 +516,20 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
 
     float bh0[2] = {0.f, 0.f}, bh1[2] = {0.f, 0.f}, bh2[2] = {0.f, 0.f};
 
+#if GSR_BLEND_PREFETCH_BWD
+    // staging gathers (list entry -> mean + conic) of the NEXT batch are issued before the walk of the current one
+    uint32_t n_gid = 0;
+    float2 n_mm = make_float2(0.f, 0.f);
+    float4 n_co = make_float4(0.f, 0.f, 0.f, 0.f);
+    {
+        const int p0 = (int)m - 1 - (int)threadIdx.x;
+        if (p0 >= 0) {
+            n_gid = __ldg(point_list + range.x + p0);
+            n_mm = __ldg(means2D + n_gid);
+            n_co = __ldg(conic_opacity + n_gid);
+        }
+    }
+#endif
     for (int hi = (int)m; hi > 0; hi -= kB2Threads) {
         __syncthreads();
         const int p = hi - 1 - (int)threadIdx.x;
@@ -492,12 +538,28 @@ __global__ void __launch_bounds__(kB2Threads, GSR_B2_MINBLOCKS) blend_backward2_
         float2 mm = make_float2(0.f, 0.f);
         float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
         if (p >= 0) {
+#if GSR_BLEND_PREFETCH_BWD
+            gid = n_gid;
+            mm = n_mm;
+            const float4 co = n_co;
+#else
             gid = __ldg(point_list + range.x + p);
             mm = __ldg(means2D + gid);
             const float4 co = __ldg(conic_opacity + gid);
+#endif
             op = co.w;
             keep = stage_test(mm, co, tile_rect, a2, b2, c2, tau2);
         }
+#if GSR_BLEND_PREFETCH_BWD
+        {
+            const int pn = p - kB2Threads;
+            if (pn >= 0) {
+                n_gid = __ldg(point_list + range.x + pn);
+                n_mm = __ldg(means2D + n_gid);
+                n_co = __ldg(conic_opacity + n_gid);
+            }
+        }
+#endif
         int total;
         const int slot = compact_slot<kB2Warps>(keep, s_wcount, total);
         if (keep) {
