@@ -252,11 +252,14 @@ static int forward_geometry_impl(const RawMode& rm, int P, int D, int M, int wid
             !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
             return GSR_ERR_INVALID_ARGUMENT;
         const Grid g = make_grid(width, height);
+        st = launch_depth_ctl_reset(P, gv, s);
+        if (st != GSR_OK) return st;
+        bool counts_done = false;   // the persistent preprocess kernel takes the depth histograms and counts itself
         st = launch_preprocess(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
                                rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tanfovx, tanfovy, radii,
-                               gv, s, debug, rm);
+                               gv, s, debug, rm, &counts_done);
         if (st != GSR_OK) return st;
-        st = launch_depth_order(P, gv, s, debug);
+        st = launch_depth_order(P, gv, s, debug, counts_done);
         if (st != GSR_OK) return st;
     }
     if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));
@@ -453,7 +456,8 @@ int gsr_depth_order(int P, int width, int height, void* geom_ws, gsr_forward_inf
     GeomView gv = geom_view(geom_ws, L);
     GSR_CUDA(cudaMemsetAsync(gv.info, 0, sizeof(gsr_forward_info), s));
     if (P > 0) {
-        st = launch_depth_order(P, gv, s, debug);
+        st = launch_depth_ctl_reset(P, gv, s);
+        if (st == GSR_OK) st = launch_depth_order(P, gv, s, debug);
         if (st != GSR_OK) return st;
     }
     if (h_info) GSR_CUDA(cudaMemcpyAsync(h_info, gv.info, sizeof(gsr_forward_info), cudaMemcpyDeviceToHost, s));

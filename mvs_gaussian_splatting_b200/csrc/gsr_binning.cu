@@ -730,19 +730,25 @@ int tile_key_bytes(int tiles) { return tiles <= 65536 ? 2 : 4; }
 
 // Per-Gaussian stage after preprocess: counts (num_visible, num_rendered) and the depth-order sort of the
 // visible (key, index) pairs; (order_keys, order)[0 .. num_visible) on return.
-int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug) {
+int launch_depth_ctl_reset(int P, GeomView gv, cudaStream_t s) {
+    GSR_CUDA(cudaMemsetAsync(gv.sort_ctl, 0, sizeof(uint32_t) * depth_sort_ctl_entries((size_t)P), s));
+    return GSR_OK;
+}
+
+int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug, bool counts_done) {
     GSR_CUDA(ensure_pass_attributes());
     const size_t nchunk = chunks_of((size_t)P);
     uint32_t* ctl = gv.sort_ctl;
     uint32_t* hist = ctl;
     uint32_t* tickets = ctl + kMaxPasses * kMaxBins;
     uint32_t* status = ctl + kCtlHeader;
-    GSR_CUDA(cudaMemsetAsync(ctl, 0, sizeof(uint32_t) * depth_sort_ctl_entries((size_t)P), s));
     StageScope scope(kStageDepthSort, s);
-    const int hblocks = (int)min((size_t)(148 * 8), ((size_t)P + kBlk - 1) / kBlk);
-    depth_hist_kernel<<<hblocks, kBlk, 0, s>>>(reinterpret_cast<const uint32_t*>(gv.depths), gv.tiles_touched,
-                                               (uint32_t)P, hist, gv.info);
-    GSR_AFTER_LAUNCH(s, debug);
+    if (!counts_done) {
+        const int hblocks = (int)min((size_t)(148 * 8), ((size_t)P + kBlk - 1) / kBlk);
+        depth_hist_kernel<<<hblocks, kBlk, 0, s>>>(reinterpret_cast<const uint32_t*>(gv.depths), gv.tiles_touched,
+                                                   (uint32_t)P, hist, gv.info);
+        GSR_AFTER_LAUNCH(s, debug);
+    }
     const size_t smem = radix_pass_smem<uint32_t>(8);
     const uint32_t* nvis_ptr = reinterpret_cast<const uint32_t*>(&gv.info->num_visible);
     // depths (identity payload, culled dropped) -> A -> B -> A -> B: 4 passes end in (order_keys, order)

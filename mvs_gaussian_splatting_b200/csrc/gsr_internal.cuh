@@ -128,11 +128,14 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
                       float scale_modifier, const float* rotations, const float* cov3D_precomp,
                       const float* view, const float* proj, const float* campos, float tanfovx,
                       float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug,
-                      const struct RawMode& rm);
+                      const struct RawMode& rm, bool* depth_counts_done = nullptr);
 
-// Counts (info->num_visible, info->num_rendered, on the device) and the depth-order sort of the visible
-// (depth bits, index) pairs.
-int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug);
+// Zeroes the control region of the depth sort (histograms, tickets, look-back words); must precede the kernels
+// that fill it: launch_preprocess when it takes the counts itself (depth_counts_done), launch_depth_order always.
+int launch_depth_ctl_reset(int P, GeomView gv, cudaStream_t s);
+// Counts (info->num_visible, info->num_rendered, on the device; skipped when the preprocess kernel already took
+// them: counts_done) and the depth-order sort of the visible (depth bits, index) pairs.
+int launch_depth_order(int P, GeomView gv, cudaStream_t s, int debug, bool counts_done = false);
 
 // The reference's 64-bit (tile << 32 | depth bits) key of every list entry, unsorted (emission order) or sorted,
 // rebuilt from the stored tile ids and depths[index] (tests / debugging; nothing on the render path reads it).
@@ -185,7 +188,8 @@ struct ForwardViewArgs {
 int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                             const float* colors_precomp, const float* opacities, const float* scales,
                             float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
-                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm = RawMode());
+                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm = RawMode(),
+                            bool* depth_counts_done = nullptr);
 
 // Multi-view form: the Gaussians' parameters are read once, `views` (host array, n_views <= GSR_MAX_VIEWS)
 // says per view where the camera, the forward rows (conic_opacity, rgb), radii and blend accumulators of

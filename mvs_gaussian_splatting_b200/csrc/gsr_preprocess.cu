@@ -57,6 +57,7 @@ struct PreParams {
     const float* cov3D_precomp;
     int raw;               // RawMode: pre-activation scales / rotations / opacities
     const float* sh_rest;  // RawMode: shs = dc [P,1,3], sh_rest = [P,M-1,3]
+    uint32_t* depth_hist;  // bulk-copy kernel: digit histograms of the depth sort [4][256] (zeroed), or null
     PreView v[kMaxViews];
 };
 
@@ -361,6 +362,8 @@ struct PreTmaSmem {
     alignas(16) float4 sh[kPreThreads * kShRow4];   // standard: row t at sh + 13 t; raw: dc block, then rest block
     alignas(8) uint64_t bar_opnd, bar_sh;
     float cam[36];
+    uint32_t hist[4][256];   // digit histograms of the visible depth keys (what depth_hist_kernel would count)
+    uint32_t sums[2];        // visible Gaussians, tile instances
 };
 
 template <bool kRaw>
@@ -373,7 +376,10 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_tma_kernel(const Pr
     else if (t < 32) sm.cam[t] = __ldg(V.proj + t - 16);
     else if (t < 35) sm.cam[t] = __ldg(V.campos + t - 32);
     if (t == 0) { mbar_init(&sm.bar_opnd, 1); mbar_init(&sm.bar_sh, 1); mbar_init_fence(); }
+    for (int i = t; i < 4 * 256; i += kPreThreads) (&sm.hist[0][0])[i] = 0;
+    if (t < 2) sm.sums[t] = 0;
     __syncthreads();
+    uint32_t my_vis = 0, my_inst = 0;
     const float* view = sm.cam;
     const float* proj = sm.cam + 16;
     const int row = 3 * p.M;                       // floats per SH row in global memory (a multiple of 4 here)
@@ -459,6 +465,21 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_tma_kernel(const Pr
                     }
                 }
             }
+            if (p.depth_hist) {   // the depth sort's histograms and the two counts, while the key is in a register
+                const uint32_t key = __float_as_uint(depth);
+                const bool full = __all_sync(0xffffffffu, alive);
+                if (alive) { ++my_vis; my_inst += (uint32_t)((x1 - x0) * (y1 - y0)); }
+#pragma unroll
+                for (int pass = 0; pass < 4; ++pass) {
+                    const uint32_t d = (key >> (8 * pass)) & 255u;
+                    const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
+                    if (full && __all_sync(0xffffffffu, d == d0)) {   // constant digit (the high depth bytes)
+                        if ((t & 31) == 0) atomicAdd(&sm.hist[pass][d0], 32u);
+                    } else if (alive) {
+                        atomicAdd(&sm.hist[pass][d], 1u);
+                    }
+                }
+            }
             if (idx < p.P) {   // everything but the colour goes out now
                 V.radii[idx] = alive ? rad : 0;
                 V.gv.tiles_touched[idx] = alive ? (uint32_t)((x1 - x0) * (y1 - y0)) : 0u;
@@ -532,6 +553,23 @@ __global__ void __launch_bounds__(kPreThreads, 6) preprocess_tma_kernel(const Pr
         prev_idx = idx;
         pmx = mx; pmy = my; pmz = mz;
     }
+    if (p.depth_hist) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            my_vis += __shfl_xor_sync(0xffffffffu, my_vis, d);
+            my_inst += __shfl_xor_sync(0xffffffffu, my_inst, d);
+        }
+        if ((t & 31) == 0 && my_vis) { atomicAdd(&sm.sums[0], my_vis); atomicAdd(&sm.sums[1], my_inst); }
+        __syncthreads();
+        for (int i = t; i < 4 * 256; i += kPreThreads) {
+            const uint32_t c = (&sm.hist[0][0])[i];
+            if (c) atomicAdd(p.depth_hist + i, c);
+        }
+        if (t == 0 && sm.sums[0] && V.gv.info) {
+            atomicAdd(&V.gv.info->num_visible, (int32_t)sm.sums[0]);
+            atomicAdd(&V.gv.info->num_rendered, (int32_t)sm.sums[1]);
+        }
+    }
 }
 
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
@@ -575,9 +613,12 @@ int launch_activate(int P, int M, const float* features_dc, const float* feature
 int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* means3D, const float* shs,
                             const float* colors_precomp, const float* opacities, const float* scales,
                             float scale_modifier, const float* rotations, const float* cov3D_precomp, int n_views,
-                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm) {
+                            const ForwardViewArgs* views, cudaStream_t s, int debug, const RawMode& rm,
+                            bool* depth_counts_done) {
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
+    if (depth_counts_done) *depth_counts_done = false;
     PreParams p;
+    p.depth_hist = nullptr;
     p.raw = rm.raw; p.sh_rest = rm.sh_rest;
     p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H; p.gx = g.gx; p.gy = g.gy;
     p.n_views = n_views;
@@ -601,6 +642,10 @@ int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* mea
     if (use_tma && n_views == 1 && shs && !colors_precomp && scales && rotations && !cov3D_precomp && (3 * M) % 4 == 0 &&
         !views[0].radii_local) {
         const int grid = std::min(blocks, 148 * 6);
+        if (depth_counts_done && views[0].gv.info && views[0].gv.sort_ctl) {   // the caller zeroed the control region
+            p.depth_hist = views[0].gv.sort_ctl;
+            *depth_counts_done = true;
+        }
         if (rm.raw) preprocess_tma_kernel<true><<<grid, kPreThreads, 0, s>>>(p);
         else preprocess_tma_kernel<false><<<grid, kPreThreads, 0, s>>>(p);
         GSR_AFTER_LAUNCH(s, debug);
@@ -621,12 +666,13 @@ int launch_preprocess(int P, int D, int M, const Grid& g, const float* means3D, 
                       const float* colors_precomp, const float* opacities, const float* scales,
                       float scale_modifier, const float* rotations, const float* cov3D_precomp,
                       const float* view, const float* proj, const float* campos, float tanfovx,
-                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug, const RawMode& rm) {
+                      float tanfovy, int32_t* radii, GeomView gv, cudaStream_t s, int debug, const RawMode& rm,
+                      bool* depth_counts_done) {
     ForwardViewArgs a;
     a.view = view; a.proj = proj; a.campos = campos; a.tanfovx = tanfovx; a.tanfovy = tanfovy;
     a.radii = radii; a.gv = gv;
     return launch_preprocess_views(P, D, M, g, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
-                                   rotations, cov3D_precomp, 1, &a, s, debug, rm);
+                                   rotations, cov3D_precomp, 1, &a, s, debug, rm, depth_counts_done);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present,

@@ -220,6 +220,7 @@ class ShardedViewRasterizer:
         self.radii_local = torch.zeros((V, Ps), dtype=torch.int32, device=dev)
         self.conic_local = f(V, Ps, 4)
         self._state = None
+        self._slot_cache: Dict = {}   # (id(cameras), workspace set) -> camera tensors + gsr_view_slot arrays
 
     # ------------------------------------------------------------------------------------------
     def local_views(self) -> List[int]:
@@ -258,6 +259,29 @@ class ShardedViewRasterizer:
         """(view, proj, campos, bg) device tensors per camera."""
         return [_settings_tensors(c, self.device) for c in cameras]   # cached per settings object (rasterizer.py)
 
+    def _step_plan(self, cameras):
+        """Camera tensors, tan(fov) pairs and the gsr_view_slot arrays of every launch chunk for this camera LIST
+        and the current workspace set.  A training loop hands the same list object (or one of a few) every step
+        and every address in a slot is fixed for the life of this object, so the ~10 pointer look-ups per view
+        and call are made once per (list, workspace set) instead of twice per step (the entry keeps the list alive,
+        so its id cannot be recycled; a list whose cameras were replaced in place must be a new list)."""
+        key = (id(cameras), self.parity)
+        hit = self._slot_cache.get(key)
+        if hit is not None and hit[0] is cameras and len(cameras) == self.V:
+            return hit[1:]
+        cams = self._camera_tensors(cameras)
+        tanfov = [(float(c.tanfovx), float(c.tanfovy)) for c in cameras]
+        order = self._view_order()
+        step = 1 if self.exchange == "nccl" else _native.MAX_VIEWS   # staged slots sit at different rows: one view per call
+        chunks = []
+        for c0 in range(0, self.V, step):
+            chunk = order[c0:c0 + step]
+            chunks.append((len(chunk),) + self._view_slots(chunk, cams, tanfov))
+        if len(self._slot_cache) >= 16:
+            self._slot_cache.pop(next(iter(self._slot_cache)))
+        self._slot_cache[key] = (cameras, cams, tanfov, chunks)
+        return cams, tanfov, chunks
+
     def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
         """params: means3D [Ps,3], shs [Ps,M,3], opacities [Ps,1], scales [Ps,3], rotations [Ps,4] of
         slice `rank` (ShardPlan.rows).  cameras[v]: settings of view v, v = 0..V-1 (same image size, sh_degree,
@@ -275,8 +299,6 @@ class ShardedViewRasterizer:
             raise ValueError("parameter slice does not match ShardPlan.rows(rank)")
         debug = 1 if rs.debug else 0
         D = int(rs.sh_degree)
-        cams = self._camera_tensors(cameras)   # (view, proj, campos, bg) per view
-        tanfov = [(float(c.tanfovx), float(c.tanfovy)) for c in cameras]
         dev_idx = dev.index if dev.index is not None else torch.cuda.current_device()
         staged = self.exchange == "nccl"
         with torch.cuda.device(dev):
@@ -284,14 +306,11 @@ class ShardedViewRasterizer:
             # no barrier here: this step's rows go to the workspace set last read two steps ago (see __init__)
             self.parity = (self.parity + 1) % self.nbuf
             bufs = self._bufs[self.parity]
-            order = self._view_order()
-            step = 1 if staged else _native.MAX_VIEWS   # staged slots sit at different rows: one view per call
-            for c0 in range(0, V, step):
-                chunk = order[c0:c0 + step]
-                slots, P_ws, row0 = self._view_slots(chunk, cams, tanfov)
+            cams, tanfov, chunks = self._step_plan(cameras)   # (view, proj, campos, bg) per view + the slot arrays
+            for n_chunk, slots, P_ws, row0 in chunks:
                 _native.check(lib.gsr_preprocess_views(
                     P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["opacities"]),
-                    _ptr(p["scales"]), float(rs.scale_modifier), _ptr(p["rotations"]), None, len(chunk), slots,
+                    _ptr(p["scales"]), float(rs.scale_modifier), _ptr(p["rotations"]), None, n_chunk, slots,
                     stream, debug), "gsr_preprocess_views")
             if self.exchange == "peer":
                 self.hdl.barrier(channel=1)   # all slices of this rank's views have landed
@@ -320,7 +339,7 @@ class ShardedViewRasterizer:
                 ctxs.append(ctx)
             # the workspace copies are overwritten two steps later: hand out stable radii
             radii = torch.stack([bufs[l][1] for l in range(L)]) if L > 1 else bufs[0][1].clone().unsqueeze(0)
-        self._state = (ctxs, p, cams, tanfov, float(rs.scale_modifier), D, debug)
+        self._state = (ctxs, p, cams, chunks, float(rs.scale_modifier), D, debug)
         return colors, radii
 
     def backward(self, dL_dpix: torch.Tensor):
@@ -329,7 +348,7 @@ class ShardedViewRasterizer:
         the next call); grad_means2D [V,Ps,3], one block per view."""
         if self._state is None:
             raise RuntimeError("backward() needs a preceding forward()")
-        ctxs, p, cams, tanfov, scale_modifier, D, debug = self._state
+        ctxs, p, cams, chunks, scale_modifier, D, debug = self._state
         N, r, dev, lib = self.world, self.rank, self.device, self.lib
         P, Ps, W, H, M, V, L = self.P, self.Ps, self.W, self.H, self.M, self.V, self.L
         g = _dense(dL_dpix, dev)
@@ -352,16 +371,12 @@ class ShardedViewRasterizer:
                                   [self.send["grad_accum"][self._slot(j + l * N)] for j in range(N)])
                                  for l in range(L)], self.group)
             G = self.grads
-            order = self._view_order()
-            step = 1 if staged else _native.MAX_VIEWS
-            for c0 in range(0, V, step):
-                chunk = order[c0:c0 + step]
-                slots, P_ws, row0 = self._view_slots(chunk, cams, tanfov)
+            for ci, (n_chunk, slots, P_ws, row0) in enumerate(chunks):
                 _native.check(lib.gsr_preprocess_backward_views(
                     P_ws, row0, Ps, D, M, W, H, _ptr(p["means3D"]), _ptr(p["shs"]), None, _ptr(p["scales"]),
-                    scale_modifier, _ptr(p["rotations"]), None, len(chunk), slots, None, _ptr(G["opacities"]),
+                    scale_modifier, _ptr(p["rotations"]), None, n_chunk, slots, None, _ptr(G["opacities"]),
                     _ptr(G["means3D"]), None, _ptr(G["shs"]), _ptr(G["scales"]), _ptr(G["rotations"]),
-                    1 if c0 > 0 else 0, stream, debug), "gsr_preprocess_backward_views")
+                    1 if ci > 0 else 0, stream, debug), "gsr_preprocess_backward_views")
         return G, self.grad_means2D
 
     def slice_radii(self) -> torch.Tensor:

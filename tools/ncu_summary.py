@@ -47,11 +47,12 @@ if __name__ == "__main__":
 
 
 # ---- profiles/traffic.json: measured DRAM bytes per launch of each bench stage -----------------
-STAGE_OF = [("preprocess_backward", "preprocess_backward"), ("preprocess_kernel", "preprocess"),
-            ("radix_hist_kernel<unsigned int", "depth_sort"), ("radix_pass_kernel<unsigned int", "depth_sort"),
-            ("scan_sorted_tiles", "scan"), ("emit_keys", "emit_keys"),
-            ("radix_hist_kernel<unsigned long", "radix_sort"), ("radix_pass_kernel<unsigned long", "radix_sort"),
-            ("tile_ranges", "tile_ranges"), ("blend_forward", "blend_forward"), ("blend_backward", "blend_backward")]
+STAGE_OF = [("preprocess_backward", "preprocess_backward"), ("preprocess_", "preprocess"),
+            ("depth_hist_kernel", "depth_sort"), ("radix_pass_kernel<unsigned int, 1", "depth_sort"),
+            ("radix_pass_kernel<unsigned int, 0, 8", "depth_sort"), ("emit_scan", "emit_keys"),
+            ("tile_offsets", "tile_ranges"), ("radix_pass_kernel<unsigned short", "radix_sort"),
+            ("radix_pass_kernel<unsigned int", "radix_sort"),
+            ("blend_forward", "blend_forward"), ("blend_backward", "blend_backward")]
 
 
 def traffic(rep, out):
