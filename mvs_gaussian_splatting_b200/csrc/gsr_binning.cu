@@ -570,11 +570,19 @@ __global__ void __launch_bounds__(kOffsThreads) tile_offsets_kernel(int tiles, c
             __syncthreads();
             const uint32_t begin = carry + s_wsum[warp] + incl - c[k];
             carry += s_wsum[kOffsThreads / 32];
-            if (t < tiles) {
-                // empty tiles: (0, 0) as the reference leaves them
+            if (t < tiles)   // empty tiles: (0, 0) as the reference leaves them
                 ranges[t] = c[k] ? make_uint2(begin, begin + c[k]) : make_uint2(0u, 0u);
-                if (c[k])
-                    for (int p = 0; p < npass; ++p) atomicAdd(&s_h[p][((uint32_t)t >> (p * bits)) & mask], c[k]);
+            // digit histograms: a warp holds 32 consecutive tiles, so every digit above the lowest is the same for
+            // all its lanes — one add of the warp's sum instead of 32 serialised adds to one shared word
+            const uint32_t wsum = __reduce_add_sync(0xffffffffu, c[k]);
+            for (int p = 0; p < npass; ++p) {
+                const uint32_t d = ((uint32_t)t >> (p * bits)) & mask;
+                const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
+                if (__all_sync(0xffffffffu, d == d0)) {
+                    if (lane == 0 && wsum) atomicAdd(&s_h[p][d0], wsum);
+                } else if (c[k]) {
+                    atomicAdd(&s_h[p][d], c[k]);
+                }
             }
             __syncthreads();
         }

@@ -29,6 +29,12 @@ CASES = [
     (5000, 320, 200, 2, 9, 2),
     (20000, 640, 360, 3, 16, 3),
     (100000, 800, 800, 3, 16, 0),   # BASELINE.json configs[1]
+    # the training schedule: all 16 coefficients stored, active degree ramping 0 -> 3 (train.py oneupSHdegree);
+    # the bulk-copy kernels fetch only the active prefix of each 192-byte row (16 / 48 / 112 bytes)
+    (6000, 320, 200, 0, 16, 4),
+    (6000, 320, 200, 1, 16, 5),
+    (6000, 320, 200, 2, 16, 6),
+    (4100, 256, 144, 1, 8, 7),      # 96-byte rows
 ]
 
 
