@@ -326,6 +326,11 @@ GSR_API int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M
                          const float* rotations, const float* cov3D_precomp, int n_views,
                          const gsr_view_slot* views, void* stream, int debug);
 
+/* `accumulate` of gsr_preprocess_backward_views is a set of flags: */
+#define GSR_BWD_ACCUMULATE 1         /* add the parameter gradients to the outputs (a second chunk of views)  */
+#define GSR_BWD_PEER_ACCUMULATORS 2  /* the views' workspaces are peer-GPU memory: fetch the 48-byte accumulator
+                                        rows by bulk asynchronous copies, four views ahead, instead of one
+                                        dependent NVLink load per view                                        */
 GSR_API int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int M, int width,
                          int height, const float* means3D, const float* shs, const float* colors_precomp,
                          const float* scales, float scale_modifier, const float* rotations,

@@ -588,7 +588,7 @@ int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int 
     return launch_preprocess_backward_views(Ps, D, M, make_grid(width, height), means3D, shs, colors_precomp != nullptr,
                                             scales, scale_modifier, rotations, cov3D_precomp, n_views, args, dL_dcolors,
                                             dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drots,
-                                            accumulate != 0, static_cast<cudaStream_t>(stream), debug);
+                                            accumulate, static_cast<cudaStream_t>(stream), debug);
 }
 
 int gsr_adam_step(int n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps, int step,

@@ -139,17 +139,38 @@ __device__ __forceinline__ void sh_backward(int deg, int M, float x, float y, fl
 // kMulti = false: one view, the dL/dsh row is formed in place over the SH values (one shared tile).
 // kMulti = true: the Gaussian's parameters and SH row are read ONCE and the views are looped over;
 // scalar gradients accumulate in registers, dL/dsh in a second shared tile; outputs written once.
-template <bool kMulti, bool kRaw>
-__global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backward_kernel(const BwdParams p) {
+// Multi-view form with PEER accumulators (kRing; the sharded step on more than one GPU): the 48-byte blend
+// accumulators of a Gaussian live in the workspace of the rank that rendered the view.  A dependent remote load per
+// view costs an NVLink round trip (~2 us) eight times in a row per thread; instead every WARP requests the 32 rows of
+// its Gaussians (1536 contiguous bytes) of up to kAccRing views ahead with cp.async.bulk into a shared ring (one
+// mbarrier per ring slot, one arrival per warp) and re-arms a slot for view v + kAccRing as soon as it has consumed
+// view v.  (One request per ROW was measured first: 36 M 48-byte requests run into the copy engine's request rate,
+// ~200 per microsecond and SM — 2.66 -> 4.06 ms on one GPU.)  Costs the fourth CTA per SM, so local accumulators
+// keep the plain loads.
+#ifndef GSR_ACC_RING
+#define GSR_ACC_RING 1   // slots: 1 keeps four CTAs per SM (56.5 KB of shared memory); 4 slots cost the fourth CTA
+#endif
+constexpr int kAccRing = GSR_ACC_RING;
+constexpr size_t kAccRingBytes = (size_t)kAccRing * kBwdThreads * 48;
+
+template <bool kMulti, bool kRaw, bool kRing = false>
+__global__ void __launch_bounds__(kBwdThreads, kMulti ? ((kRing && kAccRing > 1) ? 3 : 4) : 6) preprocess_backward_kernel(const BwdParams p) {
     extern __shared__ __align__(16) float s_dyn[];
     float* s_cam = s_dyn;                                   // view[16] proj[16] campos[3]
     float* tile_in = s_dyn + 36 + (threadIdx.x >> 5) * (32 * kShStride);
     float* tile = kMulti ? tile_in + kBwdWarps * 32 * kShStride : tile_in;   // dL/dsh rows of this warp
+    // kMulti: ring of accumulator rows [slot][thread][3 x float4] + its mbarriers, behind the two SH tiles
+    float4* s_acc = reinterpret_cast<float4*>(s_dyn + 36 + 2 * kBwdWarps * 32 * kShStride);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(s_acc) + kAccRingBytes);
 
     // camera of the first view: staged before anything else so no CTA barrier follows the SH fetch
     if (threadIdx.x < 16) s_cam[threadIdx.x] = __ldg(p.v[0].view + threadIdx.x);
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = __ldg(p.v[0].proj + threadIdx.x - 16);
     else if (threadIdx.x < 35) s_cam[threadIdx.x] = __ldg(p.v[0].campos + threadIdx.x - 32);
+    if (kRing && threadIdx.x == 0) {
+        for (int k = 0; k < kAccRing; ++k) mbar_init(&s_bar[k], kBwdWarps);
+        mbar_init_fence();
+    }
     __syncthreads();
 
     const int idx = blockIdx.x * kBwdThreads + threadIdx.x;
@@ -166,6 +187,23 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
     }
     const bool vis_any = visbits != 0;
     const unsigned vmask = __ballot_sync(0xffffffffu, vis_any);
+    // request the accumulator rows of this warp's Gaussians for view v into ring slot v % kAccRing (one arrival per warp)
+    auto request_acc = [&](int v) {
+        const unsigned any = __ballot_sync(0xffffffffu, (visbits >> v) & 1u);
+        if (lane == 0) {
+            uint64_t* bar = &s_bar[v % kAccRing];
+            const int nrows = min(32, p.P - warp_base);
+            if (any && nrows > 0) {
+                mbar_arrive_expect_tx(bar, 48u * (uint32_t)nrows);
+                bulk_g2s(s_acc + ((v % kAccRing) * kBwdThreads + warp * 32) * 3, p.v[v].grad_accum + (size_t)warp_base * 12,
+                         48u * (uint32_t)nrows, bar);
+            } else {
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+            }
+        }
+    };
+    if (kRing)
+        for (int v = 0; v < min(kAccRing, p.n_views); ++v) request_acc(v);
     const bool do_sh = (p.dL_dsh != nullptr) && !p.colors_precomp;
     const int row = 3 * p.M;
     const int need = 3 * (p.D + 1) * (p.D + 1);
@@ -274,10 +312,21 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? 4 : 6) preprocess_backwa
         const bool vis = (visbits >> vi) & 1u;
         float g2d[2] = {0.f, 0.f};
 
+        if (kRing) mbar_wait(&s_bar[vi % kAccRing], (uint32_t)(vi / kAccRing) & 1u);   // this view's rows have landed
         if (vis) {
             if (kMulti) {
-                const float4* accp = reinterpret_cast<const float4*>(V.grad_accum + (size_t)idx * 12);
+                const float4* accp = kRing ? s_acc + ((vi % kAccRing) * kBwdThreads + threadIdx.x) * 3
+                                           : reinterpret_cast<const float4*>(V.grad_accum + (size_t)idx * 12);
                 a0 = accp[0]; a1 = accp[1]; a2 = accp[2];
+            }
+        }
+        if (kRing && vi + kAccRing < p.n_views) {   // the warp's rows of this slot are in registers: re-arm it for view vi + kAccRing
+            __syncwarp();
+            fence_async_smem();
+            request_acc(vi + kAccRing);
+        }
+        if (vis) {
+            if (kMulti) {
                 if (V.radii_local) {   // forward rows kept locally: only the accumulators come from the view's owner
                     con = __ldg(V.conic_local + idx);
                     clamped_bits = (uint32_t)__ldg(V.radii_local + idx) >> 28;
@@ -873,8 +922,9 @@ __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel
     }
 }
 
-constexpr size_t bwd_smem_bytes(bool multi) {
-    return sizeof(float) * (36 + (size_t)(multi ? 2 : 1) * kBwdWarps * 32 * kShStride);
+constexpr size_t bwd_smem_bytes(bool multi, bool ring = false) {
+    return sizeof(float) * (36 + (size_t)(multi ? 2 : 1) * kBwdWarps * 32 * kShStride) +
+           (ring ? kAccRingBytes + sizeof(uint64_t) * kAccRing : 0);
 }
 
 }  // namespace
@@ -892,10 +942,12 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
         GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, true>,
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
+        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, false, true>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true, true)));
     }
     BwdParams p;
     p.raw = rm.raw; p.sh_rest = rm.sh_rest; p.dL_dsh_rest = rm.dL_dsh_rest;
-    p.accumulate = accumulate;
+    p.accumulate = accumulate & GSR_BWD_ACCUMULATE;
     p.n_views = n_views;
     p.P = P; p.D = D; p.M = M; p.W = g.W; p.H = g.H;
     p.means3D = means3D; p.shs = shs; p.colors_precomp = colors_precomp; p.scales = scales;
@@ -918,7 +970,7 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows, every output requested: the
     // persistent bulk-copy kernel
     static const bool use_tma = [] { const char* e = getenv("GSR_BACKWARD_TMA"); return !e || atoi(e) != 0; }();
-    if (use_tma && !rm.raw && n_views == 1 && !accumulate && shs && !colors_precomp && scales && rotations &&
+    if (use_tma && !rm.raw && n_views == 1 && !(accumulate & GSR_BWD_ACCUMULATE) && shs && !colors_precomp && scales && rotations &&
         !cov3D_precomp && M % 4 == 0 && dL_dsh && dL_dscales && dL_drots && !dL_dcolors && !dL_dcov3D &&
         !views[0].radii_local) {
         static unsigned long long tma_devices = 0;
@@ -935,6 +987,8 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
         else preprocess_backward_kernel<true, true><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
     } else {
         if (n_views == 1) preprocess_backward_kernel<false, false><<<blocks, kBwdThreads, bwd_smem_bytes(false), s>>>(p);
+        else if (accumulate & GSR_BWD_PEER_ACCUMULATORS)
+            preprocess_backward_kernel<true, false, true><<<blocks, kBwdThreads, bwd_smem_bytes(true, true), s>>>(p);
         else preprocess_backward_kernel<true, false><<<blocks, kBwdThreads, bwd_smem_bytes(true), s>>>(p);
     }
     GSR_AFTER_LAUNCH(s, debug);
