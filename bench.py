@@ -463,11 +463,13 @@ def run_b200_arm(args):
 
     for _ in range(warmup):
         ctx = step()
+    # NVML is initialised BEFORE the barrier: nvmlInit takes milliseconds that differ from rank to rank, and host skew
+    # after the barrier lands in the first timed step of every rank (the peers wait for the slowest at the exchange)
+    sampler = ClockSampler(local)
+    events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     barrier()
     # ---- headline: K steps, stage timing OFF, one event per step boundary on the launching stream ----
-    sampler = ClockSampler(local)
     sampler.start()
-    events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     n0 = _native.launch_count()
     # The barrier above leaves every launch queue empty and the ranks' hosts skewed: the first timed step would then
     # measure Python's launch latency (and, with peers, the slowest host) instead of the device (measured: +0.4 ms at
