@@ -467,6 +467,9 @@ def run_b200_arm(args):
     # after the barrier lands in the first timed step of every rank (the peers wait for the slowest at the exchange)
     sampler = ClockSampler(local)
     events = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    align_token = torch.zeros(1, device=dev)
+    if world > 1:
+        dist.all_reduce(align_token)   # communicator warm for the rendezvous below
     barrier()
     # ---- headline: K steps, stage timing OFF, one event per step boundary on the launching stream ----
     sampler.start()
@@ -477,6 +480,10 @@ def run_b200_arm(args):
     # one step ahead, as they do in every later step; stated in config.timing.
     prime_ms = 2.0 if world == 1 else 8.0
     torch.cuda._sleep(int(prime_ms * 1e-3 * (clock_hz(torch, dev))))
+    if world > 1:
+        # ... and a device-side rendezvous behind the delay: a host that was descheduled for a millisecond after the
+        # barrier starts its delay late, and without this its peers' first step would wait for it at the exchange
+        dist.all_reduce(align_token)
     events[0].record()
     for i in range(args.steps):
         ctx = step()
@@ -564,7 +571,7 @@ def run_b200_arm(args):
                    "timing": "value: K steps with per-stage timing OFF, CUDA events per step boundary; after the barrier + synchronize "
                              "and before the first event the stream holds a device-side delay (2 ms; 8 ms with peers) so that "
                              "the launch queue is primed as in every later step instead of timing Python's launch latency "
-                             "on an empty queue; stages: a second pass of K steps with the "
+                             "on an empty queue (with peers, a one-word all-reduce behind the delay aligns the ranks' first event); stages: a second pass of K steps with the "
                              "library's event pairs on (stage_pass_ms_per_step)"},
         "gpu_launches": int(launches),
         "clocks": clocks,
