@@ -425,8 +425,11 @@ __device__ __forceinline__ void stage_run(TK* s_tile, uint32_t* s_val, uint32_t 
     }
 }
 
+#ifndef GSR_EMIT_MINBLOCKS
+#define GSR_EMIT_MINBLOCKS 1
+#endif
 template <typename TK>
-__global__ void __launch_bounds__(kBlk) emit_scan_kernel(int gx, int gy, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(kBlk, GSR_EMIT_MINBLOCKS) emit_scan_kernel(int gx, int gy, const uint32_t* __restrict__ order,
                                                          const int32_t* __restrict__ radii,
                                                          const float2* __restrict__ means2D,
                                                          const gsr_forward_info* __restrict__ info, uint32_t cap,
