@@ -301,9 +301,10 @@ def stage_rooflines(stage_ms, counts, peaks, clocks):
     tile_key_bytes = 2.0 if keybits <= 48 else 4.0
     hbm = {
         "preprocess": 52.0 * P + 259.0 * Pv,
-        # counts + histograms: depths and tiles_touched read (8 P); pass 1 reads P keys and writes the P_visible
-        # (key, index) pairs it keeps, passes 2-4 move P_visible pairs (8 B read + 8 B write)
-        "depth_sort": 12.0 * P + 56.0 * Pv,
+        # pass 1 reads P keys and writes the P_visible (key, index) pairs it keeps, passes 2-4 move P_visible pairs
+        # (8 B read + 8 B write); the counts + histograms come from the persistent preprocess kernel on the single-view
+        # path, from one more read of depths and tiles_touched (8 P) on the multi-view / sharded path
+        "depth_sort": (4.0 if counts.get("depth_counts_in_preprocess") else 12.0) * P + 56.0 * Pv,
         # prefix sum + emission in one kernel: order, radii, means2D read per visible Gaussian; one
         # (tile id, index) entry written per instance (2 + 4 B up to 65536 tiles)
         "emit_keys": 16.0 * Pv + (tile_key_bytes + 4.0) * R,
@@ -526,7 +527,8 @@ def run_b200_arm(args):
     # per RANK and step: this rank preprocesses its slice under all V views and renders L views of all P Gaussians
     counts = dict(P=P * L_views, P_visible=nvis, R=nren, tiles=gx * gy * L_views, pairs_evaluated=ev,
                   pairs_blended=bl, pairs_evaluated_after_culling=ev_ours, warp_splat_iterations=warp_iters,
-                  sum_n_contrib=ncontrib, views_rendered_by_this_rank=L_views, instances_per_view=per_view_R)
+                  sum_n_contrib=ncontrib, views_rendered_by_this_rank=L_views, instances_per_view=per_view_R,
+                  depth_counts_in_preprocess=not sharded)
     stage_ms = {k: v[0] / max(args.steps, 1) for k, v in stages.items() if v[1]}   # per step (a stage may launch N times)
     peaks = load_peaks()
     roofs = stage_rooflines(stage_ms, counts, peaks, clocks)

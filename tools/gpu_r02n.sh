@@ -7,6 +7,7 @@ OUT=gpurun_out; mkdir -p $OUT; rm -f $OUT/grad_report.txt
 timeout 1500 python -m pytest tests -m gpu -q --timeout 900 > $OUT/${TAG}_pytest_gpu.log 2>&1
 echo "pytest exit $?" | tee -a $OUT/${TAG}_pytest_gpu.log; tail -6 $OUT/${TAG}_pytest_gpu.log
 cp $OUT/grad_report.txt $OUT/${TAG}_grad_report.txt 2>/dev/null
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
 timeout 900 python bench.py --steps 20 --warmup 5 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err
 echo "bench exit $?"; head -c 700 $OUT/${TAG}_bench.json; echo; tail -3 $OUT/${TAG}_bench.err
 BENCH="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras"
