@@ -91,3 +91,22 @@ def test_missing_library_fails_loudly(native, monkeypatch, tmp_path):
     monkeypatch.setattr(native, "LIB_PATH", str(tmp_path / "nope.so"))
     with pytest.raises(native.NativeLibraryError):
         native.lib()
+
+
+def test_every_stage_the_library_times_has_a_cost_model_in_the_bench(native):
+    """bench.py divides each stage's measured time into an algorithmic byte / flop count: a stage the library
+    reports without a model would silently vanish from the roofline table."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_for_test", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    L = native.lib()
+    names = [L.gsr_stage_name(i).decode() for i in range(L.gsr_stage_count())]
+    counts = dict(P=1000, P_visible=800, R=3000, tiles=100, pairs_evaluated=10 ** 6, pairs_blended=10 ** 5,
+                  sum_n_contrib=10 ** 6, views_rendered_by_this_rank=1, depth_counts_in_preprocess=True)
+    roofs = bench.stage_rooflines({n: 0.1 for n in names}, counts, bench.load_peaks(), None)
+    assert sorted(roofs) == sorted(names)
+    for n, r in roofs.items():
+        assert r["achieved"] > 0 and r["peak"] > 0 and r["bound"] in ("hbm", "fp32_simt_issue"), n

@@ -261,3 +261,32 @@ def test_running_error_scalar_rules(oracle):
     np.testing.assert_array_equal(out["v"][0], [0.25, 0.0, 0.0, 4.0, 0.0, 9.0])
     assert (out["e"][0][[1, 2, 4]] == 0).all()                    # sums of exact zeros
     assert (out["e"][0][[0, 3, 5]] > 0).all() and (out["e"][0][[0, 3, 5]] < 16 * out["v"][0][[0, 3, 5]]).all()
+
+
+def test_flipped_pixel_rule_on_the_cpu(oracle):
+    """The rule the GPU gradient tests use (helpers.flipped_pixels + grad_check), exercised without a GPU with
+    the binary32 oracle standing in for the CUDA path: dL/dpixel is zeroed only where a skip / stop decision
+    actually differs between the binary32 run and the binary64 running-error run — fragile pixels whose decisions
+    agree carry gradient — and every gradient element then obeys the elementwise bound.  With dL left on the
+    flipped pixels some elements must leave it (that is what makes them worth excluding)."""
+    P, W, H, D = 20000, 640, 360, 3           # the case in which the rule was found necessary (tests/test_gpu_fragile.py)
+    cam, g = Hh.make_case(P, W, H, seed=3)
+    bg = [0.3, 0.2, 0.7]
+    dL_all = np.random.default_rng(203).normal(size=(3, H, W)).astype(np.float32)
+    _, ref32, refre, fragile = Hh.gradient_reference(oracle, cam, g, bg, D, dL_all, threads=8, zero_fragile=False,
+                                                     run_backward=False)
+    flipped = Hh.flipped_pixels(ref32["fwd"]["n_contrib"], ref32["fwd"]["final_T"], ref32, refre)
+    assert flipped.any() and not (flipped & ~fragile).any()
+    assert flipped.mean() < 0.005 and fragile.sum() > 20 * flipped.sum()   # almost every fragile pixel keeps its gradient
+    dL = dL_all.copy()
+    dL[:, flipped] = 0.0
+    oracle.backward(ref32, dL)
+    oracle.backward(refre, dL)
+    for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations"):
+        ok, rep = Hh.grad_check(ref32["grads"][k], refre["grads"][k])
+        assert ok, (k, rep)
+    oracle.backward(ref32, dL_all)
+    oracle.backward(refre, dL_all)
+    outside = sum(Hh.grad_check(ref32["grads"][k], refre["grads"][k])[1]["n_outside"]
+                  for k in ("means3D", "means2D", "opacities"))
+    assert outside > 0
