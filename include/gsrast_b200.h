@@ -113,7 +113,8 @@ GSR_API int gsr_workspace_bytes(int P, int width, int height, int64_t instance_c
                         size_t* geom_bytes, size_t* binning_bytes, size_t* image_bytes);
 GSR_API int gsr_workspace_layout(int P, int width, int height, int64_t instance_capacity, gsr_layout* out);
 
-/* Forward, stage 1 (replaces the first half of `_C.rasterize_gaussians`: preprocess + prefix sum).
+/* Forward, stage 1 (replaces the first half of `_C.rasterize_gaussians`: preprocess, the instance count the
+ * reference takes with its InclusiveSum, and the per-Gaussian depth order the instances are emitted in).
  * Writes radii[P] and the geometry workspace; enqueues a copy of gsr_forward_info (num_rendered,
  * num_visible) into h_info if non-NULL.  D = active SH degree 0..3, M = coefficients per channel
  * in `shs` (>= (D+1)^2, <= 16). */
@@ -275,8 +276,8 @@ GSR_API int gsr_preprocess_slots(int P_ws, int slot_offset, int Ps, int D, int M
                          const float* projmatrix, const float* campos, float tanfovx, float tanfovy,
                          int32_t* radii_slots, void* geom_ws, void* stream, int debug);
 
-/* Depth-order sort + prefix sum over a geometry workspace whose per-Gaussian arrays are already
- * filled (second half of gsr_forward_geometry).  num_visible of the info block is not maintained. */
+/* Counts (num_visible, num_rendered) + depth-order sort over a geometry workspace whose per-Gaussian arrays are already
+ * filled (second half of gsr_forward_geometry). */
 GSR_API int gsr_depth_order(int P, int width, int height, void* geom_ws, gsr_forward_info* h_info,
                             void* stream, int debug);
 
