@@ -268,12 +268,13 @@ class ShardedViewRasterizer:
         """Camera tensors, tan(fov) pairs and the gsr_view_slot arrays of every launch chunk for this camera LIST
         and the current workspace set.  A training loop hands the same list object (or one of a few) every step
         and every address in a slot is fixed for the life of this object, so the ~10 pointer look-ups per view
-        and call are made once per (list, workspace set) instead of twice per step (the entry keeps the list alive,
-        so its id cannot be recycled; a list whose cameras were replaced in place must be a new list)."""
+        and call are made once per (list, workspace set) instead of twice per step.  The entry keeps the settings
+        objects alive and a hit requires the very same objects in the same order, so a recycled id or a list edited
+        in place is a miss, never a stale plan."""
         key = (id(cameras), self.parity)
         hit = self._slot_cache.get(key)
-        if hit is not None and hit[0] is cameras and len(cameras) == self.V:
-            return hit[1:]
+        if hit is not None and len(hit[0]) == len(cameras) and all(a is b for a, b in zip(hit[0], cameras)):
+            return hit[1:]     # the same settings objects in the same order (a list edited in place misses)
         cams = self._camera_tensors(cameras)
         tanfov = [(float(c.tanfovx), float(c.tanfovy)) for c in cameras]
         order = self._view_order()
@@ -284,7 +285,7 @@ class ShardedViewRasterizer:
             chunks.append((len(chunk),) + self._view_slots(chunk, cams, tanfov))
         if len(self._slot_cache) >= 16:
             self._slot_cache.pop(next(iter(self._slot_cache)))
-        self._slot_cache[key] = (cameras, cams, tanfov, chunks)
+        self._slot_cache[key] = (tuple(cameras), cams, tanfov, chunks)
         return cams, tanfov, chunks
 
     def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
