@@ -591,6 +591,8 @@ __global__ void __launch_bounds__(kBwdThreads, kMulti ? ((kRing && kAccRing > 1)
 //     tile's memory phase overlaps the other's arithmetic;
 //   * dL/dsh leaves as one bulk store per row straight from the staged tile (zeros for culled rows: every row of
 //     every gradient array is written, the caller passes uninitialised memory).
+// Raw-parameter mode (kRaw): the activations and their chain rules are applied in registers, the SH values arrive as
+// the tile's two contiguous blocks (dc | rest) and dL/d(dc), dL/d(rest) leave as two bulk stores per tile.
 // SH backward is evaluated coefficient-major here (t_k = g . sh_k, gdir += dY_k/ddir t_k, dL/dsh_k = Y_k g), the
 // same sums as sh_backward in a different association — gradients are a tolerance item (tests/helpers.py).
 constexpr int kBwdShRow4 = 13;
@@ -672,6 +674,29 @@ __device__ __forceinline__ void sh_backward_row(int deg, int row_floats, float x
     }
 }
 
+// The same, coefficient by coefficient, on a row whose coefficient 0 and coefficients 1.. live in two dense blocks
+// (the raw-parameter layout: dc [.,1,3] and rest [.,M-1,3]; scalar accesses, odd strides: conflict-free).
+__device__ __forceinline__ void sh_backward_split(int deg, int M, float x, float y, float z, float* dc, float* rest,
+                                                  const float* g3, float* gdir) {
+    const int used = (deg + 1) * (deg + 1);
+    gdir[0] = gdir[1] = gdir[2] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        if (k >= M) break;
+        float* c = k == 0 ? dc : rest + 3 * (k - 1);
+        if (k < used) {
+            float B, Dx, Dy, Dz;
+            sh_basis(k, x, y, z, B, Dx, Dy, Dz);
+            const float tk = g3[0] * c[0] + g3[1] * c[1] + g3[2] * c[2];
+            gdir[0] += Dx * tk; gdir[1] += Dy * tk; gdir[2] += Dz * tk;
+            c[0] = B * g3[0]; c[1] = B * g3[1]; c[2] = B * g3[2];
+        } else {
+            c[0] = c[1] = c[2] = 0.f;
+        }
+    }
+}
+
+template <bool kRaw>
 __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel(const BwdParams p) {
     extern __shared__ __align__(16) unsigned char s_tma_raw[];
     BwdTmaSmem& sm = *reinterpret_cast<BwdTmaSmem*>(s_tma_raw);
@@ -727,7 +752,7 @@ __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel
     int r_cur = radius_of(tile), r_next = radius_of(tile + (int)gridDim.x);   // radii travel one tile ahead in registers
     // state carried from a tile's phase A to its phase B one iteration later
     bool prev_any = false, prev_vis = false;
-    int prev_idx = 0;
+    int prev_idx = 0, prev_base = 0;
     float pm[3] = {0.f, 0.f, 0.f}, pvm[3] = {0.f, 0.f, 0.f}, pg3[3] = {0.f, 0.f, 0.f};
 
     for (; tile < ntiles || prev_any; tile += gridDim.x) {
@@ -743,11 +768,17 @@ __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel
             float g2d[2] = {0.f, 0.f}, gop = 0.f, gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
             if (vis) {
                 mx = sm.xyz[3 * t]; my = sm.xyz[3 * t + 1]; mz = sm.xyz[3 * t + 2];
-                const float4 q = sm.rot[t];
+                float4 q = sm.rot[t];
+                const float4 q_raw = q;
+                float rs0 = sm.scale[3 * t], rs1 = sm.scale[3 * t + 1], rs2 = sm.scale[3 * t + 2];
+                if (kRaw) {   // pre-activation inputs (scene/gaussian_model.py:28-45)
+                    q = act_rotation(q);
+                    rs0 = act_scale(rs0); rs1 = act_scale(rs1); rs2 = act_scale(rs2);
+                }
                 float s[3], c6[6], R[3][3];
-                s[0] = p.scale_modifier * sm.scale[3 * t];
-                s[1] = p.scale_modifier * sm.scale[3 * t + 1];
-                s[2] = p.scale_modifier * sm.scale[3 * t + 2];
+                s[0] = p.scale_modifier * rs0;
+                s[1] = p.scale_modifier * rs1;
+                s[2] = p.scale_modifier * rs2;
                 cov3d(s[0], s[1], s[2], q, R, c6);
                 const float4 a0 = sm.acc[3 * t], a1 = sm.acc[3 * t + 1], a2 = sm.acc[3 * t + 2], con = sm.con[t];
                 const uint32_t clamped_bits = __float_as_uint(sm.rgb[t].w);
@@ -865,6 +896,16 @@ __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel
                     gq[3] = 2.f * (r * (dR[1][0] - dR[0][1]) + x * (dR[0][2] + dR[2][0]) + y * (dR[1][2] + dR[2][1])) -
                             4.f * z * (dR[0][0] + dR[1][1]);
                 }
+                if (kRaw) {   // chain rules of sigmoid / exp / normalize
+                    const float o = con.w;
+                    gop *= o * (1.0f - o);
+                    gs[0] *= rs0; gs[1] *= rs1; gs[2] *= rs2;
+                    const float n = quat_norm(q_raw);
+                    const float dotp = q.x * gq[0] + q.y * gq[1] + q.z * gq[2] + q.w * gq[3];
+                    const float inv = 1.0f / n;
+                    gq[0] = (gq[0] - q.x * dotp) * inv; gq[1] = (gq[1] - q.y * dotp) * inv;
+                    gq[2] = (gq[2] - q.z * dotp) * inv; gq[3] = (gq[3] - q.w * dotp) * inv;
+                }
             }
             if (valid) {   // everything that does not need the SH row goes out now (zeros for culled rows)
                 const size_t i = (size_t)idx;
@@ -882,35 +923,85 @@ __global__ void __launch_bounds__(kBwdThreads, 5) preprocess_backward_tma_kernel
             mbar_wait(&sm.bar_sh, ph_sh);
             ph_sh ^= 1u;
             float4* r4 = sm.sh + kBwdShRow4 * t;
+            // raw layout: the tile's dc block [128][3], then its rest block [128][3(M-1)], both dense
+            float* dc_row = reinterpret_cast<float*>(sm.sh) + 3 * t;
+            float* rest_row = reinterpret_cast<float*>(sm.sh) + 3 * kBwdThreads + (row - 3) * t;
             float gm[3] = {pvm[0], pvm[1], pvm[2]};
             if (prev_vis) {
                 const float d0 = pm[0] - campos[0], d1 = pm[1] - campos[1], d2 = pm[2] - campos[2];
                 const float s2 = d0 * d0 + d1 * d1 + d2 * d2;
                 const float len = sqrtf(s2);
                 float gdir[3];
-                sh_backward_row(p.D, row, d0 / len, d1 / len, d2 / len, r4, pg3, gdir);
+                if (kRaw) sh_backward_split(p.D, p.M, d0 / len, d1 / len, d2 / len, dc_row, rest_row, pg3, gdir);
+                else sh_backward_row(p.D, row, d0 / len, d1 / len, d2 / len, r4, pg3, gdir);
                 const float inv32 = 1.f / sqrtf(s2 * s2 * s2);
                 const float vd = d0 * gdir[0] + d1 * gdir[1] + d2 * gdir[2];
                 gm[0] += (s2 * gdir[0] - d0 * vd) * inv32;
                 gm[1] += (s2 * gdir[1] - d1 * vd) * inv32;
                 gm[2] += (s2 * gdir[2] - d2 * vd) * inv32;
+            } else if (kRaw) {
+                dc_row[0] = dc_row[1] = dc_row[2] = 0.f;
+                for (int j = 0; j < row - 3; ++j) rest_row[j] = 0.f;
             } else {
                 for (int j = 0; j < (row >> 2); ++j) r4[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             if (prev_idx < p.P) {
                 const size_t i = (size_t)prev_idx;
                 p.dL_dmeans3D[3 * i] = gm[0]; p.dL_dmeans3D[3 * i + 1] = gm[1]; p.dL_dmeans3D[3 * i + 2] = gm[2];
-                fence_async_smem();   // my row, written through the generic proxy, is read by the copy engine next
-                bulk_s2g(p.dL_dsh + i * row, r4, 4u * (uint32_t)row);
-                bulk_commit();
-                bulk_wait_read();     // the staged row may be overwritten once the engine has read it
+                if (!kRaw) {
+                    fence_async_smem();   // my row, written through the generic proxy, is read by the copy engine next
+                    bulk_s2g(p.dL_dsh + i * row, r4, 4u * (uint32_t)row);
+                    bulk_commit();
+                    bulk_wait_read();     // the staged row may be overwritten once the engine has read it
+                }
+            }
+            if (kRaw) {   // the two gradient blocks of the whole tile leave together: dL/d(dc) and dL/d(rest)
+                const int pbase = prev_base;
+                const int n = min(kBwdThreads, p.P - pbase);
+                fence_async_smem();
+                __syncthreads();   // every row of the tile is written
+                float* dcb = reinterpret_cast<float*>(sm.sh);
+                if (n == kBwdThreads) {
+                    if (t == 0) {
+                        bulk_s2g(p.dL_dsh + 3 * (size_t)pbase, dcb, 12u * kBwdThreads);
+                        if (row > 3)
+                            bulk_s2g(p.dL_dsh_rest + (size_t)pbase * (row - 3), dcb + 3 * kBwdThreads,
+                                     4u * (uint32_t)(row - 3) * kBwdThreads);
+                        bulk_commit();
+                        bulk_wait_read();
+                    }
+                } else {   // ragged last tile: plain stores
+                    for (int j = t; j < 3 * n; j += kBwdThreads) p.dL_dsh[3 * (size_t)pbase + j] = dcb[j];
+                    for (int j = t; j < (row - 3) * n; j += kBwdThreads)
+                        p.dL_dsh_rest[(size_t)pbase * (row - 3) + j] = dcb[3 * kBwdThreads + j];
+                }
             }
         }
         const int nvis = __syncthreads_count(vis);   // also: the SH tile is free
         if (cur) {
-            if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, (uint32_t)nvis * need_bytes);
-            if (vis) bulk_g2s(sm.sh + kBwdShRow4 * t, p.shs + (size_t)idx * row, need_bytes, &sm.bar_sh);
+            if (kRaw) {   // two contiguous blocks of the tile's rows (dc | rest), whoever is visible
+                const int n = min(kBwdThreads, p.P - base);
+                float* dcb = reinterpret_cast<float*>(sm.sh);
+                if (n == kBwdThreads) {
+                    if (t == 0) {
+                        const uint32_t b_dc = 12u * kBwdThreads, b_rest = 4u * (uint32_t)(row - 3) * kBwdThreads;
+                        mbar_arrive_expect_tx(&sm.bar_sh, b_dc + b_rest);
+                        bulk_g2s(dcb, p.shs + 3 * (size_t)base, b_dc, &sm.bar_sh);
+                        if (b_rest) bulk_g2s(dcb + 3 * kBwdThreads, p.sh_rest + (size_t)base * (row - 3), b_rest, &sm.bar_sh);
+                    }
+                } else {   // ragged last tile: plain loads, then an empty phase
+                    for (int j = t; j < 3 * n; j += kBwdThreads) dcb[j] = __ldg(p.shs + 3 * (size_t)base + j);
+                    for (int j = t; j < (row - 3) * n; j += kBwdThreads)
+                        dcb[3 * kBwdThreads + j] = __ldg(p.sh_rest + (size_t)base * (row - 3) + j);
+                    __syncthreads();
+                    if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, 0u);
+                }
+            } else {
+                if (t == 0) mbar_arrive_expect_tx(&sm.bar_sh, (uint32_t)nvis * need_bytes);
+                if (vis) bulk_g2s(sm.sh + kBwdShRow4 * t, p.shs + (size_t)idx * row, need_bytes, &sm.bar_sh);
+            }
         }
+        prev_base = base;
         prev_any = cur;
         prev_vis = vis;
         prev_idx = cur ? idx : p.P;
@@ -970,15 +1061,22 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows, every output requested: the
     // persistent bulk-copy kernel
     static const bool use_tma = [] { const char* e = getenv("GSR_BACKWARD_TMA"); return !e || atoi(e) != 0; }();
-    if (use_tma && !rm.raw && n_views == 1 && !(accumulate & GSR_BWD_ACCUMULATE) && shs && !colors_precomp && scales && rotations &&
-        !cov3D_precomp && M % 4 == 0 && dL_dsh && dL_dscales && dL_drots && !dL_dcolors && !dL_dcov3D &&
-        !views[0].radii_local) {
+    static const bool use_tma_raw = [] { const char* e = getenv("GSR_BACKWARD_TMA_RAW"); return !e || atoi(e) != 0; }();
+    const bool raw_ok = rm.raw && use_tma_raw && (M == 1 || (rm.sh_rest && rm.dL_dsh_rest)) &&
+                        ((reinterpret_cast<uintptr_t>(rm.sh_rest) | reinterpret_cast<uintptr_t>(rm.dL_dsh_rest)) & 15) == 0;
+    if (use_tma && (!rm.raw || raw_ok) && n_views == 1 && !(accumulate & GSR_BWD_ACCUMULATE) && shs && !colors_precomp &&
+        scales && rotations && !cov3D_precomp && (rm.raw || M % 4 == 0) && dL_dsh && dL_dscales && dL_drots &&
+        !dL_dcolors && !dL_dcov3D && !views[0].radii_local) {
         static unsigned long long tma_devices = 0;
-        if (first_use_on_current_device(&tma_devices))
-            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)sizeof(BwdTmaSmem)));
+        if (first_use_on_current_device(&tma_devices)) {
+            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel<false>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdTmaSmem)));
+            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel<true>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdTmaSmem)));
+        }
         const unsigned grid = std::min(blocks, 148u * 5u);
-        preprocess_backward_tma_kernel<<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
+        if (rm.raw) preprocess_backward_tma_kernel<true><<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
+        else preprocess_backward_tma_kernel<false><<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
         GSR_AFTER_LAUNCH(s, debug);
         return GSR_OK;
     }
