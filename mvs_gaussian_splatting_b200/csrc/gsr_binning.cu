@@ -380,11 +380,17 @@ constexpr size_t radix_pass_smem(int bits) {
 // instances of its tile.
 constexpr int kEmitSlots = 4;
 constexpr int kEmitChunk = kBlk * kEmitSlots;
-constexpr int kEmitSmall = 12;
-// The per-tile instance counters are kept in kTileReplicas copies (chunk b adds to copy b mod kTileReplicas) and
+#ifndef GSR_EMIT_SMALL
+#define GSR_EMIT_SMALL 12
+#endif
+constexpr int kEmitSmall = GSR_EMIT_SMALL;
+// The per-tile instance counters are kept in kTileReplicas (8) copies (chunk b adds to copy b mod kTileReplicas) and
 // summed by tile_offsets_kernel: 8 M REDs into the ~250 cache lines of one copy saturate the L2 slices that hold the
 // busy screen-centre tiles (ncu: hottest slice at 88 % while the average sits at 28 %).
-constexpr int kTileReplicas = 16;
+#ifndef GSR_TILE_REPLICAS
+#define GSR_TILE_REPLICAS 8   // A/B: 1 copy 0.124 ms emission; 8 / 16 / 32 copies 0.086 ms, tile_offsets 0.015 / 0.019 / 0.023 ms
+#endif
+constexpr int kTileReplicas = GSR_TILE_REPLICAS;
 
 __device__ __forceinline__ void publish_aggregate(unsigned long long* status, uint32_t b, uint32_t total) {
     st_relaxed64(status + b, ((b == 0 ? 2ull : 1ull) << 32) | total);
