@@ -191,3 +191,11 @@ def test_speculative_capacity_overflow_reruns(cuda, oracle):
     assert last_forward_stats(cuda)["reruns"] == 0
     np.testing.assert_array_equal(color2.cpu().numpy(), color.cpu().numpy())  # forward is deterministic
     set_capacity_hint(cuda, None)
+
+
+def test_more_than_65536_tiles_uses_32_bit_tile_ids(cuda, oracle, native):
+    """Up to 65536 tiles an instance is stored as a 16-bit tile id + index; beyond (257 x 257 tiles here) the binning
+    kernels are instantiated for 32-bit tile ids and three tile-bit radix passes: same bit-exact lists, ranges, image."""
+    P, W, H = 3000, 4112, 4112
+    assert native.workspace_layout(P, W, H, 1).b_key_bytes == 4
+    check_forward(cuda, oracle, P, W, H, 3, 16, 11)
