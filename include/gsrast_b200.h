@@ -49,7 +49,9 @@ enum gsr_status {
     GSR_ERR_INVALID_ARGUMENT = 1, /* NULL / inconsistent pointers, negative sizes, bad degree */
     GSR_ERR_CUDA = 2,             /* a CUDA runtime call or (debug mode) a kernel failed     */
     GSR_ERR_WORKSPACE = 3,        /* workspace pointer NULL or misaligned                    */
-    GSR_ERR_UNSUPPORTED = 4       /* e.g. more than 2^16 tiles per axis, M > 16 coefficients */
+    GSR_ERR_UNSUPPORTED = 4,      /* e.g. more than 2^16 tiles per axis, M > 16 coefficients */
+    GSR_ERR_SCRATCH_LIMIT = 5     /* a *_static entry point was given more elements than its built-in
+                                     scratch holds (GSR_LOSS_STATIC_MAX_ELEMS)                */
 };
 
 /* Host-visible result block of a forward call.  `h_info` arguments point at PINNED host memory
@@ -227,6 +229,34 @@ GSR_API int gsr_loss_forward(int C, int H, int W, const float* image, const floa
 GSR_API int gsr_loss_backward(int C, int H, int W, const float* image, const float* gt, double a_l1,
                               double a_ssim, const void* workspace, const float* upstream, float* dL_dimage,
                               void* stream);
+
+/* ---- The same loss and its gradient for callers that cannot allocate (no counterpart in the reference:
+ * there the loss is PyTorch ops and torch's allocator is always at hand, utils/loss_utils.py).
+ * Who this is for: a host that binds this C ABI without an allocator of its own and must not call
+ * cudaMalloc where it calls us — a viewer or evaluation plugin whose render callback is forbidden to
+ * allocate, a service whose device memory was handed out in full at start-up, or a loop that shares the GPU
+ * with other streams (cudaMalloc and cudaFree wait for the whole device, so one call would stall them all).
+ * Such a caller cannot provide the workspace gsr_loss_forward / gsr_loss_backward need.
+ * This one call does both launches — out3 = { a0 + a_l1 * l1 + a_ssim * ssim, l1, ssim } and
+ * dL_dimage = upstream * d(a_l1 * l1 + a_ssim * ssim)/d image (upstream: device scalar or NULL for 1) —
+ * with the scratch (256-byte header + 12 bytes per image element) in an array built into the library.
+ * The caller still owns and passes image, gt, out3 and dL_dimage.  The call makes no cudaMalloc / cudaFree
+ * and uses no allocating library routine.
+ *   Limit: C * H * W <= GSR_LOSS_STATIC_MAX_ELEMS (a 3 x 1080 x 1920 image); larger inputs are refused with
+ *     GSR_ERR_SCRATCH_LIMIT before anything is launched.  Use the workspace form for those.
+ *   Cost: the array (about 71 MiB) occupies device memory on every GPU that loads the library's loss module,
+ *     from that load until the process exits, whether or not this entry point is ever called.
+ *   First call on each device: looks up the array's device address (cudaGetSymbolAddress, with the calling
+ *     thread's current device — make the stream's device current, as for every entry point here).  That
+ *     first call should be made before any stream capture is begun.
+ *   Sharing: every call on a device uses the same array.  It still holds the previous call's contents on
+ *     entry; the call clears the header itself and overwrites every map element it later reads, so nothing
+ *     has to be cleared by the caller.  Two calls that can run on the GPU at the same time (different streams
+ *     without an ordering between them, or two host threads) race on it and give wrong results: order them. */
+#define GSR_LOSS_STATIC_MAX_ELEMS (3 * 1080 * 1920)
+GSR_API int gsr_loss_value_and_grad_static(int C, int H, int W, const float* image, const float* gt, double a0,
+                                           double a_l1, double a_ssim, const float* upstream, float* out3,
+                                           float* dL_dimage, void* stream);
 
 /* ---- The on-disk format either side of the render path (no counterpart in `_C`: the
  * reference reads and writes Gaussian .ply files with per-property Python loops over `plyfile`,

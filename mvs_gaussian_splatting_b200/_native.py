@@ -25,6 +25,8 @@ GSR_ERR_INVALID_ARGUMENT = 1
 GSR_ERR_CUDA = 2
 GSR_ERR_WORKSPACE = 3
 GSR_ERR_UNSUPPORTED = 4
+GSR_ERR_SCRATCH_LIMIT = 5
+LOSS_STATIC_MAX_ELEMS = 3 * 1080 * 1920   # GSR_LOSS_STATIC_MAX_ELEMS
 
 # Every symbol include/gsrast_b200.h declares (tests check the .so exports all of them).
 EXPORTS = (
@@ -38,6 +40,7 @@ EXPORTS = (
     "gsr_adam_step", "gsr_densification_stats",
     "gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward",
     "gsr_ply_unpack", "gsr_ply_pack", "gsr_materialize_keys",
+    "gsr_loss_value_and_grad_static",
 )
 PLY_MAX_PROPS = 96
 MAX_ADAM_GROUPS = 16
@@ -226,6 +229,8 @@ def lib() -> ctypes.CDLL:
         L.gsr_loss_backward.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _vp, _vp, _vp, _vp]
         for name in ("gsr_loss_workspace_bytes", "gsr_loss_forward", "gsr_loss_backward"):
             getattr(L, name).restype = _i
+        L.gsr_loss_value_and_grad_static.argtypes = [_i, _i, _i, _vp, _vp, _d, _d, _d, _vp, _vp, _vp, _vp]
+        L.gsr_loss_value_and_grad_static.restype = _i
         for name in ("gsr_ply_unpack", "gsr_ply_pack"):
             getattr(L, name).argtypes = [ctypes.c_int64, ctypes.POINTER(PlyColumns)] + [_vp] * 8
             getattr(L, name).restype = _i

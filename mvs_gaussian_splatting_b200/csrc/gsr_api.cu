@@ -163,6 +163,9 @@ const char* gsr_status_string(int status) {
         case GSR_ERR_CUDA: return "CUDA error";
         case GSR_ERR_WORKSPACE: return "workspace pointer null or misaligned";
         case GSR_ERR_UNSUPPORTED: return "unsupported size or configuration";
+        case GSR_ERR_SCRATCH_LIMIT:
+            return "input larger than the built-in scratch of this *_static entry point "
+                   "(C*H*W > GSR_LOSS_STATIC_MAX_ELEMS): use the workspace form";
         default: return "unknown status";
     }
 }

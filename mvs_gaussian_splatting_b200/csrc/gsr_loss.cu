@@ -23,6 +23,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <mutex>
 
 #include "gsr_internal.cuh"
 
@@ -322,3 +323,60 @@ int launch_loss_backward(int C, int H, int W, const float* image, const float* g
 }
 
 }  // namespace gsr
+
+// ---- gsr_loss_value_and_grad_static: the loss and its image gradient without a caller-provided workspace ----
+//
+// The two kernels above need scratch in global memory: the 256-byte header (two binary64 sums and the
+// finished-CTA counter) and the three per-pixel derivative maps the forward launch leaves for the backward one
+// (12 bytes per image element).  gsr_loss_forward / gsr_loss_backward take that scratch from the caller.  This
+// entry point is for hosts that have nothing to give: it keeps the scratch in the array below, which the CUDA
+// runtime places in device memory when this file's module is loaded on a GPU and frees at process exit, so the
+// call itself never asks anybody for memory.
+namespace {
+
+constexpr size_t kStaticScratchBytes = gsr::kLossHeaderBytes + (size_t)3 * GSR_LOSS_STATIC_MAX_ELEMS * sizeof(float);
+
+// One copy per GPU that loads the library (about 71 MiB each).  Host code must not hand this NAME to a
+// kernel: on the host it is only a handle for cudaGetSymbolAddress, not a device address.
+static __device__ __align__(256) unsigned char g_loss_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+void* g_static_ptr[kMaxDevices] = {};   // device address of the array on each device, filled on first use
+
+// Looks the array's device address up once per device, with that device current (the address differs from
+// GPU to GPU).  Everything after the first call on a device is a table read under a mutex.
+int static_scratch_on_current_device(void** out) {
+    int dev = -1;
+    GSR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return GSR_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> hold(g_static_mutex);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        GSR_CUDA(cudaGetSymbolAddress(&p, g_loss_static_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255)) return GSR_ERR_WORKSPACE;
+        g_static_ptr[dev] = p;
+    }
+    *out = g_static_ptr[dev];
+    return GSR_OK;
+}
+
+}  // namespace
+
+extern "C" GSR_API int gsr_loss_value_and_grad_static(int C, int H, int W, const float* image, const float* gt,
+                                                      double a0, double a_l1, double a_ssim,
+                                                      const float* upstream, float* out3, float* dL_dimage,
+                                                      void* stream) {
+    if (C <= 0 || H <= 0 || W <= 0 || !image || !gt || !out3 || !dL_dimage) return GSR_ERR_INVALID_ARGUMENT;
+    if (C > 65535 || (H + 31) / 32 > 65535) return GSR_ERR_UNSUPPORTED;
+    if ((long long)C * H * W > (long long)GSR_LOSS_STATIC_MAX_ELEMS) return GSR_ERR_SCRATCH_LIMIT;
+    void* scratch = nullptr;
+    int st = static_scratch_on_current_device(&scratch);
+    if (st != GSR_OK) return st;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    // The forward launch zeroes the header (the sums and the counter still hold the previous call's values)
+    // and overwrites every map element the backward launch will read; nothing else carries over.
+    st = gsr::launch_loss_forward(C, H, W, image, gt, a0, a_l1, a_ssim, scratch, /*save_for_backward=*/true, out3, s);
+    if (st != GSR_OK) return st;
+    return gsr::launch_loss_backward(C, H, W, image, gt, a_l1, a_ssim, scratch, upstream, dL_dimage, s);
+}

@@ -86,6 +86,23 @@ def test_invalid_arguments_are_reported_not_crashed(native):
     assert "workspace" in str(e.value)
 
 
+def test_static_scratch_entry_point_refuses_oversized_input_on_the_host(native):
+    """gsr_loss_value_and_grad_static checks its size limit before it touches the device, so the refusal can
+    be seen without a GPU (the pointers are never dereferenced on the host)."""
+    L = native.lib()
+    fake = ctypes.c_void_p(0x1000)
+    C, W = 3, 1920
+    H = native.LOSS_STATIC_MAX_ELEMS // (C * W) + 1
+    st = L.gsr_loss_value_and_grad_static(C, H, W, fake, fake, 0.2, 0.8, -0.2, None, fake, fake, None)
+    assert st == native.GSR_ERR_SCRATCH_LIMIT
+    assert b"scratch" in L.gsr_status_string(st)
+    assert L.gsr_loss_value_and_grad_static(C, 0, W, fake, fake, 0.2, 0.8, -0.2, None, fake, fake, None) \
+        == native.GSR_ERR_INVALID_ARGUMENT
+    hdr = open(os.path.join(ROOT, "include", "gsrast_b200.h")).read()
+    assert re.search(r"#define\s+GSR_LOSS_STATIC_MAX_ELEMS\s+\(3 \* 1080 \* 1920\)", hdr)
+    assert native.LOSS_STATIC_MAX_ELEMS == 3 * 1080 * 1920
+
+
 def test_missing_library_fails_loudly(native, monkeypatch, tmp_path):
     monkeypatch.setattr(native, "_lib", None)
     monkeypatch.setattr(native, "LIB_PATH", str(tmp_path / "nope.so"))
