@@ -27,6 +27,15 @@ def test_config3_backward_full_parity(cuda, oracle):
     check_backward(cuda, oracle, 3_000_000, 1920, 1080, 3, 16, 0, threads=THREADS)
 
 
+def test_config3_forward_full_parity_orbit_camera(cuda, oracle):
+    """configs[2] under a general camera (rotated W2C, campos != 0): helpers.named_camera("orbit")."""
+    check_forward(cuda, oracle, 3_000_000, 1920, 1080, 3, 16, 0, threads=THREADS, camera="orbit")
+
+
+def test_config3_backward_full_parity_rolled_camera(cuda, oracle):
+    check_backward(cuda, oracle, 3_000_000, 1920, 1080, 3, 16, 0, threads=THREADS, camera="rolled")
+
+
 @pytest.mark.parametrize("D,M", [(3, 16), (0, 1)])
 def test_config5_forward_4k_full_parity(cuda, oracle, D, M):
     check_forward(cuda, oracle, 6_000_000, 3840, 2160, D, M, 0, threads=THREADS)
