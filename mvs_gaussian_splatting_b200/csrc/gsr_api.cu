@@ -21,15 +21,28 @@ int cuda_fail(cudaError_t e) {
     return GSR_ERR_CUDA;
 }
 
-bool first_use_on_current_device(unsigned long long* mask) {
+cudaError_t once_per_device(unsigned long long* mask, cudaError_t (*setup)()) {
     static std::mutex mu;
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;  // unknown: set the attributes again
-    std::lock_guard<std::mutex> lock(mu);
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return setup();  // unknown: set the attributes again
+    std::lock_guard<std::mutex> lock(mu);   // held across setup(): a second thread's first launch waits for the opt-in
     const unsigned long long bit = 1ull << dev;
-    if (*mask & bit) return false;
-    *mask |= bit;
-    return true;
+    if (*mask & bit) return cudaSuccess;
+    const cudaError_t e = setup();
+    if (e == cudaSuccess) *mask |= bit;     // a failed set-up is retried by the next call
+    return e;
+}
+
+int sm_count() {
+    static std::atomic<int> cached[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int n = cached[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
 }
 
 // ---- per-stage timing: event pairs appended while enabled, summed by gsr_stage_timing_read ----
@@ -251,7 +264,7 @@ static int forward_geometry_impl(const RawMode& rm, int P, int D, int M, int wid
             if (D < 0 || D > 3 || M < (D + 1) * (D + 1)) return GSR_ERR_INVALID_ARGUMENT;
             if (M > 16) return GSR_ERR_UNSUPPORTED;
         }
-        if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+        if (!aligned16(means3D) || !aligned16(opacities) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
             !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
             return GSR_ERR_INVALID_ARGUMENT;
         const Grid g = make_grid(width, height);
@@ -317,6 +330,9 @@ static int backward_impl(const RawMode& rm, int P, int D, int M, int width, int 
     if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
     if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
     if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    // the persistent backward kernels fetch these with bulk copies (16-byte aligned source addresses)
+    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations))
+        return GSR_ERR_INVALID_ARGUMENT;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     gsr_layout L;
     compute_layout(P, width, height, instance_capacity, &L);
@@ -361,7 +377,8 @@ static bool raw_args_ok(int M, const float* features_dc, const float* features_r
                         const float* scaling_raw, const float* rotation_raw) {
     if (!features_dc || !opacity_raw || !scaling_raw || !rotation_raw) return false;
     if (M < 1 || M > 16 || (M > 1 && !features_rest)) return false;
-    return aligned16(features_dc) && aligned16(features_rest) && aligned16(scaling_raw) && aligned16(rotation_raw);
+    return aligned16(features_dc) && aligned16(features_rest) && aligned16(opacity_raw) && aligned16(scaling_raw) &&
+           aligned16(rotation_raw);
 }
 
 int gsr_forward_geometry_raw(int P, int D, int M, int width, int height, const float* means3D,
@@ -437,7 +454,7 @@ int gsr_preprocess_slots(int P_ws, int slot_offset, int Ps, int D, int M, int wi
     const bool has_sr = scales != nullptr && rotations != nullptr;
     if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
     if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
-    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+    if (!aligned16(means3D) || !aligned16(opacities) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
         !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
         return GSR_ERR_INVALID_ARGUMENT;
     gsr_layout L;
@@ -502,6 +519,9 @@ int gsr_preprocess_backward_slots(int P_ws, int slot_offset, int Ps, int D, int 
     if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
     if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
     if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    // the persistent backward kernels fetch these with bulk copies (16-byte aligned source addresses)
+    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations))
+        return GSR_ERR_INVALID_ARGUMENT;
     gsr_layout L;
     compute_layout(P_ws, width, height, 0, &L);
     const GeomView gv = offset_rows(geom_view(geom_ws, L), (size_t)slot_offset);
@@ -527,7 +547,7 @@ int gsr_preprocess_views(int P_ws, int slot_offset, int Ps, int D, int M, int wi
     const bool has_sr = scales != nullptr && rotations != nullptr;
     if (has_sr == (cov3D_precomp != nullptr)) return GSR_ERR_INVALID_ARGUMENT;
     if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
-    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
+    if (!aligned16(means3D) || !aligned16(opacities) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations) ||
         !aligned16(cov3D_precomp) || !aligned16(colors_precomp))
         return GSR_ERR_INVALID_ARGUMENT;
     gsr_layout L;
@@ -570,6 +590,9 @@ int gsr_preprocess_backward_views(int P_ws, int slot_offset, int Ps, int D, int 
     if (shs && (D < 0 || D > 3 || M < (D + 1) * (D + 1) || M > 16)) return GSR_ERR_INVALID_ARGUMENT;
     if (has_sr && (!dL_dscales || !dL_drots)) return GSR_ERR_INVALID_ARGUMENT;
     if (!aligned16(dL_dsh) || !aligned16(dL_drots) || !aligned16(dL_dcov3D)) return GSR_ERR_INVALID_ARGUMENT;
+    // the persistent backward kernels fetch these with bulk copies (16-byte aligned source addresses)
+    if (!aligned16(means3D) || !aligned16(shs) || !aligned16(scales) || !aligned16(rotations))
+        return GSR_ERR_INVALID_ARGUMENT;
     gsr_layout L;
     compute_layout(P_ws, width, height, 0, &L);
     BackwardViewArgs args[GSR_MAX_VIEWS];

@@ -1028,14 +1028,15 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
                                      float* dL_drots, int accumulate, cudaStream_t s, int debug, const RawMode& rm) {
     if (n_views < 1 || n_views > kMaxViews) return GSR_ERR_INVALID_ARGUMENT;
     static unsigned long long attr_devices = 0;
-    if (first_use_on_current_device(&attr_devices)) {
-        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, false>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
-        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, true>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true)));
-        GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_kernel<true, false, true>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bwd_smem_bytes(true, true)));
-    }
+    GSR_CUDA(once_per_device(&attr_devices, []() -> cudaError_t {
+        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        cudaError_t e = cudaFuncSetAttribute(preprocess_backward_kernel<true, false>, attr, (int)bwd_smem_bytes(true));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(preprocess_backward_kernel<true, true>, attr, (int)bwd_smem_bytes(true));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(preprocess_backward_kernel<true, false, true>, attr, (int)bwd_smem_bytes(true, true));
+        return e;
+    }));
     BwdParams p;
     p.raw = rm.raw; p.sh_rest = rm.sh_rest; p.dL_dsh_rest = rm.dL_dsh_rest;
     p.accumulate = accumulate & GSR_BWD_ACCUMULATE;
@@ -1060,21 +1061,20 @@ int launch_preprocess_backward_views(int P, int D, int M, const Grid& g, const f
     const unsigned blocks = (unsigned)((P + kBwdThreads - 1) / kBwdThreads);
     // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows, every output requested: the
     // persistent bulk-copy kernel
-    static const bool use_tma = [] { const char* e = getenv("GSR_BACKWARD_TMA"); return !e || atoi(e) != 0; }();
-    static const bool use_tma_raw = [] { const char* e = getenv("GSR_BACKWARD_TMA_RAW"); return !e || atoi(e) != 0; }();
-    const bool raw_ok = rm.raw && use_tma_raw && (M == 1 || (rm.sh_rest && rm.dL_dsh_rest)) &&
+    const bool raw_ok = rm.raw && (M == 1 || (rm.sh_rest && rm.dL_dsh_rest)) &&
                         ((reinterpret_cast<uintptr_t>(rm.sh_rest) | reinterpret_cast<uintptr_t>(rm.dL_dsh_rest)) & 15) == 0;
-    if (use_tma && (!rm.raw || raw_ok) && n_views == 1 && !(accumulate & GSR_BWD_ACCUMULATE) && shs && !colors_precomp &&
+    if ((!rm.raw || raw_ok) && n_views == 1 && !(accumulate & GSR_BWD_ACCUMULATE) && shs && !colors_precomp &&
         scales && rotations && !cov3D_precomp && (rm.raw || M % 4 == 0) && dL_dsh && dL_dscales && dL_drots &&
         !dL_dcolors && !dL_dcov3D && !views[0].radii_local) {
         static unsigned long long tma_devices = 0;
-        if (first_use_on_current_device(&tma_devices)) {
-            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel<false>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdTmaSmem)));
-            GSR_CUDA(cudaFuncSetAttribute(preprocess_backward_tma_kernel<true>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdTmaSmem)));
-        }
-        const unsigned grid = std::min(blocks, 148u * 5u);
+        GSR_CUDA(once_per_device(&tma_devices, []() -> cudaError_t {
+            const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+            cudaError_t e = cudaFuncSetAttribute(preprocess_backward_tma_kernel<false>, attr, (int)sizeof(BwdTmaSmem));
+            if (e == cudaSuccess)
+                e = cudaFuncSetAttribute(preprocess_backward_tma_kernel<true>, attr, (int)sizeof(BwdTmaSmem));
+            return e;
+        }));
+        const unsigned grid = std::min(blocks, (unsigned)sm_count() * 5u);   // 5 CTAs per multiprocessor stay resident
         if (rm.raw) preprocess_backward_tma_kernel<true><<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
         else preprocess_backward_tma_kernel<false><<<grid, kBwdThreads, sizeof(BwdTmaSmem), s>>>(p);
         GSR_AFTER_LAUNCH(s, debug);

@@ -5,8 +5,8 @@
 // lanes of a warp are spatially compact; splats are staged through shared memory in batches of 256 list
 // entries.  Backward (blend_backward2_kernel, the default): 128 threads, TWO pixels per lane, warp w owns an
 // 8x8 block, batches of 128 — the per-(warp, splat) reduction is paid once per 64 pixels (0.750 -> 0.604 ms);
-// the one-pixel backward (blend_backward_kernel) is kept selectable with GSR_BLEND_BWD=1 for A/B runs.  B200-first differences from the reference algorithm, none of which changes
-// a result:
+// the round-1 one-pixel-per-lane backward is gone (A/B builds go through GSRAST_B200_LIB, never an environment
+// switch inside the library).  B200-first differences from the reference algorithm, none of which changes a result:
 //   * two-level exact culling.  Staging applies a CONSERVATIVE ellipse-vs-rectangle test (maximum of
 //     the conic's exponent over the rectangle against -log2(255*opacity)) for the TILE and compacts
 //     the batch in order with a ballot; then every WARP tests the compacted entries, 32 at a time
@@ -25,8 +25,6 @@
 //     butterfly — then flushed as 128-bit vector reductions (RED.E.ADD.F32x4) to L2: three per
 //     (8x4 block, splat) — versus 9 scalar global atomics per contributing (pixel, splat) pair in
 //     the reference.  No CTA-wide barrier inside the walk.
-#include <cstdlib>
-
 #include "gsr_internal.cuh"
 
 namespace gsr {
@@ -309,142 +307,11 @@ __device__ __forceinline__ void flush_parked(int nb, unsigned lane, const float*
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(kBlendThreads, 4) blend_backward_kernel(
-    int gx, int W, int H, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-    const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb,
-    const float* __restrict__ bg, const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-    const float* __restrict__ dL_dpix, float* __restrict__ grad_accum) {
-    // staged entry j = s_e[3j..3j+2]: (x, y, a2, b2) (c2, opacity, tau2, list position 1-based) (r, g, b, gaussian id)
-    __shared__ float4 s_e[3 * kBlendThreads];
-    __shared__ __align__(16) float s_red[kBlendWarps][kRedSplats * 9][32];  // [warp][splat*9 + term][pixel lane]
-    __shared__ __align__(16) float s_tot[kBlendWarps][kRedSplats][12];      // row totals; [..][9..11] stay zero
-    __shared__ uint32_t s_gid[kBlendWarps][kRedSplats + 1];
-    __shared__ int s_wcount[kBlendWarps];
-    __shared__ uint32_t s_wmax[kBlendWarps];
-
-    const TileCtx c = tile_ctx(gx, W, H);
-    const uint2 range = ranges[c.tile];
-    const unsigned lane = lane_id();
-    const int warp = threadIdx.x >> 5;
-    const float fx = (float)c.px, fy = (float)c.py;
-    if (lane < kRedSplats * 3) s_tot[warp][lane / 3][9 + lane % 3] = 0.0f;  // float4 padding of the totals
-    float* const my_red = &s_red[warp][0][lane];
-    int nh = 0;  // parked splats of this warp (carried across chunks and batches)
-
-    float Tfin = 0.f, g0 = 0.f, g1 = 0.f, g2 = 0.f;
-    uint32_t last = 0;
-    if (c.inside) {
-        const size_t pix = (size_t)c.py * W + c.px;
-        const size_t plane = (size_t)W * H;
-        Tfin = final_T[pix];
-        last = n_contrib[pix];
-        g0 = __ldg(dL_dpix + pix);
-        g1 = __ldg(dL_dpix + plane + pix);
-        g2 = __ldg(dL_dpix + 2 * plane + pix);
-    }
-    const float bgdot = __ldg(bg) * g0 + __ldg(bg + 1) * g1 + __ldg(bg + 2) * g2;
-
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);  // nothing behind this matters to the warp
-    if (lane == 0) s_wmax[warp] = wmax;
-    __syncthreads();
-    uint32_t m = 0;
-#pragma unroll
-    for (int i = 0; i < kBlendWarps; ++i) m = max(m, s_wmax[i]);
-
-    float T = Tfin, last_alpha = 0.f;
-    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, bh0 = 0.f, bh1 = 0.f, bh2 = 0.f;
-
-    for (int hi = (int)m; hi > 0; hi -= kBlendThreads) {
-        __syncthreads();
-        const int p = hi - 1 - (int)threadIdx.x;  // descending list position
-        bool keep = false;
-        uint32_t gid = 0;
-        float2 mm = make_float2(0.f, 0.f);
-        float a2 = 0.f, b2 = 0.f, c2 = 0.f, tau2 = 0.f, op = 0.f;
-        if (p >= 0) {
-            gid = __ldg(point_list + range.x + p);
-            mm = __ldg(means2D + gid);
-            const float4 co = __ldg(conic_opacity + gid);
-            op = co.w;
-            keep = stage_test(mm, co, c.tile_rect, a2, b2, c2, tau2);
-        }
-        int total;
-        const int slot = compact_slot(keep, s_wcount, total);
-        if (keep) {
-            const float4 col = __ldg(rgb + gid);
-            s_e[3 * slot] = make_float4(mm.x, mm.y, a2, b2);
-            s_e[3 * slot + 1] = make_float4(c2, op, tau2, __int_as_float(p + 1));
-            s_e[3 * slot + 2] = make_float4(col.x, col.y, col.z, __uint_as_float(gid));
-        }
-        __syncthreads();
-        if (wmax == 0) continue;  // warp-uniform: block outside the image or nothing blended
-
-        for (int cb = 0; cb < total; cb += 32) {
-            const int jt = cb + (int)lane;
-            bool hit = false;
-            if (jt < total) {
-                const float4 ta = s_e[3 * jt];
-                const float4 tb = s_e[3 * jt + 1];
-                hit = ((uint32_t)__float_as_int(tb.w) <= wmax) &&
-                      splat_may_reach(ta.x, ta.y, ta.z, ta.w, tb.x, tb.z, c.warp_rect);
-            }
-            unsigned mask = __ballot_sync(0xffffffffu, hit);
-            while (mask) {
-                const int j = cb + __ffs(mask) - 1;
-                mask &= mask - 1;
-                const float4 g = s_e[3 * j];
-                const float4 cc = s_e[3 * j + 1];
-                const float dx = g.x - fx, dy = g.y - fy;
-                const float pw = fmaf(cc.x * dy, dy, fmaf(g.w, dy, g.z * dx) * dx);
-                const float G = ex2_approx(pw);
-                const float alpha = fminf(0.99f, cc.y * G);
-                const bool ok = ((uint32_t)__float_as_int(cc.w) <= last) && !(pw > 0.0f) && !(alpha < kAlphaMin);
-                if (!__any_sync(0xffffffffu, ok)) continue;
-                const float4 col = s_e[3 * j + 2];
-                // the 9 sums are products of three per-pair scalars; lanes that do not blend keep zeros
-                float h = 0.0f, gdl = 0.0f, wgt = 0.0f;
-                if (ok) {
-                    const float ra = rcp_approx(1.0f - alpha);
-                    T *= ra;
-                    wgt = alpha * T;
-                    bh0 = last_alpha * lc0 + (1.0f - last_alpha) * bh0;
-                    bh1 = last_alpha * lc1 + (1.0f - last_alpha) * bh1;
-                    bh2 = last_alpha * lc2 + (1.0f - last_alpha) * bh2;
-                    lc0 = col.x; lc1 = col.y; lc2 = col.z;
-                    float dL_dalpha = (col.x - bh0) * g0 + (col.y - bh1) * g1 + (col.z - bh2) * g2;
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha -= Tfin * ra * bgdot;
-                    gdl = G * dL_dalpha;
-                    h = cc.y * gdl;  // dL/dG * G
-                }
-                const float hx = h * dx, hy = h * dy;
-                float* dst = my_red + nh * (9 * 32);
-                dst[0 * 32] = hx;
-                dst[1 * 32] = hy;
-                dst[2 * 32] = hx * dx;
-                dst[3 * 32] = hx * dy;
-                dst[4 * 32] = hy * dy;
-                dst[5 * 32] = gdl;
-                dst[6 * 32] = wgt * g0;
-                dst[7 * 32] = wgt * g1;
-                dst[8 * 32] = wgt * g2;
-                if (lane == 0) s_gid[warp][nh] = __float_as_uint(col.w);
-                if (++nh == kRedSplats) {
-                    flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
-                    nh = 0;
-                }
-            }
-        }
-    }
-    if (nh) flush_parked(nh, lane, &s_red[warp][0][0], &s_tot[warp][0][0], s_gid[warp], grad_accum);
-}
-
 // Two pixels per lane: 128 threads per tile, warp w owns an 8x8 pixel block, lane l the pixels
-// (l & 7, l >> 3) and (l & 7, (l >> 3) + 4) of it.  Same decisions and the same per-pair arithmetic as
-// blend_backward_kernel; what changes is that the per-(warp, splat) costs — the walk, the three shared
+// (l & 7, l >> 3) and (l & 7, (l >> 3) + 4) of it.  Same decisions and the same per-pair arithmetic as a
+// one-pixel-per-lane walk; what changes is that the per-(warp, splat) costs — the walk, the three shared
 // loads of the staged entry, and above all the transposed shared-memory reduction (9 stores + the row
-// sums, the pipe that bounds the one-pixel kernel) — are paid once per 64 pixels instead of once per 32:
+// sums, the pipe that bounds a one-pixel kernel) — are paid once per 64 pixels instead of once per 32:
 // each lane adds its two pixels' nine terms in registers before parking them.
 constexpr int kB2Threads = 128;
 constexpr int kB2Warps = 4;
@@ -676,15 +543,9 @@ int launch_blend_backward(int P, const Grid& g, const float* bg, GeomView gv, Bi
                           const float* dL_dpix, cudaStream_t s, int debug) {
     StageScope scope(kStageBlendBwd, s);
     GSR_CUDA(cudaMemsetAsync(gv.grad_accum, 0, sizeof(float) * 12 * (size_t)P, s));
-    static const int variant = [] { const char* e = getenv("GSR_BLEND_BWD"); return e ? atoi(e) : 2; }();
-    if (variant == 2)
-        blend_backward2_kernel<<<g.tiles, kB2Threads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
-                                                              gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
-                                                              dL_dpix, gv.grad_accum);
-    else
-        blend_backward_kernel<<<g.tiles, kBlendThreads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
-                                                                gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
-                                                                dL_dpix, gv.grad_accum);
+    blend_backward2_kernel<<<g.tiles, kB2Threads, 0, s>>>(g.gx, g.W, g.H, iv.ranges, bv.point_list, gv.means2D,
+                                                          gv.conic_opacity, gv.rgb, bg, iv.final_T, iv.n_contrib,
+                                                          dL_dpix, gv.grad_accum);
     GSR_AFTER_LAUNCH(s, debug);
     return GSR_OK;
 }

@@ -56,10 +56,13 @@ struct StageScope {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-// True the first time it is called for `mask` on the CURRENT device (per-device bit set): function
-// attributes such as the dynamic shared-memory opt-in apply only to the device that is current when they
-// are set, and one process may render on several devices.  Racing threads set the same values twice at worst.
-bool first_use_on_current_device(unsigned long long* mask);
+// Runs `setup` once per device (per-device bit in `mask`, for the CURRENT device): function attributes such as
+// the dynamic shared-memory opt-in apply only to the device that is current when they are set, and one process
+// may render on several devices.  The mutex is held across `setup`, so a second thread making its first call on
+// the same device cannot launch before the attributes exist; the bit is set only when `setup` succeeded.
+cudaError_t once_per_device(unsigned long long* mask, cudaError_t (*setup)());
+// Multiprocessors of the current device (cached per device): persistent grids are sized from it.
+int sm_count();
 
 struct Grid {
     int W, H, gx, gy, tiles;

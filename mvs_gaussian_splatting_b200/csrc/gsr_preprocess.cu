@@ -638,10 +638,9 @@ int launch_preprocess_views(int P, int D, int M, const Grid& g, const float* mea
     const int blocks = (P + kPreThreads - 1) / kPreThreads;
     StageScope scope(kStagePreprocess, s);
     // single view, SH colours, scale + rotation inputs, 16-byte-multiple SH rows: the persistent bulk-copy kernel
-    static const bool use_tma = [] { const char* e = getenv("GSR_PREPROCESS_TMA"); return !e || atoi(e) != 0; }();
-    if (use_tma && n_views == 1 && shs && !colors_precomp && scales && rotations && !cov3D_precomp && (3 * M) % 4 == 0 &&
+    if (n_views == 1 && shs && !colors_precomp && scales && rotations && !cov3D_precomp && (3 * M) % 4 == 0 &&
         !views[0].radii_local) {
-        const int grid = std::min(blocks, 148 * 6);
+        const int grid = std::min(blocks, sm_count() * 6);   // 6 CTAs per multiprocessor stay resident
         if (depth_counts_done && views[0].gv.info && views[0].gv.sort_ctl) {   // the caller zeroed the control region
             p.depth_hist = views[0].gv.sort_ctl;
             *depth_counts_done = true;

@@ -148,11 +148,14 @@ class ShardedViewRasterizer:
     single-GPU point of the scaling curve."""
 
     def __init__(self, P: int, M: int, width: int, height: int, device, group=None, exchange: str = "peer",
-                 n_views: Optional[int] = None):
+                 n_views: Optional[int] = None, peer_accumulator_ring: Optional[bool] = None,
+                 standalone: bool = False):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("the B200 rasterizer has no CPU path: tensors must be on a CUDA device")
-        if dist.is_available() and dist.is_initialized():
+        # standalone: this process renders the whole batch by itself (world 1, "local" transport) even though a
+        # process group exists — bench.py measures the single-GPU point of the scaling curve inside an N-rank run
+        if dist.is_available() and dist.is_initialized() and not standalone:
             self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         else:
             self.world, self.rank = 1, 0
@@ -220,12 +223,12 @@ class ShardedViewRasterizer:
         self.radii_local = torch.zeros((V, Ps), dtype=torch.int32, device=dev)
         self.conic_local = f(V, Ps, 4)
         self._state = None
-        self._slot_cache: Dict = {}   # (id(cameras), workspace set) -> camera tensors + gsr_view_slot arrays
-        # GSR_BWD_PEER_ACCUMULATORS: accumulator rows fetched by bulk copies one view ahead (2 GPUs: 1.55 -> 1.39 ms);
-        # GSR_PEER_ACC_RING=0/1 overrides for A/B runs
-        import os
-        ring = os.environ.get("GSR_PEER_ACC_RING", "auto")
-        self._acc_flag = 2 if (ring == "1" or (ring == "auto" and exchange == "peer")) else 0
+        self._slot_cache: Dict = {}   # (ids of the settings objects, workspace set) -> camera tensors + gsr_view_slot arrays
+        # GSR_BWD_PEER_ACCUMULATORS: accumulator rows fetched by bulk copies one view ahead (2 GPUs: 1.55 -> 1.39 ms).
+        # `peer_accumulator_ring` (constructor argument, None = on exactly when the accumulators sit on a peer) lets a
+        # test run the ring kernel on local memory; no environment variable selects a kernel.
+        ring = (exchange == "peer") if peer_accumulator_ring is None else bool(peer_accumulator_ring)
+        self._acc_flag = 2 if ring else 0
 
     # ------------------------------------------------------------------------------------------
     def local_views(self) -> List[int]:
@@ -271,11 +274,16 @@ class ShardedViewRasterizer:
         and call are made once per (list, workspace set) instead of twice per step.  The entry keeps the settings
         objects alive and a hit requires the very same objects in the same order, so a recycled id or a list edited
         in place is a miss, never a stale plan."""
-        key = (id(cameras), self.parity)
+        key = (tuple(id(c) for c in cameras), self.parity)   # a fresh LIST of the same settings objects still hits
         hit = self._slot_cache.get(key)
         if hit is not None and len(hit[0]) == len(cameras) and all(a is b for a, b in zip(hit[0], cameras)):
-            return hit[1:]     # the same settings objects in the same order (a list edited in place misses)
+            return hit[1:]     # the same settings objects in the same order (the entry keeps them alive: no recycled ids)
         cams = self._camera_tensors(cameras)
+        # like rasterizer._settings_cache: a plan is kept only when its camera tensors ARE the caller's tensors.  Where
+        # a camera had to be copied (CPU, strided or non-float32 blocks) the slots point at the copies, and a caller
+        # that refreshes its own tensors in place would be ignored by every later hit.
+        own = all(t is src for c, ts in zip(cameras, cams)
+                  for t, src in zip(ts, (c.viewmatrix, c.projmatrix, c.campos, c.bg)))
         tanfov = [(float(c.tanfovx), float(c.tanfovy)) for c in cameras]
         order = self._view_order()
         step = 1 if self.exchange == "nccl" else _native.MAX_VIEWS   # staged slots sit at different rows: one view per call
@@ -283,9 +291,10 @@ class ShardedViewRasterizer:
         for c0 in range(0, self.V, step):
             chunk = order[c0:c0 + step]
             chunks.append((len(chunk),) + self._view_slots(chunk, cams, tanfov))
-        if len(self._slot_cache) >= 16:
-            self._slot_cache.pop(next(iter(self._slot_cache)))
-        self._slot_cache[key] = (tuple(cameras), cams, tanfov, chunks)
+        if own:
+            if len(self._slot_cache) >= 16:
+                self._slot_cache.pop(next(iter(self._slot_cache)))
+            self._slot_cache[key] = (tuple(cameras), cams, tanfov, chunks)
         return cams, tanfov, chunks
 
     def forward(self, params: Dict[str, torch.Tensor], cameras: Sequence[GaussianRasterizationSettings]):
