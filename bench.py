@@ -563,7 +563,9 @@ def run_b200_arm(args):
         "warmup": warmup, "ms_per_step": ms_step, "ms_per_step_median": ms_median, "ms_per_step_p90": ms_p90,
         "ms_per_step_rank0": ms_all,
         "ms_per_view": ms_step / V, "higher_is_better": True,
-        "scaling": "weak" if (args.views is None and world == 1) or V == world else "strong",
+        # the sharded step splits ONE fixed V-view batch over the N ranks: strong scaling at every N > 1 (the N = 1
+        # headline is configs[2], a different workload; config.n1_same_workload_views_per_s is this batch on one GPU)
+        "scaling": "strong" if (sharded and world > 1) else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_text(P, D, W, H, V), "baseline_config": baseline_config(P, V, W, H),
                    "l2": f"inputs ({236 * P / 1e6:.0f} MB) larger than L2, no flush",
@@ -595,9 +597,42 @@ def run_b200_arm(args):
             line["reference_cuda"] = probe_reference_cuda.summary()
         except Exception as e:   # the probe must never break the bench line
             line["reference_cuda"] = f"probe failed: {e}"
+    if sharded and world > 1 and not args.no_extras:
+        # (1) parity of THIS run's workload on THIS box: every rank renders the batch with the single-GPU entry points
+        # on the full parameter set and with the sharded step on its slice (tools/sharded_check.run_check: images,
+        # radii, sorted lists bit-exact; slice gradients / statistics to 5e-5 relative L1).  A mismatch fails the run.
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import sharded_check
+        del sr, slices, dL_local
+        torch.cuda.empty_cache()
+        ok, worst = sharded_check.run_check(P, W, H, V, dev, rank, world, "nccl" if args.multi == "sharded-nccl" else "peer")
+        flag = torch.tensor([0 if ok else 1], device=dev)
+        dist.all_reduce(flag)
+        parity_ok = flag.item() == 0
+        line["config"]["sharded_parity"] = (f"ok (all {world} ranks; worst slice-gradient rel_l1 on rank 0 {worst:.1e})"
+                                            if parity_ok else f"FAIL on {int(flag.item())} rank(s)")
+        # (2) the same batch on ONE GPU of this box (rank 0, world-1 "local" transport; the other ranks wait): the
+        # like-for-like single-GPU point of the scaling curve, as scalars the driver's record keeps
+        torch.cuda.empty_cache()
+        if rank == 0:
+            one = run_multi_view_batch(torch, dev, D, W, H, 8, P=P, V=V, t=t, standalone=True)
+            line["config"]["n1_same_workload_views_per_s"] = one["value"]
+            line["config"]["n1_same_workload_ms_per_step"] = one["ms_per_step"]
+            line["config"]["efficiency_vs_n1_same_workload"] = value / (world * one["value"])
+            if e2e and e2e.get("value"):
+                line["config"]["e2e_efficiency_vs_n1_same_workload_device_timed"] = e2e["value"] / (world * one["value"])
+        dist.barrier()
+        if not parity_ok:
+            if rank == 0:
+                _emit(line)
+            dist.destroy_process_group()
+            raise SystemExit("bench.py: the sharded step does not match the single-GPU path on this workload")
     if world == 1 and not multi and not args.no_extras:
         line["multi_view_batch"] = run_multi_view_batch(torch, dev, D, W, H, min(args.steps, 5))
+        line["config"]["n1_multi_view_batch_views_per_s"] = line["multi_view_batch"]["value"]
         line["forward_only"] = run_forward_only_extra(torch, dev, min(args.steps, 10), not args.no_cpu_baseline)
+        for name in ("sh3", "sh0"):    # configs[4] as scalars the driver's record keeps
+            line["config"][f"forward_only_fps_{name}"] = line["forward_only"][name]["value"]
         line["raw_entry"] = run_raw_compare(args, torch, dev, t, rs, dL, GaussianRasterizer)
         line["optimizer_step"] = run_optimizer_compare(torch, dev, t)
         line["loss_step"] = run_loss_compare(torch, dev, W, H)
@@ -613,7 +648,7 @@ def run_b200_arm(args):
         dist.destroy_process_group()
 
 
-def run_multi_view_batch(torch, dev, D, W, H, steps, P=6_000_000, V=8):
+def run_multi_view_batch(torch, dev, D, W, H, steps, P=6_000_000, V=8, t=None, standalone=False):
     """BASELINE.json configs[3] on ONE GPU — the single-GPU point of the multi-GPU scaling curve: the same
     Gaussian-sharded step with world 1 ("local" transport): the multi-view per-Gaussian kernels read the 6 M
     parameters once for the 8 views, every view is binned / blended in turn, gradients are summed over the
@@ -621,15 +656,17 @@ def run_multi_view_batch(torch, dev, D, W, H, steps, P=6_000_000, V=8):
     from mvs_gaussian_splatting_b200 import GaussianRasterizationSettings
     from mvs_gaussian_splatting_b200.sharded import ShardedViewRasterizer
     M = 16
-    g = S.make_gaussians(P, S.front_camera(W, H), sh_coeffs=M, seed=0)
-    t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
+    own_t = t is None
+    if own_t:
+        g = S.make_gaussians(P, S.front_camera(W, H), sh_coeffs=M, seed=0)
+        t = {k: torch.from_numpy(v).to(dev) for k, v in g.items()}
     cams = []
     for c in S.batch_cameras(V, W, H):
         kw = S.settings_kwargs(c, [0.0, 0.0, 0.0], D)
         for k in ("bg", "viewmatrix", "projmatrix", "campos"):
             kw[k] = torch.from_numpy(np.ascontiguousarray(kw[k])).to(dev)
         cams.append(GaussianRasterizationSettings(**kw))
-    sr = ShardedViewRasterizer(P, M, W, H, dev, n_views=V)
+    sr = ShardedViewRasterizer(P, M, W, H, dev, n_views=V, standalone=standalone)
     gen = torch.Generator(device="cpu").manual_seed(1234)
     dL = torch.randn(3, H, W, generator=gen).to(dev).unsqueeze(0).expand(V, 3, H, W).contiguous()
     for _ in range(3):
@@ -649,7 +686,9 @@ def run_multi_view_batch(torch, dev, D, W, H, steps, P=6_000_000, V=8):
            "instances_per_view": [int(c.num_rendered) for c in sr._state[0]],
            "note": "the N = 1 point of the configs[3] scaling curve: bench.py --gpus N (N > 1) runs this same batch "
                    "split over N GPUs; efficiency(N) = value(N) / (N x this value)"}
-    del sr, t
+    del sr
+    if own_t:
+        del t
     torch.cuda.empty_cache()
     return out
 

@@ -66,7 +66,24 @@ def _ptr(t: Optional[torch.Tensor]):
 
 
 _tls = threading.local()
-_capacity_hint: dict = {}     # device index -> instance capacity to speculate with
+# Instance capacity to speculate with, per WORKLOAD: (device index, P, W, H) -> capacity.  A loop that alternates
+# resolutions or models (the reference evaluates its test cameras every few thousand iterations, train.py:210-222)
+# keeps one hint per shape instead of re-running binning + blend on every upward switch.  (device index,) alone is
+# the device-wide value set_capacity_hint() installs; a workload's own entry wins over it.
+_capacity_hint: dict = {}
+_HINT_ENTRIES = 64
+
+
+def _hint_lookup(dev_idx: int, P: int, W: int, H: int):
+    h = _capacity_hint.get((dev_idx, P, W, H))
+    return _capacity_hint.get((dev_idx,)) if h is None else h
+
+
+def _hint_store(dev_idx: int, P: int, W: int, H: int, capacity: int) -> None:
+    key = (dev_idx, P, W, H)
+    if key not in _capacity_hint and len(_capacity_hint) >= _HINT_ENTRIES:
+        _capacity_hint.pop(next(iter(_capacity_hint)))
+    _capacity_hint[key] = int(capacity)
 _last_stats: dict = {}
 
 
@@ -85,10 +102,10 @@ def set_capacity_hint(device, capacity: Optional[int]) -> None:
     """Instance capacity the next forward on `device` speculates with (None: forget; the next
     call then waits for the exact count before binning, which is what the reference always does)."""
     idx = torch.device(device).index or 0
-    if capacity is None:
-        _capacity_hint.pop(idx, None)
-    else:
-        _capacity_hint[idx] = int(capacity)
+    for key in [k for k in _capacity_hint if k[0] == idx]:   # the per-workload entries of this device too
+        del _capacity_hint[key]
+    if capacity is not None:
+        _capacity_hint[(idx,)] = int(capacity)
 
 
 def last_forward_stats(device=None) -> dict:
@@ -187,12 +204,13 @@ def _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(device))
 
-    speculative = capacity is None and dev_idx in _capacity_hint
+    hint = _hint_lookup(dev_idx, P, W, H)
+    speculative = capacity is None and hint is not None
     if capacity is None:
         if speculative:
-            capacity = _capacity_hint[dev_idx]
+            capacity = hint
         else:
-            ev.synchronize()           # first call on this device: size exactly, like the reference
+            ev.synchronize()           # first call of this workload on this device: size exactly, like the reference
             capacity = int(info[0, 0])
     capacity = max(int(capacity), 1)
 
@@ -212,8 +230,8 @@ def _render_stage(L, ctx, P, W, H, bg, radii, color, info, capacity, device, dev
         render(R + R // 8 + 1024)
     ctx.num_rendered, ctx.num_visible, ctx.radii = R, nvis, radii
     # speculate next time with 25% head-room over the largest recent count
-    prev = _capacity_hint.get(dev_idx, 0)
-    _capacity_hint[dev_idx] = max(int(prev * 0.97), R + R // 4 + 4096)
+    prev = _capacity_hint.get((dev_idx, P, W, H), 0)
+    _hint_store(dev_idx, P, W, H, max(int(prev * 0.97), R + R // 4 + 4096))
     _last_stats[dev_idx] = dict(num_rendered=R, num_visible=nvis, capacity=ctx.capacity,
                                 reruns=ctx.reruns, speculative=bool(speculative))
 

@@ -229,6 +229,24 @@ def test_speculative_capacity_overflow_reruns(cuda, oracle):
     set_capacity_hint(cuda, None)
 
 
+def test_alternating_resolutions_keep_their_own_capacity_hint(cuda, oracle):
+    """A loop that switches between two image sizes (training views and evaluation views) speculates with each
+    size's own instance capacity: after one pass over both, no forward re-runs its binning."""
+    from mvs_gaussian_splatting_b200 import set_capacity_hint, last_forward_stats
+    set_capacity_hint(cuda, None)
+    cases = [Hh.make_case(5000, 160, 100, seed=2, camera="orbit"), Hh.make_case(5000, 640, 400, seed=2, camera="orbit")]
+    want = [Hh.run_oracle(oracle, cam, g, [0, 0, 0], 3)["binned"]["num_rendered"] for cam, g in cases]
+    assert want[1] > 2 * want[0]            # the small view's hint would overflow on the large one
+    for it in range(3):
+        for (cam, g), R in zip(cases, want):
+            _, _, _, _, ctx, _ = _gpu_forward(cuda, cam, g, [0, 0, 0], 3)
+            st = last_forward_stats(cuda)
+            assert ctx.num_rendered == R
+            assert st["reruns"] == 0, (it, st)
+            assert st["speculative"] == (it > 0)
+    set_capacity_hint(cuda, None)
+
+
 def test_more_than_65536_tiles_uses_32_bit_tile_ids(cuda, oracle, native):
     """Up to 65536 tiles an instance is stored as a 16-bit tile id + index; beyond (257 x 257 tiles here) the binning
     kernels are instantiated for 32-bit tile ids and three tile-bit radix passes: same bit-exact lists, ranges, image."""

@@ -76,3 +76,25 @@ def test_gradient_arena_layout():
         assert v.untyped_storage().data_ptr() == a.flat.untyped_storage().data_ptr()
     a.shs.fill_(2.0)
     assert float(a.flat.sum()) == 2.0 * 3 * M * P
+
+
+def test_capacity_hints_are_kept_per_workload():
+    """rasterizer._capacity_hint: one speculative instance capacity per (device, P, W, H); set_capacity_hint installs a
+    device-wide value that a workload's own entry overrides, and forgets every entry of that device."""
+    from mvs_gaussian_splatting_b200 import rasterizer as R
+    R._capacity_hint.clear()
+    assert R._hint_lookup(0, 1000, 64, 64) is None
+    R._hint_store(0, 1000, 64, 64, 5000)
+    R._hint_store(0, 1000, 128, 128, 20000)          # another resolution of the same model keeps its own hint
+    assert R._hint_lookup(0, 1000, 64, 64) == 5000 and R._hint_lookup(0, 1000, 128, 128) == 20000
+    assert R._hint_lookup(1, 1000, 64, 64) is None   # per device
+    R.set_capacity_hint("cuda:0", 16)                # device-wide: drops the per-workload entries of cuda:0 ...
+    assert R._hint_lookup(0, 1000, 64, 64) == 16 and R._hint_lookup(0, 7, 8, 8) == 16
+    R._hint_store(0, 1000, 64, 64, 6000)             # ... until a forward of that workload stores its own again
+    assert R._hint_lookup(0, 1000, 64, 64) == 6000 and R._hint_lookup(0, 1000, 128, 128) == 16
+    R.set_capacity_hint("cuda:0", None)
+    assert R._hint_lookup(0, 1000, 64, 64) is None
+    for i in range(3 * R._HINT_ENTRIES):             # bounded
+        R._hint_store(0, i, 8, 8, 1)
+    assert len(R._capacity_hint) <= R._HINT_ENTRIES
+    R._capacity_hint.clear()
