@@ -234,7 +234,8 @@ def test_alternating_resolutions_keep_their_own_capacity_hint(cuda, oracle):
     size's own instance capacity: after one pass over both, no forward re-runs its binning."""
     from mvs_gaussian_splatting_b200 import set_capacity_hint, last_forward_stats
     set_capacity_hint(cuda, None)
-    cases = [Hh.make_case(5000, 160, 100, seed=2, camera="orbit"), Hh.make_case(5000, 640, 400, seed=2, camera="orbit")]
+    # (splat sizes are drawn in pixels, so the instance count follows the number of Gaussians, not the resolution)
+    cases = [Hh.make_case(2000, 160, 100, seed=2, camera="orbit"), Hh.make_case(20000, 640, 400, seed=2, camera="orbit")]
     want = [Hh.run_oracle(oracle, cam, g, [0, 0, 0], 3)["binned"]["num_rendered"] for cam, g in cases]
     assert want[1] > 2 * want[0]            # the small view's hint would overflow on the large one
     for it in range(3):
